@@ -1,0 +1,1044 @@
+// Host side of libkvarq_b200.so: the C ABI of include/kvarq_b200.h, the FastQ streaming reader
+// (plain / gzip / in-memory) that cuts the stream exactly where the reference's fastq_read would
+// (csrc/workhorse.c:737-956), the pinned multi-buffered batch pipeline and result marshalling.
+// All matching happens in scan_kernel.cu; there is no CPU matcher in this library.
+#include <cuda_runtime.h>
+#include <zlib.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/kvarq_b200.h"
+#include "kvq_device.h"
+
+namespace {
+
+constexpr int64_t REF_CHUNK = 1024 * 1024;          // SCANBUFSIZE, workhorse.c:15
+constexpr int64_t BATCH_BYTES = 64ll << 20;         // stream bytes per GPU batch
+constexpr int64_t BATCH_PAD = 256;                  // readable slack behind a batch
+constexpr int NSLOT = 3;
+
+struct KvqError {
+    int cls; std::string msg;
+    KvqError(int c, const std::string &m) : cls(c), msg(m) {}
+};
+
+inline void cuda_check(cudaError_t e, const char *what)
+{
+    if (e != cudaSuccess)
+        throw KvqError(KVQ_ERR_RUNTIME, std::string("CUDA failure in ") + what + ": " + cudaGetErrorString(e));
+}
+#define CK(call) cuda_check((call), #call)
+
+double now_ms()
+{
+    using namespace std::chrono;
+    return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+// ------------------------------------------------------------------------------- byte sources
+// One "file" of the scan.  fill() behaves like the fread / mz_inflate block of fastq_read:
+// it delivers up to cap bytes and says whether the window could be filled.
+struct Source {
+    virtual ~Source() {}
+    virtual int64_t fill(char *dst, int64_t cap, bool *window_filled) = 0;
+    virtual int64_t disk_size() const = 0;          // on-disk (compressed) size
+    virtual int64_t disk_pos() const = 0;           // ftell() of the reference at this point
+    virtual bool compressed() const = 0;
+};
+
+struct MemSource : Source {
+    const char *p; int64_t n, at;
+    MemSource(const char *p_, int64_t n_) : p(p_), n(n_), at(0) {}
+    int64_t fill(char *dst, int64_t cap, bool *filled) override {
+        int64_t m = std::min(cap, n - at);
+        memcpy(dst, p + at, m); at += m;
+        *filled = (m == cap);
+        return m;
+    }
+    int64_t disk_size() const override { return n; }
+    int64_t disk_pos() const override { return at; }
+    bool compressed() const override { return false; }
+};
+
+struct PlainFileSource : Source {
+    FILE *fd; int64_t size;
+    explicit PlainFileSource(const char *name) {
+        fd = fopen(name, "rb");
+        if (!fd) throw KvqError(KVQ_ERR_IO, "cannot open file");                     // workhorse.c:577
+        fseek(fd, 0, SEEK_END); size = ftell(fd); fseek(fd, 0, SEEK_SET);
+        setvbuf(fd, nullptr, _IONBF, 0);
+    }
+    ~PlainFileSource() override { if (fd) fclose(fd); }
+    int64_t fill(char *dst, int64_t cap, bool *filled) override {
+        int64_t m = (int64_t) fread(dst, 1, cap, fd);
+        if (ferror(fd)) throw KvqError(KVQ_ERR_IO, "error while reading from file in fastq_read");   // :894
+        *filled = (m == cap);       // feof() is set exactly when fread came up short (:901)
+        return m;
+    }
+    int64_t disk_size() const override { return size; }
+    int64_t disk_pos() const override { return ftell(fd); }
+    bool compressed() const override { return false; }
+};
+
+// gzip member header (skip_gz_header, workhorse.c:482-541): magic, method, flags, optional fields
+const char *skip_gzip_header(FILE *fd, int dist)
+{
+    int state = 0, junk = 0, c = fgetc(fd);
+    while (state != 2 && junk <= dist && c != EOF) {
+        if (state == 0 && c == 0x1F) state = 1;
+        else if (state == 1 && c == 0x8B) state = 2;
+        else { state = 0; junk++; }
+        c = fgetc(fd);
+    }
+    if (state != 2) return "magic bytes not found";
+    if (c != 8) return "expected method==DEFLATED";
+    int flags = fgetc(fd);
+    if (flags & (0x02 | 0x20 | 0xC0)) return "unsupported flags (CONTINUATION or ENCRYPTED or RESERVED)";
+    for (int i = 0; i < 6; i++) (void) fgetc(fd);
+    if (flags & 0x04) { int n = fgetc(fd); n |= fgetc(fd) << 8; while (n-- > 0) (void) fgetc(fd); }
+    if (flags & 0x08) { do c = fgetc(fd); while (c > 0); }
+    if (flags & 0x10) { do c = fgetc(fd); while (c > 0); }
+    return nullptr;
+}
+
+// .gz input: raw inflate of every member (workhorse.c:781-885), zlib instead of miniz
+struct GzFileSource : Source {
+    FILE *fd; int64_t size, remaining; z_stream zs; std::vector<unsigned char> in;
+    explicit GzFileSource(const char *name) : in(REF_CHUNK) {
+        fd = fopen(name, "rb");
+        if (!fd) throw KvqError(KVQ_ERR_IO, "cannot open file");
+        memset(&zs, 0, sizeof(zs));
+        if (inflateInit2(&zs, -15) != Z_OK) { fclose(fd); throw KvqError(KVQ_ERR_RUNTIME, "cannot mz_inflateInit()"); }
+        fseek(fd, 0, SEEK_END); size = remaining = ftell(fd); fseek(fd, 0, SEEK_SET);
+        const char *msg = skip_gzip_header(fd, 0);
+        if (msg) {
+            inflateEnd(&zs); fclose(fd);
+            throw KvqError(KVQ_ERR_IO, std::string("no valid gzip header found at beginning of file : ") + msg);
+        }
+        remaining -= ftell(fd);
+    }
+    ~GzFileSource() override { inflateEnd(&zs); if (fd) fclose(fd); }
+    int64_t fill(char *dst, int64_t cap, bool *filled) override {
+        int64_t got = 0;
+        zs.next_out = (unsigned char *) dst; zs.avail_out = (unsigned) cap;
+        do {
+            if (zs.avail_in == 0) {
+                int64_t m = std::min<int64_t>(REF_CHUNK, remaining);
+                if ((int64_t) fread(in.data(), 1, m, fd) != m)
+                    throw KvqError(KVQ_ERR_IO, "could not read enough bytes from .fastq.gz");
+                zs.next_in = in.data(); zs.avail_in = (unsigned) m; remaining -= m;
+            }
+            unsigned before = zs.avail_out;
+            int st = inflate(&zs, Z_SYNC_FLUSH);
+            if (st == Z_BUF_ERROR && zs.avail_out == 0) st = Z_OK;
+            if (st != Z_OK && st != Z_STREAM_END)
+                throw KvqError(KVQ_ERR_IO, "error while inflating compressed data : status=" + std::to_string(st));
+            got += before - zs.avail_out;
+            if (st == Z_STREAM_END && remaining + zs.avail_in > 10) {
+                // another member may follow after <= 10 junk bytes (:842-866)
+                fseek(fd, -((long) zs.avail_in), SEEK_CUR);
+                remaining += zs.avail_in;
+                long pos = ftell(fd);
+                if (skip_gzip_header(fd, 10) != nullptr) { remaining = 0; zs.avail_in = 0; break; }
+                remaining -= ftell(fd) - pos;
+                inflateReset2(&zs, -15);
+                zs.avail_in = 0;
+            } else if (st == Z_STREAM_END) {
+                break;
+            }
+        } while (remaining + zs.avail_in > 10 && zs.avail_out > 0);
+        *filled = (zs.avail_out == 0);
+        return got;
+    }
+    int64_t disk_size() const override { return size; }
+    int64_t disk_pos() const override { return ftell(fd); }
+    bool compressed() const override { return true; }
+};
+
+bool has_gz_suffix(const std::string &s)
+{
+    return s.size() >= 3 && s.compare(s.size() - 3, 3, ".gz") == 0;                 // workhorse.c:582
+}
+
+} // namespace
+
+namespace {
+
+// ------------------------------------------------------------------------------- stream cutter
+// fastq_rewind (workhorse.c:696-718): going backwards, a line that starts with '+' arms the
+// search, the next line start holding '@' is where the deferred tail begins.
+int64_t deferred_tail(const char *buf, int64_t n)
+{
+    bool armed = false;
+    for (int64_t back = 1; back + 1 < n; back++) {
+        const char c = buf[n - back], prev = buf[n - back - 1];
+        const bool line_start = (prev == '\n' || prev == '\r');
+        if (c == '+' && line_start) armed = true;
+        else if (armed && c == '@' && line_start) return back;
+    }
+    return -1;
+}
+
+struct LiveStats {                      // what engine.stats() may read while a scan runs
+    std::atomic<int64_t> parsed{0}, total{0}, records{0}, longest{-1}, sigints{0};
+    std::atomic<int64_t> rls[KVQ_MAX_READLENGTH];
+    std::vector<std::atomic<int64_t>> seqhits, seqbasehits;
+    void reset(int nseqs) {
+        parsed = 0; total = 0; records = 0; longest = -1; sigints = 0;
+        for (auto &r : rls) r = 0;
+        seqhits = std::vector<std::atomic<int64_t>>(nseqs);
+        seqbasehits = std::vector<std::atomic<int64_t>>(nseqs);
+        for (auto &v : seqhits) v = 0;
+        for (auto &v : seqbasehits) v = 0;
+    }
+};
+
+struct HostBatch {
+    char *data = nullptr;               // pinned, BATCH_BYTES + BATCH_PAD
+    int64_t nbytes = 0;
+    int64_t base_fpos = 0;
+    std::vector<int64_t> cuts;          // segment boundaries, cuts[0] == 0, cuts.back() == nbytes
+};
+
+// Reproduces the sequence of fastq_read() calls of one reference worker thread and lays the
+// returned chunks back to back into batches.
+class StreamCutter {
+public:
+    StreamCutter(std::vector<std::string> names, std::vector<std::pair<const char *, int64_t>> mems,
+                 LiveStats *live)
+        : names_(std::move(names)), mems_(std::move(mems)), live_(live)
+    {
+        nfiles_ = names_.empty() ? (int) mems_.size() : (int) names_.size();
+        // fastq_open (:659-677): total size first, then the first file
+        for (int i = 0; i < nfiles_; i++) {
+            if (!names_.empty()) {
+                FILE *fd = fopen(names_[i].c_str(), "rb");
+                if (!fd) throw KvqError(KVQ_ERR_IO, "cannot open file '" + names_[i] + "' for getting filesize");
+                fseek(fd, 0, SEEK_END); size_all_ += ftell(fd); fclose(fd);
+            } else size_all_ += mems_[i].second;
+        }
+        live_->parsed = 0; live_->total = size_all_;
+        if (nfiles_ == 0) { finished_ = true; return; }
+        open_next();
+    }
+
+    bool finished() const { return finished_; }
+
+    // Fills one batch; returns false when the stream is exhausted and the batch is empty.
+    bool next_batch(HostBatch &b, const std::atomic<int> &stop)
+    {
+        b.cuts.clear(); b.cuts.push_back(0); b.nbytes = 0;
+        int64_t left = (int64_t) carry_.size();
+        if (left) memcpy(b.data, carry_.data(), left);
+        carry_.clear();
+        b.base_fpos = fpos_ - left;
+        int64_t win = 0;
+        while (!finished_) {
+            if (stop.load(std::memory_order_relaxed)) { finished_ = true; left = 0; break; }
+            if (win + REF_CHUNK > BATCH_BYTES) break;                       // batch full
+            if (at_eof_ && next_file_ < nfiles_) open_next();               // :749-753
+            at_eof_ = false;
+            bool filled = false;
+            const int64_t got = src_->fill(b.data + win + left, REF_CHUNK - left, &filled);
+            at_eof_ = !filled;
+            if (compressed_) {                                              // :883-884, single precision
+                float est = (float) (uint64_t) size_all_ * (float) (uint64_t) (fpos_ + got)
+                          / (float) (uint64_t) (done_disk_ + src_->disk_pos());
+                live_->total = (int64_t) (uint64_t) est;
+            }
+            if (got == 0) {                                                 // :905-910
+                if (left == 0) { finished_ = true; break; }
+                win += left; b.cuts.push_back(win); left = 0;
+                continue;
+            }
+            fpos_ += got; live_->parsed += got;
+            if (!at_eof_) {
+                const int64_t t = deferred_tail(b.data + win, left + got);
+                if (t < 0)
+                    throw KvqError(KVQ_ERR_RUNTIME, "could find beginning of record; read " + std::to_string(got)
+                                   + " bytes up to " + std::to_string(src_->disk_pos()));
+                win += left + got - t; left = t;
+            } else {
+                win += left + got; left = 0;
+            }
+            b.cuts.push_back(win);
+        }
+        if (left) carry_.assign(b.data + win, b.data + win + left);
+        b.nbytes = win;
+        memset(b.data + win, 0, BATCH_PAD);
+        return win > 0;
+    }
+
+private:
+    void open_next()                                                        // fastq_open_next, :559-629
+    {
+        if (src_) { done_disk_ += src_->disk_pos(); src_.reset(); }
+        const int i = next_file_++;
+        if (!names_.empty()) {
+            if (has_gz_suffix(names_[i])) {
+                src_.reset(new GzFileSource(names_[i].c_str()));
+                compressed_ = true;
+                live_->total = live_->total * 3;                            // "random guess", :625
+            } else {
+                if (compressed_)
+                    throw KvqError(KVQ_ERR_IO, "error while inflating compressed data : plain file after .gz");
+                src_.reset(new PlainFileSource(names_[i].c_str()));
+            }
+        } else {
+            src_.reset(new MemSource(mems_[i].first, mems_[i].second));
+        }
+    }
+
+    std::vector<std::string> names_;
+    std::vector<std::pair<const char *, int64_t>> mems_;
+    LiveStats *live_;
+    int nfiles_ = 0, next_file_ = 0;
+    std::unique_ptr<Source> src_;
+    bool at_eof_ = false, compressed_ = false, finished_ = false;
+    int64_t size_all_ = 0, done_disk_ = 0, fpos_ = 0;
+    std::vector<char> carry_;
+};
+
+} // namespace
+
+namespace {
+
+// ------------------------------------------------------------------------------- device memory
+struct DevBuf {
+    void *p = nullptr; size_t cap = 0;
+    ~DevBuf() { if (p) cudaFree(p); }
+    void ensure(size_t n) {
+        if (n <= cap && p) return;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = std::max<size_t>(n, 256);
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { p = nullptr; throw KvqError(KVQ_ERR_MEMORY, std::string("cudaMalloc: ") + cudaGetErrorString(e)); }
+        cap = want;
+    }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct PinBuf {
+    void *p = nullptr; size_t cap = 0;
+    ~PinBuf() { if (p) cudaFreeHost(p); }
+    void ensure(size_t n) {
+        if (n <= cap && p) return;
+        if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+        cudaError_t e = cudaHostAlloc(&p, n, cudaHostAllocDefault);
+        if (e != cudaSuccess) { p = nullptr; throw KvqError(KVQ_ERR_MEMORY, std::string("cudaHostAlloc: ") + cudaGetErrorString(e)); }
+        cap = n;
+    }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+template <class T> void upload(DevBuf &d, const std::vector<T> &v, size_t min_elems = 1)
+{
+    d.ensure(std::max(v.size(), min_elems) * sizeof(T));
+    if (!v.empty()) CK(cudaMemcpy(d.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+}
+
+// ------------------------------------------------------------------------------- templates
+inline uint32_t code_of(unsigned char c) { return KVQ_CODE(c); }
+
+uint32_t kmer_key(const unsigned char *s)            // KVQ_SEED_K bases, base 0 in the low bits
+{
+    uint32_t k = 0;
+    for (int i = 0; i < KVQ_SEED_K; i++) k |= code_of(s[i]) << (2 * i);
+    return k;
+}
+
+struct SeedTable {
+    std::vector<uint32_t> bitmap, off; std::vector<uint2> ent;
+    void build(std::vector<std::pair<uint32_t, uint2>> &items) {
+        bitmap.assign(KVQ_BITMAP_WORDS, 0); off.assign(KVQ_NKEYS + 1, 0); ent.resize(items.size());
+        for (auto &it : items) { off[it.first + 1]++; bitmap[it.first >> 5] |= 1u << (it.first & 31); }
+        for (int k = 0; k < KVQ_NKEYS; k++) off[k + 1] += off[k];
+        std::vector<uint32_t> at(off.begin(), off.end() - 1);
+        for (auto &it : items) ent[at[it.first]++] = it.second;
+    }
+};
+
+struct TemplateSet {
+    int nseqs = 0, nplus = 0; int64_t cov_total = 0;
+    std::vector<int32_t> len;
+    KvqTemplates dev{}; KvqParams par{};
+    DevBuf d_bytes, d_boff, d_packed, d_poff, d_len, d_seedable, d_exh;
+    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff;
+
+    static unsigned char comp(unsigned char c) {
+        switch (c) { case 'A': return 'T'; case 'T': return 'A'; case 'C': return 'G'; case 'G': return 'C'; default: return c; }
+    }
+
+    void build(const char *const *seqs, const int32_t *lens, int n, int np, const kvq_config_t &cfg)
+    {
+        if (n < 0 || (n > 0 && (!seqs || !lens))) throw KvqError(KVQ_ERR_TYPE, "seqlist must be sequence of strings");
+        nseqs = n; nplus = np; len.assign(lens, lens + n);
+        for (int i = 0; i < n; i++)
+            if (lens[i] < 0 || !seqs[i]) throw KvqError(KVQ_ERR_TYPE, "seqlist must be list of strings");
+        if (np > 0) {
+            if (n != 2 * np) throw KvqError(KVQ_ERR_TYPE, "nplus must be half the number of sequences");
+            for (int i = 0; i < np; i++) {
+                if (lens[i] != lens[np + i]) throw KvqError(KVQ_ERR_TYPE, "minus sequence length differs from plus sequence");
+                for (int j = 0; j < lens[i]; j++)
+                    if ((unsigned char) seqs[np + i][j] != comp((unsigned char) seqs[i][lens[i] - 1 - j]))
+                        throw KvqError(KVQ_ERR_TYPE, "seqs[nplus+i] is not the reverse complement of seqs[i]");
+            }
+        }
+        const int E = cfg.maxerrors, O = cfg.minoverlap;
+        const int pieces = E + 1;
+        const bool seed_ok = E >= 0 && pieces <= KVQ_MAX_PIECES && O >= 1 && O / pieces >= KVQ_SEED_K;
+
+        std::vector<uint8_t> bytes; std::vector<uint32_t> boff(n + 1, 0), packed, poff(n + 1, 0);
+        std::vector<uint8_t> seedable(n, 0); std::vector<int32_t> exh;
+        std::vector<std::pair<uint32_t, uint2>> it1, it2;
+        int max_len = 0;
+        for (int i = 0; i < n; i++) {
+            const unsigned char *s = (const unsigned char *) seqs[i]; const int sl = lens[i];
+            boff[i] = (uint32_t) bytes.size(); bytes.insert(bytes.end(), s, s + sl);
+            poff[i] = (uint32_t) packed.size();
+            const int words = (sl + 15) / 16 + 2;
+            packed.resize(packed.size() + words, 0);
+            for (int j = 0; j < sl; j++) packed[poff[i] + j / 16] |= code_of(s[j]) << (2 * (j % 16));
+            max_len = std::max(max_len, sl);
+            const bool ok = seed_ok && sl / pieces >= KVQ_SEED_K && sl <= KVQ_MAX_SEEDED_SEQLEN;
+            seedable[i] = ok;
+            if (!ok) { exh.push_back(i); continue; }
+            for (int j = 0; j < pieces; j++) {
+                const int toff = (int) ((int64_t) j * sl / pieces);
+                it1.push_back({kmer_key(s + toff), make_uint2((unsigned) i, (unsigned) toff)});
+            }
+            for (int toff = 0; toff + KVQ_SEED_K <= sl; toff++)
+                it2.push_back({kmer_key(s + toff), make_uint2((unsigned) i, (unsigned) toff)});
+        }
+        boff[n] = (uint32_t) bytes.size(); poff[n] = (uint32_t) packed.size();
+        bytes.resize(bytes.size() + 64, 0);
+        SeedTable t1, t2; t1.build(it1); t2.build(it2);
+        std::vector<uint32_t> covoff(np + 1, 0);
+        for (int i = 0; i < np; i++) covoff[i + 1] = covoff[i] + (uint32_t) lens[i];
+        cov_total = np > 0 ? covoff[np] : 0;
+
+        upload(d_bytes, bytes); upload(d_boff, boff); upload(d_packed, packed, 4); upload(d_poff, poff);
+        upload(d_len, len); upload(d_seedable, seedable); upload(d_exh, exh);
+        upload(d_bm1, t1.bitmap); upload(d_off1, t1.off); upload(d_ent1, t1.ent);
+        upload(d_bm2, t2.bitmap); upload(d_off2, t2.off); upload(d_ent2, t2.ent);
+        upload(d_covoff, covoff);
+
+        dev.bytes = d_bytes.as<uint8_t>(); dev.byte_off = d_boff.as<uint32_t>();
+        dev.packed = d_packed.as<uint32_t>(); dev.packed_off = d_poff.as<uint32_t>();
+        dev.len = d_len.as<int32_t>(); dev.seedable = d_seedable.as<uint8_t>();
+        dev.exh_list = d_exh.as<int32_t>(); dev.nseqs = n; dev.n_exh = (int) exh.size();
+        dev.t1_bitmap = d_bm1.as<uint32_t>(); dev.t1_off = d_off1.as<uint32_t>(); dev.t1_ent = d_ent1.as<uint2>();
+        dev.t2_bitmap = d_bm2.as<uint32_t>(); dev.t2_off = d_off2.as<uint32_t>(); dev.t2_ent = d_ent2.as<uint2>();
+        dev.cov_off = d_covoff.as<uint32_t>(); dev.nplus = np;
+
+        par.maxerrors = E; par.minoverlap = O; par.minreadlength = cfg.minreadlength;
+        par.amin = (int) (signed char) cfg.Amin;
+        par.seed_ok = seed_ok; par.npieces = pieces < 1 ? 1 : pieces; par.max_seqlen = max_len;
+        par.want_hits = 1; par.accumulate = 1;
+    }
+};
+
+} // namespace
+
+// ------------------------------------------------------------------------------- engine objects
+struct kvq_result {
+    std::vector<kvq_hit_t> hits;
+    std::vector<char> blob;
+    std::vector<int64_t> offsets;
+    kvq_stats_t stats{};
+    std::vector<int64_t> nseqhits, nseqbasehits, coverage, mutcount;
+    kvq_timing_t timing{};
+};
+
+namespace {
+
+struct Slot {                           // one batch in flight
+    HostBatch hb; PinBuf pin;
+    DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs;
+    PinBuf h_ctr, h_seg;
+    cudaStream_t stream = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
+    int64_t data_bytes = 0;
+};
+
+struct Accum {                          // device-wide accumulators of one scan
+    DevBuf d_seqhits, d_seqbase, d_cov, d_mut;
+};
+
+struct RawHit { KvqHitRec h; };
+
+} // namespace
+
+struct kvq_engine {
+    int device = 0, sm_count = 148;
+    kvq_config_t cfg{0, 20, 10, 1, '!', '!'};      // workhorse.c:71-75
+    std::mutex mu;                                  // guards cfg / running / error
+    bool running = false;
+    std::atomic<int> stop{0};
+    int err_cls = 0; std::string err_msg;
+    LiveStats live;
+    Slot slots[NSLOT]; bool slots_ready = false;
+    Accum acc;
+    TemplateSet tpl;
+
+    void set_error(int cls, const std::string &m) { std::lock_guard<std::mutex> g(mu); err_cls = cls; err_msg = m; }
+};
+
+struct kvq_staged {
+    kvq_engine *e = nullptr;
+    DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs;
+    size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
+    int64_t nbytes = 0, base_fpos = 0, parsed = 0, total = 0; int nseg = 0;
+};
+
+namespace {
+
+void init_slots(kvq_engine *e)
+{
+    if (e->slots_ready) return;
+    for (auto &s : e->slots) {
+        s.pin.ensure(BATCH_BYTES + BATCH_PAD);
+        s.hb.data = s.pin.as<char>();
+        s.d_data.ensure(BATCH_BYTES + BATCH_PAD);
+        const size_t nseg_max = (size_t) (BATCH_BYTES / 4096) + 64;     // cuts are >= 1 byte apart; see launch
+        s.d_seg.ensure(nseg_max * sizeof(int64_t)); s.h_seg.ensure(nseg_max * sizeof(int64_t));
+        s.d_ctr.ensure(sizeof(KvqCounters)); s.h_ctr.ensure(sizeof(KvqCounters));
+        s.long_cap = (size_t) (BATCH_BYTES / 1024) + 64;
+        s.d_longs.ensure(s.long_cap * sizeof(KvqLongRec));
+        s.hit_cap = 1u << 18; s.d_hits.ensure(s.hit_cap * sizeof(KvqHitRec));
+        s.blob_cap = 32u << 20; s.d_blob.ensure(s.blob_cap);
+        CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        CK(cudaEventCreate(&s.ev0)); CK(cudaEventCreate(&s.ev1));
+    }
+    e->slots_ready = true;
+}
+
+struct ScanTotals {
+    std::vector<KvqHitRec> hits; std::vector<char> blob;
+    int64_t rls[KVQ_HIST]; int64_t longest = -1, records = 0, bases = 0, exh = 0, cands = 0;
+    unsigned long long err_key = ~0ULL;
+    double kernel_ms = 0; int64_t launches = 0, h2d = 0, d2h = 0, stream_bytes = 0;
+    ScanTotals() { memset(rls, 0, sizeof(rls)); }
+};
+
+KvqOut make_out(kvq_engine *e, DevBuf &ctr, DevBuf &hits, size_t hit_cap, DevBuf &blob, size_t blob_cap,
+                DevBuf &longs, size_t long_cap)
+{
+    KvqOut o{};
+    o.ctr = ctr.as<KvqCounters>();
+    o.hits = hits.as<KvqHitRec>(); o.hit_cap = hit_cap;
+    o.blob = blob.as<uint8_t>(); o.blob_cap = blob_cap;
+    o.longs = longs.as<KvqLongRec>(); o.long_cap = long_cap;
+    o.nseqhits = e->acc.d_seqhits.as<unsigned long long>();
+    o.nseqbasehits = e->acc.d_seqbase.as<unsigned long long>();
+    o.coverage = e->acc.d_cov.as<unsigned long long>();
+    o.mutcount = e->acc.d_mut.as<unsigned long long>();
+    return o;
+}
+
+void reset_accum(kvq_engine *e)
+{
+    const TemplateSet &t = e->tpl;
+    const size_t ns = std::max(1, t.nseqs), nc = (size_t) std::max<int64_t>(1, t.cov_total);
+    e->acc.d_seqhits.ensure(ns * 8); e->acc.d_seqbase.ensure(ns * 8);
+    e->acc.d_cov.ensure(nc * 8); e->acc.d_mut.ensure(nc * 6 * 8);
+    CK(cudaMemset(e->acc.d_seqhits.p, 0, ns * 8)); CK(cudaMemset(e->acc.d_seqbase.p, 0, ns * 8));
+    CK(cudaMemset(e->acc.d_cov.p, 0, nc * 8)); CK(cudaMemset(e->acc.d_mut.p, 0, nc * 6 * 8));
+}
+
+// enqueue memset + scan + long-record kernels for one batch already resident on the device
+void enqueue_kernels(kvq_engine *e, const KvqBatch &b, const KvqParams &p, const KvqOut &o,
+                     cudaStream_t st, cudaEvent_t ev0, cudaEvent_t ev1)
+{
+    CK(cudaMemsetAsync(o.ctr, 0, sizeof(KvqCounters), st));
+    CK(cudaMemsetAsync(&o.ctr->err_key, 0xFF, sizeof(unsigned long long), st));
+    if (ev0) CK(cudaEventRecord(ev0, st));
+    cuda_check((cudaError_t) kvq_launch_scan(b, e->tpl.dev, p, o, e->sm_count, st), "scan kernel launch");
+    cuda_check((cudaError_t) kvq_launch_long(b, e->tpl.dev, p, o, e->sm_count, st), "long-record kernel launch");
+    if (ev1) CK(cudaEventRecord(ev1, st));
+}
+
+void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
+{
+    const HostBatch &hb = s.hb;
+    const int nseg = (int) hb.cuts.size() - 1;
+    s.d_seg.ensure(hb.cuts.size() * 8); s.h_seg.ensure(hb.cuts.size() * 8);
+    memcpy(s.h_seg.p, hb.cuts.data(), hb.cuts.size() * 8);
+    CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes + BATCH_PAD, cudaMemcpyHostToDevice, s.stream));
+    CK(cudaMemcpyAsync(s.d_seg.p, s.h_seg.p, hb.cuts.size() * 8, cudaMemcpyHostToDevice, s.stream));
+    KvqBatch b{s.d_data.as<uint8_t>(), hb.nbytes, s.d_seg.as<int64_t>(), nseg, hb.base_fpos};
+    KvqOut o = make_out(e, s.d_ctr, s.d_hits, s.hit_cap, s.d_blob, s.blob_cap, s.d_longs, s.long_cap);
+    enqueue_kernels(e, b, e->tpl.par, o, s.stream, s.ev0, s.ev1);
+    CK(cudaMemcpyAsync(s.h_ctr.p, s.d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s.stream));
+    tot.launches += 2; tot.h2d += hb.nbytes + (int64_t) hb.cuts.size() * 8; tot.d2h += sizeof(KvqCounters);
+    tot.stream_bytes += hb.nbytes;
+}
+
+// Fetch hits of a finished batch (re-running it with larger buffers when they overflowed).
+void collect_hits(kvq_engine *e, const KvqBatch &b, DevBuf &d_ctr, DevBuf &d_hits, size_t &hit_cap,
+                  DevBuf &d_blob, size_t &blob_cap, DevBuf &d_longs, size_t long_cap,
+                  const KvqCounters &c, cudaStream_t st, ScanTotals &tot)
+{
+    unsigned long long nh = c.hit_count, nb = c.blob_used;
+    if (nh > hit_cap || nb > blob_cap) {
+        hit_cap = (size_t) (nh + nh / 4 + 1024); blob_cap = (size_t) (nb + nb / 4 + 4096);
+        d_hits.ensure(hit_cap * sizeof(KvqHitRec)); d_blob.ensure(blob_cap);
+        KvqParams p = e->tpl.par; p.accumulate = 0;
+        KvqOut o = make_out(e, d_ctr, d_hits, hit_cap, d_blob, blob_cap, d_longs, long_cap);
+        enqueue_kernels(e, b, p, o, st, nullptr, nullptr);
+        CK(cudaStreamSynchronize(st));
+        tot.launches += 2;
+    }
+    if (nh == 0) return;
+    const size_t h0 = tot.hits.size(), b0 = tot.blob.size();
+    tot.hits.resize(h0 + nh); tot.blob.resize(b0 + nb);
+    CK(cudaMemcpyAsync(tot.hits.data() + h0, d_hits.p, nh * sizeof(KvqHitRec), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(tot.blob.data() + b0, d_blob.p, nb, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    for (size_t i = h0; i < h0 + nh; i++) tot.hits[i].blob_off += (int64_t) b0;
+    tot.d2h += (int64_t) (nh * sizeof(KvqHitRec) + nb);
+}
+
+void add_counters(kvq_engine *e, const KvqCounters &c, ScanTotals &tot)
+{
+    for (int i = 0; i < KVQ_HIST; i++) if (c.rls[i]) { tot.rls[i] += (int64_t) c.rls[i]; e->live.rls[i] += (int64_t) c.rls[i]; }
+    tot.longest = std::max<int64_t>(tot.longest, c.longest);
+    if (c.longest > e->live.longest) e->live.longest = c.longest;
+    tot.records += (int64_t) c.records; e->live.records += (int64_t) c.records;
+    tot.bases += (int64_t) c.bases; tot.exh += (int64_t) c.exhaustive_reads; tot.cands += (int64_t) c.candidates;
+    tot.err_key = std::min(tot.err_key, c.err_key);
+}
+
+void harvest_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
+{
+    CK(cudaStreamSynchronize(s.stream));
+    float ms = 0; CK(cudaEventElapsedTime(&ms, s.ev0, s.ev1)); tot.kernel_ms += ms;
+    const KvqCounters &c = *s.h_ctr.as<KvqCounters>();
+    add_counters(e, c, tot);
+    KvqBatch b{s.d_data.as<uint8_t>(), s.hb.nbytes, s.d_seg.as<int64_t>(), (int) s.hb.cuts.size() - 1, s.hb.base_fpos};
+    if (e->tpl.par.want_hits)
+        collect_hits(e, b, s.d_ctr, s.d_hits, s.hit_cap, s.d_blob, s.blob_cap, s.d_longs, s.long_cap, c, s.stream, tot);
+    // live per-template counters for engine.stats()
+    if (e->tpl.nseqs > 0) {
+        std::vector<unsigned long long> a(e->tpl.nseqs), bb(e->tpl.nseqs);
+        CK(cudaMemcpy(a.data(), e->acc.d_seqhits.p, a.size() * 8, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(bb.data(), e->acc.d_seqbase.p, bb.size() * 8, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < e->tpl.nseqs; i++) { e->live.seqhits[i] = (int64_t) a[i]; e->live.seqbasehits[i] = (int64_t) bb[i]; }
+    }
+}
+
+} // namespace
+
+namespace {
+
+template <class T> class Chan {        // tiny blocking queue
+public:
+    void push(T v) { { std::lock_guard<std::mutex> g(mu_); q_.push_back(v); } cv_.notify_one(); }
+    T pop() { std::unique_lock<std::mutex> g(mu_); cv_.wait(g, [&] { return !q_.empty(); }); T v = q_.front(); q_.pop_front(); return v; }
+private:
+    std::mutex mu_; std::condition_variable cv_; std::deque<T> q_;
+};
+
+// reference emission order for nthreads=1 (workhorse.c:1107-1175): file order, then template,
+// then (a) shifts descending, (b) shifts descending, (c)/(d) shifts ascending
+bool hit_before(const KvqHitRec &x, const KvqHitRec &y)
+{
+    if (x.file_pos != y.file_pos) return x.file_pos < y.file_pos;
+    if (x.seq_nr != y.seq_nr) return x.seq_nr < y.seq_nr;
+    if (x.rule != y.rule) return x.rule < y.rule;
+    const int ox = x.rule == 0 ? x.seq_pos : x.rule == 1 ? -x.seq_pos : std::abs(x.seq_pos);
+    const int oy = y.rule == 0 ? y.seq_pos : y.rule == 1 ? -y.seq_pos : std::abs(y.seq_pos);
+    return ox < oy;
+}
+
+std::string format_error_message(unsigned long long key)
+{
+    // see report_format_error() in scan_kernel.cu; texts are workhorse.c:1039-1046
+    const long long rec = (long long) (key >> 22); const int type = (int) ((key >> 21) & 1);
+    const unsigned payload = (unsigned) (key & 0x1FFFFF);
+    char buf[256];
+    if (type == 0)
+        snprintf(buf, sizeof(buf), "record must start with '@' (and not '%c') fpos=%ld", (char) payload, (long) rec);
+    else
+        snprintf(buf, sizeof(buf), "3rd line of record must start with '+' fpos=%ld", (long) (rec + payload));
+    return buf;
+}
+
+void fill_stats(kvq_engine *e, kvq_stats_t &st, const int64_t *rls, int64_t longest, int64_t records)
+{
+    memset(&st, 0, sizeof(st));
+    for (int i = 0; i < KVQ_MAX_READLENGTH; i++) st.readlengths[i] = rls[i];
+    st.rls_longest = longest; st.records_parsed = records;
+    st.parsed = e->live.parsed; st.total = e->live.total; st.sigints = e->live.sigints;
+    st.progress = 0;
+    if (st.total > 0)                                                       // workhorse.c:1230-1232
+        st.progress = ((float) (uint64_t) std::min(st.parsed, st.total)) / (float) (uint64_t) st.total;
+    st.nseqs = e->tpl.nseqs;
+}
+
+kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
+{
+    std::unique_ptr<kvq_result> r(new kvq_result());
+    std::stable_sort(tot.hits.begin(), tot.hits.end(), hit_before);
+    const size_t nh = tot.hits.size();
+    r->hits.resize(nh); r->offsets.resize(nh + 1); r->blob.resize(tot.blob.size());
+    int64_t at = 0;
+    for (size_t i = 0; i < nh; i++) {
+        const KvqHitRec &h = tot.hits[i];
+        r->hits[i] = kvq_hit_t{h.seq_nr, h.seq_pos, h.file_pos, h.length, h.readlength};
+        r->offsets[i] = at;
+        memcpy(r->blob.data() + at, tot.blob.data() + h.blob_off, h.length);
+        at += h.length;
+    }
+    r->offsets[nh] = at;
+    fill_stats(e, r->stats, tot.rls, tot.longest, tot.records);
+    const int ns = e->tpl.nseqs; const int64_t nc = e->tpl.cov_total;
+    r->nseqhits.assign(ns, 0); r->nseqbasehits.assign(ns, 0);
+    if (ns > 0) {
+        CK(cudaMemcpy(r->nseqhits.data(), e->acc.d_seqhits.p, (size_t) ns * 8, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(r->nseqbasehits.data(), e->acc.d_seqbase.p, (size_t) ns * 8, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < ns; i++) { e->live.seqhits[i] = r->nseqhits[i]; e->live.seqbasehits[i] = r->nseqbasehits[i]; }
+    }
+    if (e->tpl.nplus > 0 && nc > 0) {
+        r->coverage.resize(nc); r->mutcount.resize(nc * 6);
+        CK(cudaMemcpy(r->coverage.data(), e->acc.d_cov.p, (size_t) nc * 8, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(r->mutcount.data(), e->acc.d_mut.p, (size_t) nc * 48, cudaMemcpyDeviceToHost));
+        tot.d2h += nc * 56;
+    }
+    tot.d2h += (int64_t) ns * 16;
+    r->timing.kernel_ms = tot.kernel_ms; r->timing.wall_ms = wall_ms; r->timing.launches = tot.launches;
+    r->timing.h2d_bytes = tot.h2d; r->timing.d2h_bytes = tot.d2h; r->timing.bases = tot.bases;
+    r->timing.stream_bytes = tot.stream_bytes; r->timing.exhaustive_reads = tot.exh; r->timing.candidates = tot.cands;
+    return r.release();
+}
+
+// The whole streaming scan: a producer thread cuts the stream into pinned batches while this
+// thread keeps up to two batches in flight on the GPU.
+kvq_result *run_stream_scan(kvq_engine *e, std::vector<std::string> names,
+                            std::vector<std::pair<const char *, int64_t>> mems)
+{
+    const double t_begin = now_ms();
+    init_slots(e);
+    reset_accum(e);
+    StreamCutter cutter(std::move(names), std::move(mems), &e->live);
+    ScanTotals tot;
+    Chan<int> free_q, ready_q;
+    for (int i = 0; i < NSLOT; i++) free_q.push(i);
+    std::unique_ptr<KvqError> producer_err;
+    std::atomic<int> abort_flag{0};
+    std::thread producer([&] {
+        try {
+            for (;;) {
+                int si = free_q.pop();
+                if (si < 0 || abort_flag.load()) break;
+                if (!cutter.next_batch(e->slots[si].hb, e->stop)) break;
+                ready_q.push(si);
+            }
+        } catch (const KvqError &err) { producer_err.reset(new KvqError(err)); }
+        catch (const std::exception &err) { producer_err.reset(new KvqError(KVQ_ERR_RUNTIME, err.what())); }
+        ready_q.push(-1);
+    });
+    std::unique_ptr<KvqError> consumer_err;
+    std::deque<int> inflight;
+    try {
+        for (;;) {
+            int si = ready_q.pop();
+            if (si < 0) break;
+            launch_slot(e, e->slots[si], tot);
+            inflight.push_back(si);
+            if ((int) inflight.size() >= 2) {
+                int done = inflight.front(); inflight.pop_front();
+                harvest_slot(e, e->slots[done], tot);
+                free_q.push(done);
+                if (tot.err_key != ~0ULL) e->stop = 1;          // first format error ends the scan
+            }
+        }
+        while (!inflight.empty()) {
+            int done = inflight.front(); inflight.pop_front();
+            harvest_slot(e, e->slots[done], tot);
+        }
+    } catch (const KvqError &err) {
+        consumer_err.reset(new KvqError(err));
+        abort_flag = 1; e->stop = 1;
+        cudaDeviceSynchronize();
+        for (int i = 0; i < NSLOT + 1; i++) free_q.push(-1);
+        // drain so the producer can finish
+        std::thread drain([&] { for (;;) { if (ready_q.pop() < 0) break; } });
+        producer.join(); drain.join();
+        throw *consumer_err;
+    }
+    free_q.push(-1);
+    producer.join();
+    // a format error lies in data already scanned, i.e. before whatever stopped the reader
+    if (tot.err_key != ~0ULL) throw KvqError(KVQ_ERR_FASTQ_FORMAT, format_error_message(tot.err_key));
+    if (producer_err) throw *producer_err;
+    return finish_result(e, tot, now_ms() - t_begin);
+}
+
+} // namespace
+
+// ------------------------------------------------------------------------------- C ABI
+namespace {
+
+struct RunGuard {                       // `running` flag of workhorse.c:1258-1265
+    kvq_engine *e; bool owns = false;
+    explicit RunGuard(kvq_engine *e_) : e(e_) {
+        std::lock_guard<std::mutex> g(e->mu);
+        if (e->running) return;
+        e->running = true; owns = true;
+    }
+    ~RunGuard() { if (owns) { std::lock_guard<std::mutex> g(e->mu); e->running = false; } }
+};
+
+template <class F> int guarded(kvq_engine *e, F &&body)
+{
+    if (!e) return KVQ_ERR_TYPE;
+    try { body(); return KVQ_OK; }
+    catch (const KvqError &err) { e->set_error(err.cls, err.msg); return err.cls; }
+    catch (const std::bad_alloc &) { e->set_error(KVQ_ERR_MEMORY, "out of memory"); return KVQ_ERR_MEMORY; }
+    catch (const std::exception &err) { e->set_error(KVQ_ERR_RUNTIME, err.what()); return KVQ_ERR_RUNTIME; }
+}
+
+int scan_entry(kvq_engine *e, std::vector<std::string> names, std::vector<std::pair<const char *, int64_t>> mems,
+               const char *const *seqs, const int32_t *seqlens, int nseqs, int nplus, kvq_result **out)
+{
+    if (out) *out = nullptr;
+    return guarded(e, [&] {
+        if (!out) throw KvqError(KVQ_ERR_TYPE, "result pointer is NULL");
+        RunGuard run(e);
+        if (!run.owns) throw KvqError(KVQ_ERR_RUNTIME, "findseqs() already running!");
+        e->stop = 0;
+        CK(cudaSetDevice(e->device));
+        kvq_config_t cfg;
+        { std::lock_guard<std::mutex> g(e->mu); cfg = e->cfg; }
+        { std::lock_guard<std::mutex> g(e->mu); e->live.reset(nseqs); }
+        e->tpl.build(seqs, seqlens, nseqs, nplus, cfg);
+        *out = run_stream_scan(e, std::move(names), std::move(mems));
+    });
+}
+
+} // namespace
+
+extern "C" {
+
+const char *kvq_version(void) { return "kvarq_b200 0.1 (sm_100a)"; }
+
+int kvq_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int kvq_create(kvq_engine **out, int device)
+{
+    if (!out) return KVQ_ERR_TYPE;
+    *out = nullptr;
+    int n = kvq_device_count();
+    if (n <= 0 || device < 0 || device >= n) return KVQ_ERR_RUNTIME;     // no CPU fallback
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return KVQ_ERR_RUNTIME;
+    if (prop.major < 10) return KVQ_ERR_RUNTIME;                         // kernels are sm_100a only
+    kvq_engine *e = new kvq_engine();
+    e->device = device; e->sm_count = prop.multiProcessorCount;
+    *out = e;
+    return KVQ_OK;
+}
+
+void kvq_destroy(kvq_engine *e)
+{
+    if (!e) return;
+    cudaSetDevice(e->device);
+    for (auto &s : e->slots) {
+        if (s.stream) cudaStreamDestroy(s.stream);
+        if (s.ev0) cudaEventDestroy(s.ev0);
+        if (s.ev1) cudaEventDestroy(s.ev1);
+    }
+    delete e;
+}
+
+int kvq_config(kvq_engine *e, const kvq_config_t *cfg)
+{
+    if (!e || !cfg) return KVQ_ERR_TYPE;
+    std::lock_guard<std::mutex> g(e->mu);
+    e->cfg = *cfg;
+    return KVQ_OK;
+}
+
+int kvq_get_config(kvq_engine *e, kvq_config_t *cfg)
+{
+    if (!e || !cfg) return KVQ_ERR_TYPE;
+    std::lock_guard<std::mutex> g(e->mu);
+    *cfg = e->cfg;
+    return KVQ_OK;
+}
+
+int kvq_findseqs(kvq_engine *e, const char *const *fnames, int nfiles, const char *const *seqs,
+                 const int32_t *seqlens, int nseqs, int nplus, kvq_result **out)
+{
+    std::vector<std::string> names;
+    if (nfiles < 0 || (nfiles > 0 && !fnames)) { if (e) e->set_error(KVQ_ERR_TYPE, "fname must be [sequence of] string[s]"); return KVQ_ERR_TYPE; }
+    for (int i = 0; i < nfiles; i++) {
+        if (!fnames[i]) { e->set_error(KVQ_ERR_TYPE, "fname must be [sequence of] string[s]"); return KVQ_ERR_TYPE; }
+        names.push_back(fnames[i]);
+    }
+    return scan_entry(e, std::move(names), {}, seqs, seqlens, nseqs, nplus, out);
+}
+
+int kvq_findseqs_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens, int nbufs,
+                     const char *const *seqs, const int32_t *seqlens, int nseqs, int nplus, kvq_result **out)
+{
+    std::vector<std::pair<const char *, int64_t>> mems;
+    if (nbufs < 0 || (nbufs > 0 && (!bufs || !buflens))) { if (e) e->set_error(KVQ_ERR_TYPE, "bad buffers"); return KVQ_ERR_TYPE; }
+    for (int i = 0; i < nbufs; i++) mems.push_back({bufs[i], buflens[i]});
+    return scan_entry(e, {}, std::move(mems), seqs, seqlens, nseqs, nplus, out);
+}
+
+int64_t kvq_result_nhits(const kvq_result *r) { return r ? (int64_t) r->hits.size() : 0; }
+const kvq_hit_t *kvq_result_hits(const kvq_result *r) { return r ? r->hits.data() : nullptr; }
+const char *kvq_result_hitseq_blob(const kvq_result *r) { return r ? r->blob.data() : nullptr; }
+const int64_t *kvq_result_hitseq_offsets(const kvq_result *r) { return r ? r->offsets.data() : nullptr; }
+const kvq_stats_t *kvq_result_stats(const kvq_result *r) { return r ? &r->stats : nullptr; }
+const int64_t *kvq_result_nseqhits(const kvq_result *r) { return r ? r->nseqhits.data() : nullptr; }
+const int64_t *kvq_result_nseqbasehits(const kvq_result *r) { return r ? r->nseqbasehits.data() : nullptr; }
+const int64_t *kvq_result_coverage(const kvq_result *r, int64_t *n)
+{
+    if (n) *n = r ? (int64_t) r->coverage.size() : 0;
+    return r && !r->coverage.empty() ? r->coverage.data() : nullptr;
+}
+const int64_t *kvq_result_mutcount(const kvq_result *r, int64_t *n)
+{
+    if (n) *n = r ? (int64_t) r->mutcount.size() : 0;
+    return r && !r->mutcount.empty() ? r->mutcount.data() : nullptr;
+}
+const kvq_timing_t *kvq_result_timing(const kvq_result *r) { return r ? &r->timing : nullptr; }
+void kvq_result_free(kvq_result *r) { delete r; }
+
+int kvq_stats_snapshot(kvq_engine *e, kvq_stats_t *out, int64_t *nseqhits, int64_t *nseqbasehits, int cap)
+{
+    if (!e || !out) return KVQ_ERR_TYPE;
+    std::lock_guard<std::mutex> g(e->mu);
+    int64_t rls[KVQ_MAX_READLENGTH];
+    for (int i = 0; i < KVQ_MAX_READLENGTH; i++) rls[i] = e->live.rls[i];
+    fill_stats(e, *out, rls, e->live.longest, e->live.records);
+    const int n = (int) e->live.seqhits.size();
+    out->nseqs = n;
+    for (int i = 0; i < n && i < cap; i++) {
+        if (nseqhits) nseqhits[i] = e->live.seqhits[i];
+        if (nseqbasehits) nseqbasehits[i] = e->live.seqbasehits[i];
+    }
+    return KVQ_OK;
+}
+
+int kvq_stop(kvq_engine *e)
+{
+    if (!e) return KVQ_ERR_TYPE;
+    e->stop++;                                                           // workhorse.c:1476
+    return KVQ_OK;
+}
+
+const char *kvq_last_error(kvq_engine *e, int *cls)
+{
+    if (!e) { if (cls) *cls = KVQ_ERR_TYPE; return "engine is NULL"; }
+    std::lock_guard<std::mutex> g(e->mu);
+    if (cls) *cls = e->err_cls;
+    return e->err_msg.c_str();
+}
+
+} // extern "C"
+
+// ------------------------------------------------------------------------------- HBM-resident stream
+extern "C" {
+
+int kvq_stage_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens, int nbufs, kvq_staged **out)
+{
+    if (out) *out = nullptr;
+    return guarded(e, [&] {
+        if (!out || nbufs < 0 || (nbufs > 0 && (!bufs || !buflens))) throw KvqError(KVQ_ERR_TYPE, "bad buffers");
+        RunGuard run(e);
+        if (!run.owns) throw KvqError(KVQ_ERR_RUNTIME, "findseqs() already running!");
+        CK(cudaSetDevice(e->device));
+        int64_t total = 0;
+        std::vector<std::pair<const char *, int64_t>> mems;
+        for (int i = 0; i < nbufs; i++) { mems.push_back({bufs[i], buflens[i]}); total += buflens[i]; }
+        std::unique_ptr<kvq_staged> st(new kvq_staged());
+        st->e = e;
+        st->d_data.ensure((size_t) total + BATCH_PAD + 256);
+        LiveStats live; live.reset(0);
+        StreamCutter cutter(std::vector<std::string>(), std::move(mems), &live);
+        std::vector<char> tmp((size_t) (BATCH_BYTES + BATCH_PAD));
+        HostBatch hb; hb.data = tmp.data();
+        std::vector<int64_t> cuts; cuts.push_back(0);
+        std::atomic<int> nostop{0};
+        int64_t at = 0; bool first = true;
+        while (cutter.next_batch(hb, nostop)) {
+            if (first) { st->base_fpos = hb.base_fpos; first = false; }
+            CK(cudaMemcpy(st->d_data.as<char>() + at, hb.data, (size_t) hb.nbytes, cudaMemcpyHostToDevice));
+            for (size_t k = 1; k < hb.cuts.size(); k++) cuts.push_back(at + hb.cuts[k]);
+            at += hb.nbytes;
+        }
+        CK(cudaMemset(st->d_data.as<char>() + at, 0, BATCH_PAD));
+        st->nbytes = at; st->nseg = (int) cuts.size() - 1;
+        st->parsed = live.parsed; st->total = live.total;
+        st->d_seg.ensure(cuts.size() * 8);
+        CK(cudaMemcpy(st->d_seg.p, cuts.data(), cuts.size() * 8, cudaMemcpyHostToDevice));
+        st->d_ctr.ensure(sizeof(KvqCounters));
+        st->long_cap = (size_t) (at / 1024) + 64; st->d_longs.ensure(st->long_cap * sizeof(KvqLongRec));
+        st->hit_cap = 1u << 18; st->d_hits.ensure(st->hit_cap * sizeof(KvqHitRec));
+        st->blob_cap = 32u << 20; st->d_blob.ensure(st->blob_cap);
+        *out = st.release();
+    });
+}
+
+int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, const int32_t *seqlens,
+                    int nseqs, int nplus, int want_hits, kvq_result **out)
+{
+    if (out) *out = nullptr;
+    return guarded(e, [&] {
+        if (!out || !st || st->e != e) throw KvqError(KVQ_ERR_TYPE, "bad staged stream");
+        RunGuard run(e);
+        if (!run.owns) throw KvqError(KVQ_ERR_RUNTIME, "findseqs() already running!");
+        const double t_begin = now_ms();
+        e->stop = 0;
+        CK(cudaSetDevice(e->device));
+        kvq_config_t cfg;
+        { std::lock_guard<std::mutex> g(e->mu); cfg = e->cfg; e->live.reset(nseqs); }
+        e->tpl.build(seqs, seqlens, nseqs, nplus, cfg);
+        e->tpl.par.want_hits = want_hits ? 1 : 0;
+        reset_accum(e);
+        e->live.parsed = st->parsed; e->live.total = st->total;
+        init_slots(e);                                  // borrow slot 0's stream and events
+        Slot &s0 = e->slots[0];
+        ScanTotals tot;
+        KvqBatch b{st->d_data.as<uint8_t>(), st->nbytes, st->d_seg.as<int64_t>(), st->nseg, st->base_fpos};
+        KvqOut o = make_out(e, st->d_ctr, st->d_hits, st->hit_cap, st->d_blob, st->blob_cap, st->d_longs, st->long_cap);
+        enqueue_kernels(e, b, e->tpl.par, o, s0.stream, s0.ev0, s0.ev1);
+        CK(cudaMemcpyAsync(s0.h_ctr.p, st->d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s0.stream));
+        CK(cudaStreamSynchronize(s0.stream));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1));
+        tot.kernel_ms = ms; tot.launches = 2; tot.stream_bytes = st->nbytes; tot.d2h = sizeof(KvqCounters);
+        const KvqCounters &c = *s0.h_ctr.as<KvqCounters>();
+        add_counters(e, c, tot);
+        if (want_hits)
+            collect_hits(e, b, st->d_ctr, st->d_hits, st->hit_cap, st->d_blob, st->blob_cap, st->d_longs,
+                         st->long_cap, c, s0.stream, tot);
+        if (tot.err_key != ~0ULL) throw KvqError(KVQ_ERR_FASTQ_FORMAT, format_error_message(tot.err_key));
+        *out = finish_result(e, tot, now_ms() - t_begin);
+    });
+}
+
+void kvq_staged_free(kvq_staged *st) { delete st; }
+
+} // extern "C"

@@ -1,0 +1,96 @@
+// Structures shared between the host engine (engine.cpp) and the sm_100a kernels (scan_kernel.cu).
+// All pointers are device pointers unless a field name ends in _h.
+#pragma once
+#include <stdint.h>
+
+#define KVQ_SEED_K 8                    // seed length in bases (16-bit keys)
+#define KVQ_NKEYS (1 << (2 * KVQ_SEED_K))
+#define KVQ_BITMAP_WORDS (KVQ_NKEYS / 32)
+#define KVQ_MAX_PIECES 8                // seeded path needs maxerrors+1 <= 8
+#define KVQ_MAX_SEEDED_SEQLEN 32000     // diagonal must fit the candidate encoding
+#define KVQ_HIST 1024                   // MAX_READLENGTH, workhorse.c:105
+
+// 2-bit code of a raw byte: A->0 C->1 T->2 G->3; any other byte maps to *some* code.  Equal
+// bytes always give equal codes, so exact-match seeds found in code space are complete; every
+// accepted alignment is confirmed on the raw bytes afterwards.
+#define KVQ_CODE(c) ((((unsigned) (c)) >> 1) & 3u)
+
+struct KvqParams {
+    int32_t maxerrors, minoverlap, minreadlength;
+    int32_t amin;                       // signed char value of Amin
+    int32_t seed_ok;                    // floor(minoverlap/(E+1)) >= K and E+1 <= KVQ_MAX_PIECES
+    int32_t npieces;                    // E+1
+    int32_t max_seqlen;                 // longest template (decides the whole-read T2 probes)
+    int32_t want_hits;                  // 0: count only (no hit records / blob written)
+    int32_t accumulate;                 // 0: re-run after a buffer overflow, counters already taken
+};
+
+struct KvqTemplates {
+    const uint8_t *bytes;               // concatenated raw template bytes
+    const uint32_t *byte_off;           // [nseqs+1]
+    const uint32_t *packed;             // 2-bit codes, 16 bases per word, 2 zero pad words per seq
+    const uint32_t *packed_off;         // [nseqs+1] word offsets
+    const int32_t *len;                 // [nseqs]
+    const uint8_t *seedable;            // [nseqs]
+    const int32_t *exh_list;            // indices of non-seedable seqs
+    int32_t nseqs, n_exh;
+    const uint32_t *t1_bitmap, *t1_off; const uint2 *t1_ent;   // template-piece seeds   (seq, toff)
+    const uint32_t *t2_bitmap, *t2_off; const uint2 *t2_ent;   // every template offset  (seq, toff)
+    const uint32_t *cov_off;            // [nplus+1] offset of each plus template in coverage[]
+    int32_t nplus;                      // 0 = no fused coverage
+};
+
+struct KvqBatch {
+    const uint8_t *data;                // batch bytes, 16-byte aligned, readable 64 B past nbytes
+    int64_t nbytes;
+    const int64_t *seg_off;             // [nseg+1] record-aligned cuts (reference chunk emulation)
+    int32_t nseg;
+    int64_t base_fpos;                  // stream offset of data[0]
+};
+
+struct KvqHitRec {                      // 40 bytes
+    int32_t seq_nr, seq_pos;
+    int64_t file_pos;
+    int32_t length, readlength;
+    int64_t blob_off;
+    int32_t rule;                       // 0 = (a) read tail on template head, 1 = (b) read head on
+    int32_t pad;                        //     template tail, 2 = (c)/(d) containment (emission order)
+};
+
+struct KvqLongRec {                     // work for the long-record kernel
+    int64_t start;                      // batch offset: record start (kind 0) or trimmed read start (kind 1)
+    int64_t seg_end;                    // batch offset of the end of the owning segment
+    int32_t kind;                       // 0 = parse + account + match, 1 = match only
+    int32_t rl;                         // kind 1: trimmed read length
+};
+
+struct KvqCounters {                    // zeroed before every batch launch (except the accumulators)
+    unsigned long long hit_count;       // hits wanted (may exceed capacity)
+    unsigned long long blob_used;
+    unsigned long long long_count;
+    unsigned long long err_key;         // min over format errors, ~0 = none (see scan_kernel.cu)
+    unsigned long long records, bases, exhaustive_reads, candidates;
+    unsigned long long rls[KVQ_HIST];
+    long long longest;
+    unsigned int seg_next;              // dynamic segment queue
+    unsigned int long_next;
+    unsigned int overflow_rounds;
+    unsigned int pad;
+};
+
+struct KvqOut {
+    KvqCounters *ctr;
+    KvqHitRec *hits; unsigned long long hit_cap;
+    uint8_t *blob; unsigned long long blob_cap;
+    KvqLongRec *longs; unsigned long long long_cap;
+    unsigned long long *nseqhits, *nseqbasehits;        // [nseqs]
+    unsigned long long *coverage;                       // [cov_total]
+    unsigned long long *mutcount;                       // [cov_total][6]
+};
+
+// launch wrappers (scan_kernel.cu); return cudaError_t as int
+int kvq_launch_scan(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
+                    int sm_count, void *stream);
+int kvq_launch_long(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
+                    int sm_count, void *stream);
+int kvq_scan_smem_bytes(void);
