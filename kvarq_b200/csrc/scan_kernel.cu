@@ -89,7 +89,7 @@ __device__ __forceinline__ uint32_t ge_nibble(uint32_t w, uint32_t cl, bool chi)
 // 4 bases (bytes of w) -> 8 bits of 2-bit codes, base 0 in the low bits
 __device__ __forceinline__ uint32_t pack4(uint32_t w)
 {
-    return (((w >> 1) & 0x03030303u) * 0x40100401u) >> 24;
+    return (((w >> 1) & 0x03030303u) * 0x01041040u) >> 24;
 }
 
 // 16 bases starting at base offset `b` of a packed array (needs word b/16+1 readable)
