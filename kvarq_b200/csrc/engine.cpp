@@ -564,6 +564,7 @@ void enqueue_kernels(kvq_engine *e, const KvqBatch &b, const KvqParams &p, const
 {
     CK(cudaMemsetAsync(o.ctr, 0, sizeof(KvqCounters), st));
     CK(cudaMemsetAsync(&o.ctr->err_key, 0xFF, sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(&o.ctr->longest, 0xFF, sizeof(long long), st));        // rls_longest = -1 (workhorse.c:332)
     if (ev0) CK(cudaEventRecord(ev0, st));
     cuda_check((cudaError_t) kvq_launch_scan(b, e->tpl.dev, p, o, e->sm_count, st), "scan kernel launch");
     cuda_check((cudaError_t) kvq_launch_long(b, e->tpl.dev, p, o, e->sm_count, st), "long-record kernel launch");

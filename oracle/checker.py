@@ -111,7 +111,7 @@ def findseqs(fnames, seqs, maxerrors=0, minoverlap=20, minreadlength=10, nthread
             # workhorse.c:1230-1232 -- single precision
             progress = float(C.c_float(float(C.c_float(min(res.parsed, total)).value) / total).value)
         stats = {
-            'readlengths': tuple(res.readlengths[i] for i in range(min(res.rls_longest + 1, 1024)))  # the reference reads past rls_buf beyond 1024 (workhorse.c:1214-1216),
+            'readlengths': tuple(res.readlengths[i] for i in range(min(res.rls_longest + 1, 1024))),  # the reference reads past rls_buf beyond 1024 (workhorse.c:1214-1216)
             'progress': progress,
             'nseqbasehits': tuple(res.nseqbasehits[i] for i in range(res.nseqs)),
             'nseqhits': tuple(res.nseqhits[i] for i in range(res.nseqs)),
