@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py -- Gbp scanned/sec of the read-scanning hot path on N B200s (BASELINE.json metric).
+
+Workload (BASELINE.json configs[1]): synthetic H37Rv-like 4.4 Mb genome, 100x coverage, 3 M
+single-end 150 bp Illumina-profile reads (~0.98 GB FastQ) against the MTBC-shaped template set
+(132 templates -> 264 seqs incl. reverse complements), product defaults maxerrors=2
+minoverlap=25 minreadlength=25 Q13 (Amin='.').  One "step" = one full pass of the scan over
+that FastQ.  With N GPUs every rank scans its own isolate of that shape (weak scaling, no
+data-path collective); per-template coverage / hit counters are summed with one NCCL
+all-reduce at the end.
+
+  value     : bases scanned / time, FastQ resident in HBM (kvq_scan_staged), hits + fused
+              coverage produced and read back every step
+  e2e       : same scan through kvq_findseqs_mem on HOST buffers: host -> pinned -> HBM copies
+              and the device -> host result copies inside the timed region
+  roofline  : algorithmic bytes (= FastQ bytes, each read once) / CUDA-event time of the scan
+              kernels, against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline / --impl reference : the reference's own C engine (oracle/_ref, csrc/workhorse.c
+              compiled unmodified) on the host cores, bounded sample of the same workload
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFG = dict(maxerrors=2, minoverlap=25, minreadlength=25, Amin='.')
+READS = int(os.environ.get('KVQ_BENCH_READS', 3000000))
+READLEN = 150
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+        return float(p['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        threading.Thread.__init__(self, daemon=True)
+        self.index = index
+        self.samples = []
+        self.stop_flag = False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                      '--format=csv,noheader,nounits'], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(',')])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v == 'Active'})
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': reasons, 'samples': len(self.samples)}
+
+
+def make_workload(rank):
+    from kvarq_b200 import synth
+    t0 = time.time()
+    g = synth.genome()
+    ts = synth.mtbc_templates(g, seed=1)
+    iso = synth.isolate(g, ts, seed=7 + rank)
+    fq = synth.fastq_reads(iso, READS, readlen=READLEN, seed=2 + 1000 * rank)
+    log('[rank %d] workload: %d reads, %.1f MB FastQ, %d seqs, %.1f s' %
+        (rank, READS, fq.nbytes / 1e6, 2 * ts.nplus, time.time() - t0))
+    return ts, fq
+
+
+def cpu_scan(fq_bytes, seqs, nthreads, tmpdir, tag):
+    """Times the reference CPU engine (oracle/_ref, else the port) on a FastQ sample."""
+    from oracle import checker
+    if not checker.available('oracle'):
+        checker.build()
+    impl = 'ref' if checker.available('ref') else 'oracle'
+    fn = os.path.join(tmpdir, 'kvq_cpu_%s_%d.fastq' % (tag, os.getpid()))
+    with open(fn, 'wb') as f:
+        f.write(fq_bytes)
+    try:
+        t0 = time.time()
+        r = checker.findseqs(fn, seqs, nthreads=nthreads, impl=impl, want_hits=False, **CFG)
+        dt = time.time() - t0
+    finally:
+        os.remove(fn)
+    return dt, r, impl
+
+
+def sample_bytes(fq, nreads):
+    """First nreads records of the (fixed-width per decade) synthetic FastQ."""
+    import numpy as np
+    nl = np.flatnonzero(fq[:min(fq.nbytes, nreads * 400 + 4096)] == 10)
+    return fq[:int(nl[4 * nreads - 1]) + 1]
+
+
+def run_reference_arm(args, rank, world):
+    """--impl reference: the reference's own C engine on the host cores, rank 0 only."""
+    if rank != 0:
+        return
+    from kvarq_b200 import synth
+    import numpy as np
+    cores = os.cpu_count() or 1
+    ts, fq = None, None
+    g = synth.genome()
+    ts = synth.mtbc_templates(g, seed=1)
+    # ~0.75 ms per read and core (BASELINE.md probe): size one step to ~8 s of wall clock
+    per_step = int(min(READS, max(2000, 8.0 * cores / 0.00075 * 0.6)))
+    total = per_step * (args.steps + args.warmup)
+    fq = synth.fastq_reads(synth.isolate(g, ts, seed=7), total, readlen=READLEN, seed=2)
+    tmp = '/dev/shm' if os.path.isdir('/dev/shm') else '/tmp'
+    seqs = ts.seqs()
+    nl = np.flatnonzero(fq == 10)
+    cut = lambda i: 0 if i == 0 else int(nl[4 * per_step * i - 1]) + 1
+    times, impl = [], None
+    for i in range(args.warmup + args.steps):
+        dt, r, impl = cpu_scan(fq[cut(i):cut(i + 1)].tobytes(), seqs, cores, tmp, 'ref')
+        if i >= args.warmup:
+            times.append(dt)
+        log('[reference] step %d: %d reads in %.2f s' % (i, per_step, dt))
+    t = sum(times)
+    bases = per_step * READLEN * args.steps
+    val = bases / t / 1e9
+    kind = 'reference' if impl == 'ref' else 'port'
+    sample = '%d steps x first-%d-record slices of the 3M-read workload, nthreads=%d' % (args.steps, per_step, cores)
+    print(json.dumps({
+        'impl': 'reference', 'metric': 'Gbp scanned/sec', 'value': val, 'unit': 'Gbp/s', 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * t / args.steps,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'u8', 'data': 'synthetic',
+        'config': workload_config(),
+        'cpu_baseline': {'value': val, 'unit': 'Gbp/s', 'cores': cores, 'kind': kind, 'sample': sample},
+        'e2e': {'value': val, 'unit': 'Gbp/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }), flush=True)
+
+
+def workload_config():
+    return {'workload': 'configs[1]: synthetic H37Rv-like 4.4 Mb genome, 100x, %d x %d bp SE reads vs MTBC '
+                        'templates (132 -> 264 seqs), maxerrors=2 minoverlap=25 minreadlength=25 Q13' % (READS, READLEN),
+            'reads_per_gpu': READS, 'readlen': READLEN, 'nseqs': 264,
+            'l2_policy': 'input (0.98 GB per pass) larger than L2; no flush needed'}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--e2e-steps', type=int, default=0, help='0 = min(steps, 3)')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+
+    if args.impl == 'reference':
+        run_reference_arm(args, rank, world)
+        return
+
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def allmax(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    from kvarq_b200.engine import Engine
+    ts, fq = make_workload(rank)
+    seqs = ts.seqs()
+    eng = Engine(local)
+    eng.config(nthreads=max(1, (os.cpu_count() or 8) // max(1, world)), **CFG)
+
+    # ---- value: FastQ resident in HBM ------------------------------------------------------
+    staged = eng.stage([fq])
+    for _ in range(args.warmup):
+        r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert=False)
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    kernel_ms, launches, d2h = 0.0, 0, 0
+    for _ in range(args.steps):
+        r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert=False)   # syncs the stream
+        kernel_ms += r.timing['kernel_ms']; launches += r.timing['launches']; d2h += r.timing['d2h_bytes']
+    barrier()
+    dt = allmax(time.perf_counter() - t0)
+    clocks = sampler.summary()
+    bases = r.timing['bases']
+    stream_bytes = r.timing['stream_bytes']
+    total_bases = allsum(bases * args.steps)
+    value = total_bases / dt / 1e9
+    kms = allmax(kernel_ms / args.steps)
+    log('[rank %d] resident: %.3f ms/step wall, %.3f ms/step kernels, %d hits, %d records' %
+        (rank, 1e3 * dt / args.steps, kernel_ms / args.steps, r.nhits, r['stats']['records_parsed']))
+
+    # ---- one NCCL reduce of the per-template counters (north_star; not in the timed region) --
+    if dist is not None:
+        import torch
+        cov = torch.tensor(r.coverage + list(r['stats']['nseqhits']) + list(r['stats']['nseqbasehits']),
+                           dtype=torch.int64, device='cuda')
+        dist.all_reduce(cov, op=dist.ReduceOp.SUM)
+        log('[rank %d] NCCL all-reduce of %d counters: total coverage %d' % (rank, cov.numel(), int(cov[:len(r.coverage)].sum())))
+
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region -----------------
+    e2e_steps = args.e2e_steps or min(args.steps, 3)
+    eng.findseqs_mem([fq], seqs, nplus=ts.nplus, want_hits=False)                  # warm-up (pinned pools)
+    barrier()
+    t0 = time.perf_counter()
+    h2d = d2h_e = 0
+    for _ in range(e2e_steps):
+        q = eng.findseqs_mem([fq], seqs, nplus=ts.nplus, want_hits=False)
+        h2d += q.timing['h2d_bytes']; d2h_e += q.timing['d2h_bytes']
+    barrier()
+    dt_e = allmax(time.perf_counter() - t0)
+    e2e = allsum(q.timing['bases'] * e2e_steps) / dt_e / 1e9
+    assert q.nhits == r.nhits and q['stats']['records_parsed'] == r['stats']['records_parsed']
+    log('[rank %d] e2e: %.1f ms/step' % (rank, 1e3 * dt_e / e2e_steps))
+
+    # ---- CPU baseline on rank 0 at N=1 -------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        n = int(min(READS, max(5000, 15.0 * cores / 0.00075 * 0.6)))
+        tmp = '/dev/shm' if os.path.isdir('/dev/shm') else '/tmp'
+        cdt, cr, impl = cpu_scan(sample_bytes(fq, n).tobytes(), seqs, cores, tmp, 'base')
+        cpu = {'value': n * READLEN / cdt / 1e9, 'unit': 'Gbp/s', 'cores': cores,
+               'kind': 'reference' if impl == 'ref' else 'port',
+               'sample': 'first %d of %d records, nthreads=%d, %.1f s' % (n, READS, cores, cdt)}
+        log('[cpu] %s' % cpu)
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        achieved = stream_bytes / (kms * 1e-3) / 1e9
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))['dram_bytes_per_launch']
+        except Exception:
+            pass
+        print(json.dumps({
+            'metric': 'Gbp scanned/sec', 'value': value, 'unit': 'Gbp/s', 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'u8', 'data': 'synthetic',
+            'config': workload_config(),
+            'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                         'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
+                         'kernel': 'kvq_scan_kernel', 'kernel_ms_per_step': kms,
+                         'algorithmic_bytes_per_launch': stream_bytes},
+            'cpu_baseline': cpu,
+            'e2e': {'value': e2e, 'unit': 'Gbp/s', 'h2d_bytes_per_step': h2d // e2e_steps,
+                    'd2h_bytes_per_step': d2h_e // e2e_steps, 'steps': e2e_steps},
+            'gpu_launches': launches, 'clocks': clocks,
+            'hits_per_step': r.nhits, 'records_per_step': r['stats']['records_parsed'],
+        }), flush=True)
+    staged.free()
+    eng.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -180,7 +180,9 @@ class Engine(object):
         return self._take_result(res)
 
     def findseqs_mem(self, buffers, seqlist, nplus=0, want_hits=True):
-        """Scan in-memory FastQ 'files' (bytes / numpy uint8 / anything with a buffer)."""
+        """Scan in-memory FastQ 'files' (bytes / numpy uint8 / anything with a buffer).
+        want_hits=False only skips the Python-side conversion of the hit list (result.nhits
+        still counts them); the scan itself is identical."""
         views, ptrs, lens64 = self._buffers(buffers)
         _, arr, lens, n = self._seq_args(seqlist)
         res = C.c_void_p()
@@ -207,14 +209,16 @@ class Engine(object):
             self._raise(rc)
         return Staged(self, st)
 
-    def scan_staged(self, staged, seqlist, nplus=0, want_hits=True):
+    def scan_staged(self, staged, seqlist, nplus=0, want_hits=True, convert=None):
+        """want_hits=False: the kernels only count hits (no hit records / hitseqs written);
+        convert=False: hits are produced and copied back but not turned into Python tuples."""
         _, arr, lens, n = self._seq_args(seqlist)
         res = C.c_void_p()
         rc = self._lib.kvq_scan_staged(self._h, staged._h, arr, lens, n, nplus, 1 if want_hits else 0,
                                        C.byref(res))
         if rc != 0:
             self._raise(rc)
-        return self._take_result(res, want_hits)
+        return self._take_result(res, want_hits if convert is None else convert)
 
     # -- engine.stats / engine.stop (workhorse.c:1205-1244 / 1469-1479) ----------------------
     def stats(self):
