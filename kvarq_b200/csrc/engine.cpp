@@ -447,6 +447,42 @@ struct TemplateSet {
         par.amin = (int) (signed char) cfg.Amin;
         par.seed_ok = seed_ok; par.npieces = pieces < 1 ? 1 : pieces; par.max_seqlen = max_len;
         par.want_hits = 1; par.accumulate = 1;
+        par.min_seed_rl = KVQ_SEED_K * par.npieces;
+        par.div_magic = (uint32_t) ((65536 + par.npieces - 1) / par.npieces);
+        for (int x = 0; x < 8192; x++)                  // the kernels divide by multiplication
+            if ((int) (((uint32_t) x * par.div_magic) >> 16) != x / par.npieces)
+                throw KvqError(KVQ_ERR_RUNTIME, "internal: reciprocal division is inexact");
+        for (int j = 0; j < KVQ_MAX_PIECES; j++) par.o_piece[j] = (int) ((int64_t) j * O / par.npieces);
+    }
+};
+
+} // namespace
+
+namespace {
+
+// tiles of KVQ_TILE bytes inside every segment, in stream order
+void build_tiles(const std::vector<int64_t> &cuts, std::vector<int64_t> &toff, std::vector<int32_t> &tseg)
+{
+    toff.clear(); tseg.clear();
+    for (size_t sgi = 0; sgi + 1 < cuts.size(); sgi++)
+        for (int64_t t0 = cuts[sgi]; t0 < cuts[sgi + 1]; t0 += KVQ_TILE) { toff.push_back(t0); tseg.push_back((int32_t) sgi); }
+}
+
+struct TileBufs {
+    DevBuf d_off, d_seg, d_status; int ntiles = 0;
+    void upload_async(const std::vector<int64_t> &toff, const std::vector<int32_t> &tseg, PinBuf &stage, cudaStream_t st) {
+        ntiles = (int) toff.size();
+        const size_t n = std::max<size_t>(1, toff.size());
+        d_off.ensure(n * 8); d_seg.ensure(n * 4); d_status.ensure(n * 4);
+        stage.ensure(n * 12);
+        memcpy(stage.p, toff.data(), toff.size() * 8);
+        memcpy(stage.as<char>() + n * 8, tseg.data(), tseg.size() * 4);
+        CK(cudaMemcpyAsync(d_off.p, stage.p, toff.size() * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(d_seg.p, stage.as<char>() + n * 8, tseg.size() * 4, cudaMemcpyHostToDevice, st));
+    }
+    void fill(KvqBatch &b) const {
+        b.tile_off = d_off.as<int64_t>(); b.tile_seg = d_seg.as<int32_t>();
+        b.tile_status = d_status.as<uint32_t>(); b.ntiles = ntiles;
     }
 };
 
@@ -467,7 +503,8 @@ namespace {
 struct Slot {                           // one batch in flight
     HostBatch hb; PinBuf pin;
     DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs;
-    PinBuf h_ctr, h_seg;
+    PinBuf h_ctr, h_seg, h_tiles;
+    TileBufs tiles;
     cudaStream_t stream = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
     int64_t data_bytes = 0;
@@ -499,6 +536,7 @@ struct kvq_engine {
 struct kvq_staged {
     kvq_engine *e = nullptr;
     DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs;
+    TileBufs tiles;
     size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
     int64_t nbytes = 0, base_fpos = 0, parsed = 0, total = 0; int nseg = 0;
 };
@@ -565,6 +603,7 @@ void enqueue_kernels(kvq_engine *e, const KvqBatch &b, const KvqParams &p, const
     CK(cudaMemsetAsync(o.ctr, 0, sizeof(KvqCounters), st));
     CK(cudaMemsetAsync(&o.ctr->err_key, 0xFF, sizeof(unsigned long long), st));
     CK(cudaMemsetAsync(&o.ctr->longest, 0xFF, sizeof(long long), st));        // rls_longest = -1 (workhorse.c:332)
+    CK(cudaMemsetAsync(b.tile_status, 0, (size_t) std::max(1, b.ntiles) * 4, st));
     if (ev0) CK(cudaEventRecord(ev0, st));
     cuda_check((cudaError_t) kvq_launch_scan(b, e->tpl.dev, p, o, e->sm_count, st), "scan kernel launch");
     cuda_check((cudaError_t) kvq_launch_long(b, e->tpl.dev, p, o, e->sm_count, st), "long-record kernel launch");
@@ -579,7 +618,11 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     memcpy(s.h_seg.p, hb.cuts.data(), hb.cuts.size() * 8);
     CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes + BATCH_PAD, cudaMemcpyHostToDevice, s.stream));
     CK(cudaMemcpyAsync(s.d_seg.p, s.h_seg.p, hb.cuts.size() * 8, cudaMemcpyHostToDevice, s.stream));
+    std::vector<int64_t> toff; std::vector<int32_t> tseg;
+    build_tiles(hb.cuts, toff, tseg);
+    s.tiles.upload_async(toff, tseg, s.h_tiles, s.stream);
     KvqBatch b{s.d_data.as<uint8_t>(), hb.nbytes, s.d_seg.as<int64_t>(), nseg, hb.base_fpos};
+    s.tiles.fill(b);
     KvqOut o = make_out(e, s.d_ctr, s.d_hits, s.hit_cap, s.d_blob, s.blob_cap, s.d_longs, s.long_cap);
     enqueue_kernels(e, b, e->tpl.par, o, s.stream, s.ev0, s.ev1);
     CK(cudaMemcpyAsync(s.h_ctr.p, s.d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s.stream));
@@ -629,6 +672,7 @@ void harvest_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     const KvqCounters &c = *s.h_ctr.as<KvqCounters>();
     add_counters(e, c, tot);
     KvqBatch b{s.d_data.as<uint8_t>(), s.hb.nbytes, s.d_seg.as<int64_t>(), (int) s.hb.cuts.size() - 1, s.hb.base_fpos};
+    s.tiles.fill(b);
     if (e->tpl.par.want_hits)
         collect_hits(e, b, s.d_ctr, s.d_hits, s.hit_cap, s.d_blob, s.blob_cap, s.d_longs, s.long_cap, c, s.stream, tot);
     // live per-template counters for engine.stats()
@@ -995,6 +1039,12 @@ int kvq_stage_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens
         st->parsed = live.parsed; st->total = live.total;
         st->d_seg.ensure(cuts.size() * 8);
         CK(cudaMemcpy(st->d_seg.p, cuts.data(), cuts.size() * 8, cudaMemcpyHostToDevice));
+        {
+            std::vector<int64_t> toff; std::vector<int32_t> tseg; PinBuf stage;
+            build_tiles(cuts, toff, tseg);
+            st->tiles.upload_async(toff, tseg, stage, nullptr);
+            CK(cudaDeviceSynchronize());
+        }
         st->d_ctr.ensure(sizeof(KvqCounters));
         st->long_cap = (size_t) (at / 1024) + 64; st->d_longs.ensure(st->long_cap * sizeof(KvqLongRec));
         st->hit_cap = 1u << 18; st->d_hits.ensure(st->hit_cap * sizeof(KvqHitRec));
@@ -1024,6 +1074,7 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         Slot &s0 = e->slots[0];
         ScanTotals tot;
         KvqBatch b{st->d_data.as<uint8_t>(), st->nbytes, st->d_seg.as<int64_t>(), st->nseg, st->base_fpos};
+        st->tiles.fill(b);
         KvqOut o = make_out(e, st->d_ctr, st->d_hits, st->hit_cap, st->d_blob, st->blob_cap, st->d_longs, st->long_cap);
         enqueue_kernels(e, b, e->tpl.par, o, s0.stream, s0.ev0, s0.ev1);
         CK(cudaMemcpyAsync(s0.h_ctr.p, st->d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s0.stream));

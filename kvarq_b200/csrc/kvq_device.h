@@ -9,6 +9,7 @@
 #define KVQ_MAX_PIECES 8                // seeded path needs maxerrors+1 <= 8
 #define KVQ_MAX_SEEDED_SEQLEN 32000     // diagonal must fit the candidate encoding
 #define KVQ_HIST 1024                   // MAX_READLENGTH, workhorse.c:105
+#define KVQ_TILE 32768                  // bytes of a segment owned by one tile (host builds the tile table)
 
 // 2-bit code of a raw byte: A->0 C->1 T->2 G->3; any other byte maps to *some* code.  Equal
 // bytes always give equal codes, so exact-match seeds found in code space are complete; every
@@ -22,6 +23,9 @@ struct KvqParams {
     int32_t npieces;                    // E+1
     int32_t max_seqlen;                 // longest template (decides the whole-read T2 probes)
     int32_t want_hits;                  // 0: count only (no hit records / blob written)
+    int32_t min_seed_rl;                // KVQ_SEED_K * npieces: shortest read the seed scheme covers
+    uint32_t div_magic;                 // floor(x / npieces) == (x * div_magic) >> 16 for x < 8192
+    int32_t o_piece[KVQ_MAX_PIECES];    // floor(j * minoverlap / npieces)
     int32_t accumulate;                 // 0: re-run after a buffer overflow, counters already taken
 };
 
@@ -46,6 +50,10 @@ struct KvqBatch {
     const int64_t *seg_off;             // [nseg+1] record-aligned cuts (reference chunk emulation)
     int32_t nseg;
     int64_t base_fpos;                  // stream offset of data[0]
+    const int64_t *tile_off;            // [ntiles] start of every tile (KVQ_TILE bytes of one segment)
+    const int32_t *tile_seg;            // [ntiles] owning segment
+    uint32_t *tile_status;              // [ntiles] look-back words, zeroed before the launch
+    int32_t ntiles;
 };
 
 struct KvqHitRec {                      // 40 bytes
@@ -72,7 +80,7 @@ struct KvqCounters {                    // zeroed before every batch launch (exc
     unsigned long long records, bases, exhaustive_reads, candidates;
     unsigned long long rls[KVQ_HIST];
     long long longest;
-    unsigned int seg_next;              // dynamic segment queue
+    unsigned int tile_next;             // dynamic tile queue (tiles are claimed in stream order)
     unsigned int long_next;
     unsigned int overflow_rounds;
     unsigned int pad;

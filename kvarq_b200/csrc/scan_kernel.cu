@@ -1,17 +1,19 @@
-// sm_100a kernels of the KvarQ read-scanning path.
+// sm_100a kernels of the KvarQ read-scanning path (reference: csrc/workhorse.c:976-1197).
 //
-// One persistent CTA takes record-aligned segments of the FastQ stream from a queue and walks
-// each of them tile by tile (32 KiB + spill margin, staged in shared memory).  Per tile:
-//   P1  newline bitmap (SWAR compare on 128-bit loads) + block prefix scan   [workhorse.c:1018-1030]
-//   P2  record table: record k of a segment = its lines 4k..4k+3             [workhorse.c:1010-1052]
-//   P3  '@' / '+' sanity checks, Phred trim (first longest run >= Amin),
-//       read-length histogram, length filter                                [workhorse.c:1037-1103]
-//   P4  2-bit packing of the trimmed reads
-//   P5  seed probes: every read offset against the template-piece table (T1), a few fixed read
-//       offsets against the all-offsets table (T2); bitmaps live in shared memory
-//   P6  bucket expansion -> candidate diagonals
-//   P7  XOR/popc Hamming verify on packed words, byte-exact confirm, hit emission through
-//       atomics, fused coverage                                             [workhorse.c:1107-1175,408-443]
+// Persistent kernel, one CTA per SM.  A CTA holds G independent warp groups; every group claims
+// 32 KiB tiles of the FastQ stream in stream order from a global queue and runs the whole path
+// on its tile in shared memory, synchronising only inside the group (named barriers):
+//   P1  stage tile (+ spill margin) with 128-bit loads, SWAR newline bitmap, group prefix scan;
+//       the tile's newline count is published and the line phase of the tile (newlines of its
+//       segment before it, mod 4) resolved by decoupled look-back      [workhorse.c:1018-1030]
+//   P2  one thread per record: select its 4 newlines from the bitmap, '@' / '+' sanity checks,
+//       Phred trim (first longest run >= Amin), histogram, length filter [workhorse.c:1037-1103]
+//   P3  2-bit packing of the trimmed reads (dense work lists, 16 bases per step)
+//   P4  seed probes against bitmaps in shared memory: every read offset vs the template-piece
+//       table T1, a few fixed read offsets vs the all-offsets table T2
+//   P5  bucket expansion (tables in L2) -> candidate diagonals
+//   P6  XOR/popc Hamming verify on packed words, byte-exact confirm, canonical-seed dedupe,
+//       hit emission through atomics, fused coverage            [workhorse.c:1107-1175,408-443]
 // Reads or templates the seed scheme cannot cover take the exhaustive matcher (same acceptance
 // rule, every diagonal).  Acceptance rule: SURVEY.md Appendix B / workhorse.c:1112-1174.
 #include <cuda_runtime.h>
@@ -20,70 +22,106 @@
 
 namespace {
 
-constexpr int THREADS = 512;
-constexpr int NWARPS = THREADS / 32;
-constexpr int TILE = 32768;                 // bytes of a segment owned by one tile
-constexpr int MARGIN = 8192;                // spill: records starting in the tile may end here
-constexpr int LOADMAX = TILE + MARGIN + 16; // + alignment slack of the first 16-byte chunk
-constexpr int NLW = LOADMAX / 32 + 2;       // newline bitmap words
-constexpr int CAP = 256;                    // records per round
+constexpr int G = 2;                        // warp groups per CTA
+constexpr int GT = 256;                     // threads per group
+constexpr int THREADS = G * GT;
+constexpr int GW = GT / 32;                 // warps per group
+constexpr int TILE = KVQ_TILE;
+constexpr int MARGIN = 3072;                // spill: records starting in the tile may end here
+constexpr int LOADMAX = TILE + MARGIN + 32; // + alignment slack of the first 32-byte word
+constexpr int NLW = LOADMAX / 32 + 1;       // newline bitmap words (32 bytes each)
+constexpr int WPT = (NLW + GT - 1) / GT;    // bitmap words per thread in the prefix scan
+constexpr int CAP = GT;                     // records per round (one thread per record)
 constexpr int MAXRL_FAST = 512;             // longer trimmed reads go to the long-record kernel
-constexpr int SLOTW = MAXRL_FAST / 16 + 2;  // packed words per read slot
-constexpr int SEEDQ = 4096;
-constexpr int CANDQ = 4096;
+constexpr int PACKW = 4096;                 // packed words per round (16 bases each)
+constexpr int QCAP = 4096;                  // T1 probe items per round (16 read offsets each)
+constexpr int SEEDQ = 2048;
+constexpr int CANDQ = 1536;
 constexpr int MAXP2 = 3 * KVQ_MAX_PIECES;
 
-struct Rec { uint16_t start; uint16_t nl[4]; };
-struct Rd { uint16_t pos; uint16_t rl; };
+struct Rd { uint16_t pos, rl, poff, flags; };   // flags bit0: seedable
 
-struct Smem {
-    uint4 tile[LOADMAX / 16 + 4];      // + slack for word-aligned over-reads
-    uint32_t nlmask[NLW];
+struct GroupSmem {
+    uint4 tile[LOADMAX / 16 + 4];           // + slack for word-aligned over-reads
+    uint32_t nlmask[NLW + 1];
     uint32_t nlpref[NLW + 1];
-    Rec rec[CAP];
     Rd rd[CAP];
-    uint32_t packed[CAP * SLOTW];
-    uint32_t bm1[KVQ_BITMAP_WORDS];
-    uint32_t bm2[KVQ_BITMAP_WORDS];
+    uint32_t packed[PACKW + 2];
+    uint8_t pitem[PACKW];                   // packed word -> read
+    uint16_t qitem[QCAP];                   // probe item -> read << 6 | block
     uint32_t seedq[SEEDQ];
     unsigned long long candq[CANDQ];
-    uint32_t hist[KVQ_HIST];
     uint16_t exh_reads[CAP];
     uint16_t seed_reads[CAP];
-    uint32_t warp_tot[NWARPS];
-    // per-round / per-tile scalars
-    int nrd, nseed, ncand, n_exh_reads, n_seed_reads, overflow;
-    int seg_cur;
-    // per-CTA accumulators
-    unsigned long long records, bases, exh_count, cand_count;
-    int longest;
+    uint32_t warp_tot[GW];
+    int nrd, nseed, ncand, n_exh_reads, n_seed_reads;
+    int tile_cur, phase_in;
 };
+
+struct Smem {
+    uint32_t bm1[KVQ_BITMAP_WORDS];
+    uint32_t bm2[KVQ_BITMAP_WORDS];
+    uint32_t hist[KVQ_HIST];
+    int longest;
+    GroupSmem g[G];
+};
+static_assert(sizeof(Smem) <= 232448, "shared memory budget (227 KB) exceeded");
+
+struct ThreadStats { unsigned long long records, bases, exh, cands; };
+
+__device__ __forceinline__ void group_sync(int gid)
+{
+    asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "r"(GT) : "memory");
+}
 
 __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t s)
 {
-    return __funnelshift_r(lo, hi, s);      // (hi:lo >> (s & 31)) low word
+    return __funnelshift_r(lo, hi, s);
 }
 
-// 4-bit mask of the bytes of w equal to '\n'
-__device__ __forceinline__ uint32_t nl_nibble(uint32_t w)
+// bit7 of every byte of w that equals '\n' (other bits 0)
+__device__ __forceinline__ uint32_t nl_bits(uint32_t w)
 {
     uint32_t t = w ^ 0x0A0A0A0Au;
     uint32_t z = ((t & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | t;     // bit7 set <=> byte != 0
-    uint32_t m = (~z & 0x80808080u) >> 7;
-    return (m * 0x10204080u) >> 28;
+    return ~z & 0x80808080u;
+}
+// bits 7,15,23,31 -> 4-bit value in the top nibble (no carries: all partial products distinct)
+__device__ __forceinline__ uint32_t top_nibble(uint32_t e) { return e * 0x00204081u; }
+
+// 32-bit newline mask of 32 bytes
+__device__ __forceinline__ uint32_t nl_mask32(uint4 a, uint4 b)
+{
+    uint32_t m = top_nibble(nl_bits(a.x)) >> 28;
+    m |= (top_nibble(nl_bits(a.y)) >> 24) & 0x000000F0u;
+    m |= (top_nibble(nl_bits(a.z)) >> 20) & 0x00000F00u;
+    m |= (top_nibble(nl_bits(a.w)) >> 16) & 0x0000F000u;
+    m |= (top_nibble(nl_bits(b.x)) >> 12) & 0x000F0000u;
+    m |= (top_nibble(nl_bits(b.y)) >> 8) & 0x00F00000u;
+    m |= (top_nibble(nl_bits(b.z)) >> 4) & 0x0F000000u;
+    m |= top_nibble(nl_bits(b.w)) & 0xF0000000u;
+    return m;
 }
 
-// 4-bit mask of bytes b of w with (signed char) b >= amin.  cl = (amin & 0x7f) * 0x01010101,
-// chi = amin has bit 7 set (negative).
-__device__ __forceinline__ uint32_t ge_nibble(uint32_t w, uint32_t cl, bool chi)
+// bit7 of every byte b of w with (signed char) b >= amin.  cl = (amin & 0x7f) * 0x01010101,
+// chi = amin is negative.  Compares (b ^ 0x80) >= (amin ^ 0x80) as unsigned bytes.
+__device__ __forceinline__ uint32_t ge_bits(uint32_t w, uint32_t cl, bool chi)
 {
-    // compare (b ^ 0x80) >= (amin ^ 0x80) as unsigned bytes
-    uint32_t t = (w | 0x80808080u) - cl;                    // bit7: low 7 bits of b >= low 7 bits of amin
-    uint32_t uhi = ~w;                                      // bit7 of (b ^ 0x80)
-    // amin^0x80 has bit7 = !chi
-    uint32_t ge = chi ? (uhi | t) : (uhi & t);
-    uint32_t m = (ge & 0x80808080u) >> 7;
-    return (m * 0x10204080u) >> 28;
+    uint32_t t = (w | 0x80808080u) - cl;            // bit7: low 7 bits of b >= low 7 bits of amin
+    uint32_t uhi = ~w;                              // bit7 of (b ^ 0x80)
+    return (chi ? (uhi | t) : (uhi & t)) & 0x80808080u;
+}
+__device__ __forceinline__ uint32_t ge_mask32(uint4 a, uint4 b, uint32_t cl, bool chi)
+{
+    uint32_t m = top_nibble(ge_bits(a.x, cl, chi)) >> 28;
+    m |= (top_nibble(ge_bits(a.y, cl, chi)) >> 24) & 0x000000F0u;
+    m |= (top_nibble(ge_bits(a.z, cl, chi)) >> 20) & 0x00000F00u;
+    m |= (top_nibble(ge_bits(a.w, cl, chi)) >> 16) & 0x0000F000u;
+    m |= (top_nibble(ge_bits(b.x, cl, chi)) >> 12) & 0x000F0000u;
+    m |= (top_nibble(ge_bits(b.y, cl, chi)) >> 8) & 0x00F00000u;
+    m |= (top_nibble(ge_bits(b.z, cl, chi)) >> 4) & 0x0F000000u;
+    m |= top_nibble(ge_bits(b.w, cl, chi)) & 0xF0000000u;
+    return m;
 }
 
 // 4 bases (bytes of w) -> 8 bits of 2-bit codes, base 0 in the low bits
@@ -98,9 +136,6 @@ __device__ __forceinline__ uint32_t extract16(const uint32_t *pk, int b)
     int w = b >> 4;
     return funnel_r(pk[w], pk[w + 1], (uint32_t) ((b & 15) << 1));
 }
-
-__device__ __forceinline__ uint32_t ldg32(const uint32_t *p) { return __ldg(p); }
-
 __device__ __forceinline__ uint32_t extract16_g(const uint32_t *pk, int b)
 {
     int w = b >> 4;
@@ -109,7 +144,7 @@ __device__ __forceinline__ uint32_t extract16_g(const uint32_t *pk, int b)
 
 // Is diagonal d (= seq index aligned with read[0]) one the reference evaluates?  Returns the
 // number of hits an accepted alignment yields there (0, 1 or 2 -- the (b)+(d) duplicate,
-// workhorse.c:1130-1141 + 1163-1173) and the overlap geometry.
+// workhorse.c:1130-1141 + 1163-1173), the overlap geometry and the rule (emission phase).
 __device__ __forceinline__ int diag_rule(int d, int rl, int sl, int O, int &ro, int &to, int &L, int &rule)
 {
     rule = 2;
@@ -118,17 +153,12 @@ __device__ __forceinline__ int diag_rule(int d, int rl, int sl, int O, int &ro, 
     int lr = rl - ro, ls = sl - to;
     L = lr < ls ? lr : ls;
     if (L <= 0) return 0;
-    if (d <= 0 && d + rl >= sl) {
-        // template inside read: rule (c) needs rl > sl, else d == 0 && rl == sl is rule (d)
+    if (d <= 0 && d + rl >= sl) return 1;           // template inside read: rule (c) / (d) at d == 0
+    if (d >= 0 && d + rl <= sl) {                   // read inside template: rule (d)
+        if (d > 0 && d + rl == sl && rl > O && sl > O) return 2;    // flush right: rule (b) fires too
         return 1;
     }
-    if (d >= 0 && d + rl <= sl) {
-        // read inside template, rule (d); flush-right also satisfies rule (b)
-        if (d > 0 && d + rl == sl && rl > O && sl > O) return 2;
-        return 1;
-    }
-    // partial overlaps, rules (a) / (b)
-    rule = d < 0 ? 0 : 1;
+    rule = d < 0 ? 0 : 1;                           // partial overlaps: rules (a) / (b)
     if (rl > O && sl > O && L >= O) return 1;
     return 0;
 }
@@ -138,20 +168,19 @@ __device__ __forceinline__ int diag_rule(int d, int rl, int sl, int O, int &ro, 
 namespace {
 
 struct TileCtx {
-    int64_t a0;          // batch offset of smem byte 0 (16-byte aligned)
+    int64_t a0;          // batch offset of smem byte 0 (32-byte aligned)
     int shift;           // smem coordinate of the first byte of the tile
     int tile_end;        // smem coordinate one past the bytes owned by the tile
-    int reg_end;         // smem coordinate one past the loaded region
+    int reg_end;         // smem coordinate one past the staged region
     int first;           // first tile of its segment
     int at_seg_end;      // the region reaches the end of the segment
-    int phase_in;        // newlines of the segment before the tile, mod 4
     int64_t seg_end;     // batch offset of the segment end
 };
 
-// block-wide exclusive scan of one value per thread; returns the exclusive prefix, *total = sum
-__device__ __forceinline__ uint32_t block_exscan(uint32_t v, uint32_t *warp_tot, uint32_t *total)
+// group-wide exclusive scan of one value per thread; returns the exclusive prefix, *total = sum
+__device__ __forceinline__ uint32_t group_exscan(uint32_t v, uint32_t *warp_tot, uint32_t *total, int gid, int gt)
 {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int lane = gt & 31, wid = gt >> 5;
     uint32_t inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -159,99 +188,88 @@ __device__ __forceinline__ uint32_t block_exscan(uint32_t v, uint32_t *warp_tot,
         if (lane >= o) inc += n;
     }
     if (lane == 31) warp_tot[wid] = inc;
-    __syncthreads();
+    group_sync(gid);
     uint32_t base = 0, tot = 0;
 #pragma unroll
-    for (int w = 0; w < NWARPS; w++) {
+    for (int w = 0; w < GW; w++) {
         uint32_t t = warp_tot[w];
         if (w < wid) base += t;
         tot += t;
     }
-    __syncthreads();
+    group_sync(gid);
     *total = tot;
     return base + inc - v;
 }
 
-// P1: stage the region in shared memory and build the newline bitmap + prefix counts.
-// Returns (to every thread) the number of newlines in the whole region.
-__device__ uint32_t load_and_index(Smem &s, const KvqBatch &b, const TileCtx &t)
+// P1: stage the region in shared memory, build the newline bitmap + prefix counts.
+// Returns (to every thread of the group) the number of newlines in the whole region.
+__device__ uint32_t load_and_index(GroupSmem &s, const KvqBatch &b, const TileCtx &t, int gid, int gt)
 {
-    const int nchunks = (t.reg_end + 15) >> 4;
+    const int nwords = (t.reg_end + 31) >> 5;
     const uint4 *src = reinterpret_cast<const uint4 *>(b.data + t.a0);
-    uint16_t *nl16 = reinterpret_cast<uint16_t *>(s.nlmask);
-    for (int c = threadIdx.x; c < NLW * 2; c += THREADS) {
+    for (int w = gt; w < NLW + 1; w += GT) {
         uint32_t m = 0;
-        if (c < nchunks) {
-            uint4 v = __ldg(src + c);
-            s.tile[c] = v;
-            m = nl_nibble(v.x) | (nl_nibble(v.y) << 4) | (nl_nibble(v.z) << 8) | (nl_nibble(v.w) << 12);
-            int lo = t.shift - (c << 4), hi = t.reg_end - (c << 4);
-            if (lo > 0) m &= lo >= 16 ? 0u : (0xFFFFu << lo);
-            if (hi < 16) m &= hi <= 0 ? 0u : ((1u << hi) - 1u);
+        if (w < nwords) {
+            uint4 va = __ldg(src + 2 * w), vb = __ldg(src + 2 * w + 1);
+            s.tile[2 * w] = va; s.tile[2 * w + 1] = vb;
+            m = nl_mask32(va, vb);
+            const int lo = t.shift - (w << 5), hi = t.reg_end - (w << 5);
+            if (lo > 0) m &= lo >= 32 ? 0u : (0xFFFFFFFFu << lo);
+            if (hi < 32) m &= hi <= 0 ? 0u : ((1u << hi) - 1u);
         }
-        nl16[c] = (uint16_t) m;
+        s.nlmask[w] = m;
     }
-    __syncthreads();
-    // three bitmap words per thread
-    const int w0 = threadIdx.x * 3;
-    uint32_t c0 = 0, c1 = 0, c2 = 0;
-    if (w0 < NLW) c0 = __popc(s.nlmask[w0]);
-    if (w0 + 1 < NLW) c1 = __popc(s.nlmask[w0 + 1]);
-    if (w0 + 2 < NLW) c2 = __popc(s.nlmask[w0 + 2]);
+    group_sync(gid);
+    const int w0 = gt * WPT;
+    uint32_t c[WPT]; uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < WPT; i++) {
+        c[i] = (w0 + i < NLW) ? __popc(s.nlmask[w0 + i]) : 0;
+        sum += c[i];
+    }
     uint32_t total;
-    uint32_t ex = block_exscan(c0 + c1 + c2, s.warp_tot, &total);
-    if (w0 < NLW) s.nlpref[w0] = ex;
-    if (w0 + 1 < NLW) s.nlpref[w0 + 1] = ex + c0;
-    if (w0 + 2 < NLW) s.nlpref[w0 + 2] = ex + c0 + c1;
-    if (threadIdx.x == 0) s.nlpref[NLW] = total;
-    __syncthreads();
+    uint32_t ex = group_exscan(sum, s.warp_tot, &total, gid, gt);
+#pragma unroll
+    for (int i = 0; i < WPT; i++) {
+        if (w0 + i < NLW) s.nlpref[w0 + i] = ex;
+        ex += c[i];
+    }
+    if (gt == 0) s.nlpref[NLW] = total;
+    group_sync(gid);
     return total;
 }
 
 // newlines at smem coordinates < pos
-__device__ __forceinline__ uint32_t nl_before(const Smem &s, int pos)
+__device__ __forceinline__ uint32_t nl_before(const GroupSmem &s, int pos)
 {
     int w = pos >> 5;
     uint32_t m = s.nlmask[w] & ((1u << (pos & 31)) - 1u);
     return s.nlpref[w] + __popc(m);
 }
 
-// P2: fill the record table for records [k0, k0+CAP) of the tile.  `off` shifts newline ranks
-// to record-relative numbering: newline v = rank - off is line (v & 3) of record (v >> 2); the
-// byte after newline v = 4k-1 is the start of record k.
-__device__ void fill_records(Smem &s, const TileCtx &t, int off, int k0)
+// Decoupled look-back over the tiles of one segment: every tile publishes its newline count
+// (mod 4); a tile's phase is the sum over its predecessors.  Status word: bit3 = inclusive
+// prefix, bit2 = tile aggregate, bits 1:0 = value.  Tiles are claimed in stream order, so a
+// predecessor is always resident or finished.
+__device__ int resolve_phase(const KvqBatch &b, int tile, int first, int n_tile)
 {
-    if (threadIdx.x == 0 && t.first && k0 == 0) s.rec[0].start = (uint16_t) t.shift;
-    const int vlo = 4 * k0 - 1, vhi = 4 * (k0 + CAP) - 1;       // inclusive range of interest
-    const int w0 = threadIdx.x * 3;
-#pragma unroll
-    for (int i = 0; i < 3; i++) {
-        int w = w0 + i;
-        if (w >= NLW) break;
-        uint32_t m = s.nlmask[w];
-        if (!m) continue;
-        int v = (int) s.nlpref[w] - off;
-        if (v > vhi || v + 32 < vlo) continue;
-        while (m) {
-            int bit = __ffs(m) - 1;
-            m &= m - 1;
-            int pos = (w << 5) + bit;
-            if (v >= vlo && v <= vhi) {
-                if (v >= 0 && (v >> 2) < k0 + CAP && (v >> 2) >= k0)
-                    s.rec[(v >> 2) - k0].nl[v & 3] = (uint16_t) pos;
-                if (((v + 1) & 3) == 0) {
-                    int k = (v + 1) >> 2;
-                    if (k >= k0 && k < k0 + CAP) s.rec[k - k0].start = (uint16_t) (pos + 1);
-                }
-            }
-            v++;
-        }
+    volatile uint32_t *st = b.tile_status;
+    if (first) {
+        st[tile] = 8u | (uint32_t) (n_tile & 3);
+        return 0;
     }
+    st[tile] = 4u | (uint32_t) (n_tile & 3);
+    int acc = 0;
+    for (int j = tile - 1;; j--) {
+        uint32_t v;
+        while ((v = st[j]) == 0) __nanosleep(20);
+        acc += (int) (v & 3);
+        if (v & 8u) break;
+    }
+    acc &= 3;
+    st[tile] = 8u | (uint32_t) ((acc + n_tile) & 3);
+    return acc;
 }
-
-} // namespace
-
-namespace {
 
 // format-error key: smaller = earlier in the stream.  [63:22] stream offset of the record start,
 // [21] 0 = bad '@' / 1 = bad '+', [20:0] payload (the offending byte, or plus_pos - record_start)
@@ -273,18 +291,13 @@ __device__ __forceinline__ void push_long(const KvqOut &o, int64_t start, int64_
 
 // Phred trim of the quality line [qs, qe] (qe = its '\n'), workhorse.c:1055-1068: the first
 // longest run of bytes >= Amin that is closed by a byte < Amin at or before qe.
-__device__ __forceinline__ void phred_trim(const Smem &s, int qs, int qe, uint32_t cl, bool chi,
+__device__ __forceinline__ void phred_trim(const GroupSmem &s, int qs, int qe, uint32_t cl, bool chi,
                                            int &rl, int &best)
 {
     int runstart = qs;
     rl = 0; best = qs;
     for (int gb = qs & ~31; gb <= qe; gb += 32) {
-        uint4 a = s.tile[gb >> 4], b = s.tile[(gb >> 4) + 1];
-        uint32_t good = ge_nibble(a.x, cl, chi) | (ge_nibble(a.y, cl, chi) << 4)
-                      | (ge_nibble(a.z, cl, chi) << 8) | (ge_nibble(a.w, cl, chi) << 12)
-                      | (ge_nibble(b.x, cl, chi) << 16) | (ge_nibble(b.y, cl, chi) << 20)
-                      | (ge_nibble(b.z, cl, chi) << 24) | (ge_nibble(b.w, cl, chi) << 28);
-        uint32_t bad = ~good;
+        uint32_t bad = ~ge_mask32(s.tile[gb >> 4], s.tile[(gb >> 4) + 1], cl, chi);
         if (gb < qs) bad &= 0xFFFFFFFFu << (qs - gb);
         if (qe - gb < 31) bad &= (2u << (qe - gb)) - 1u;
         while (bad) {
@@ -297,63 +310,62 @@ __device__ __forceinline__ void phred_trim(const Smem &s, int qs, int qe, uint32
     }
 }
 
-// P3: one thread per record of the round.
-__device__ void process_records(Smem &s, const KvqBatch &b, const TileCtx &t, const KvqParams &p,
-                                const KvqOut &o, int k0, int nrec, int kcomplete)
+// P2: one thread per record of the round.  Newline ranks are record-relative: newline
+// v = rank - off is line (v & 3) of record (v >> 2); the byte after newline 4k-1 starts record k.
+__device__ void process_records(GroupSmem &s, Smem &sh, const KvqBatch &b, const TileCtx &t,
+                                const KvqParams &p, const KvqOut &o, int off, int k0, int nrec,
+                                int kcomplete, int gt, ThreadStats &ts)
 {
+    if (gt >= nrec) return;
     const uint8_t *tb = reinterpret_cast<const uint8_t *>(s.tile);
+    const int k = k0 + gt;
+    // locate the newline that precedes the record (or the record's first newline for k == 0
+    // of a segment's first tile) by binary search over the per-word prefix counts
+    const bool has_prev = !(t.first && k == 0);
+    const int r0 = 4 * k + off - (has_prev ? 1 : 0);        // rank of the first newline we need
+    int lo = 0, hi = NLW;                                   // largest w with nlpref[w] <= r0
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if ((int) s.nlpref[mid] <= r0) lo = mid; else hi = mid;
+    }
+    int w = lo;
+    uint32_t m = s.nlmask[w];
+    for (int skip = r0 - (int) s.nlpref[w]; skip > 0; skip--) m &= m - 1;
+    // walk to the next newline of the bitmap
+    auto next_nl = [&]() -> int {
+        while (m == 0) m = s.nlmask[++w];
+        const int pos = (w << 5) + __ffs(m) - 1;
+        m &= m - 1;
+        return pos;
+    };
+    int S = t.shift;
+    if (has_prev) S = next_nl() + 1;
+    if (k > kcomplete) {
+        // the record runs past the staged region: a partial record at the end of the segment
+        // is dropped (workhorse.c:1033), anything else is a long record
+        if (!t.at_seg_end) push_long(o, t.a0 + S, t.seg_end, 0, 0);
+        return;
+    }
+    const int n0 = next_nl(), n1 = next_nl(), n2 = next_nl(), n3 = next_nl();
+    if (tb[S] != '@')
+        report_format_error(o, b.base_fpos + t.a0 + S, 0, tb[S]);
+    else if (tb[n1 + 1] != '+')
+        report_format_error(o, b.base_fpos + t.a0 + S, 1, (uint32_t) (n1 + 1 - S));
+    ts.records++;
+    ts.bases += (unsigned long long) (n1 - n0 - 1);
     const uint32_t cl = (uint32_t) (p.amin & 0x7F) * 0x01010101u;
     const bool chi = (p.amin & 0x80) != 0;
-    for (int i = threadIdx.x; i < nrec; i += THREADS) {
-        const int k = k0 + i;
-        const Rec r = s.rec[i];
-        if (k > kcomplete) {
-            // the record runs past the staged region: partial at the end of the segment is
-            // dropped (workhorse.c:1033), anything else is a long record
-            if (!t.at_seg_end) push_long(o, t.a0 + r.start, t.seg_end, 0, 0);
-            continue;
-        }
-        const int S = r.start, n0 = r.nl[0], n1 = r.nl[1], n2 = r.nl[2], n3 = r.nl[3];
-        if (tb[S] != '@')
-            report_format_error(o, b.base_fpos + t.a0 + S, 0, tb[S]);
-        else if (tb[n1 + 1] != '+')
-            report_format_error(o, b.base_fpos + t.a0 + S, 1, (uint32_t) (n1 + 1 - S));
-        atomicAdd(&s.records, 1ULL);
-        atomicAdd(&s.bases, (unsigned long long) (n1 - n0 - 1));
-        int rl, best;
-        phred_trim(s, n2 + 1, n3, cl, chi, rl, best);
-        if (rl < KVQ_HIST) atomicAdd(&s.hist[rl], 1u);                  // add_rl, workhorse.c:394-402
-        atomicMax(&s.longest, rl);
-        if (rl < p.minreadlength || rl == 0) continue;                  // workhorse.c:1100
-        const int rd0 = n0 + 1 + (best - (n2 + 1));                     // workhorse.c:1070
-        if (rl > MAXRL_FAST) { push_long(o, t.a0 + rd0, t.seg_end, 1, rl); continue; }
-        int idx = atomicAdd(&s.nrd, 1);
-        Rd q; q.pos = (uint16_t) rd0; q.rl = (uint16_t) rl;
-        s.rd[idx] = q;
-    }
-}
-
-// P4: 2-bit pack the trimmed reads of the round, 16 bases per thread-step
-__device__ void pack_reads(Smem &s)
-{
-    const uint32_t *tw = reinterpret_cast<const uint32_t *>(s.tile);
-    const int nrd = s.nrd;
-    for (int item = threadIdx.x; item < nrd * SLOTW; item += THREADS) {
-        const int r = item / SLOTW, j = item - r * SLOTW;
-        const int rl = s.rd[r].rl;
-        const int nvalid = rl - 16 * j;
-        if (nvalid <= -16) continue;                 // words beyond ceil(rl/16) are never read
-        uint32_t codes = 0;
-        if (nvalid > 0) {
-            const int pos = s.rd[r].pos + 16 * j;
-            const int a = pos >> 2; const uint32_t sh = (uint32_t) (pos & 3) << 3;
-            uint32_t w0 = tw[a], w1 = tw[a + 1], w2 = tw[a + 2], w3 = tw[a + 3], w4 = tw[a + 4];
-            codes = pack4(funnel_r(w0, w1, sh)) | (pack4(funnel_r(w1, w2, sh)) << 8)
-                  | (pack4(funnel_r(w2, w3, sh)) << 16) | (pack4(funnel_r(w3, w4, sh)) << 24);
-            if (nvalid < 16) codes &= (1u << (2 * nvalid)) - 1u;
-        }
-        s.packed[r * SLOTW + j] = codes;
-    }
+    int rl, best;
+    phred_trim(s, n2 + 1, n3, cl, chi, rl, best);
+    if (rl < KVQ_HIST) atomicAdd(&sh.hist[rl], 1u);                 // add_rl, workhorse.c:394-402
+    atomicMax(&sh.longest, rl);
+    if (rl < p.minreadlength || rl == 0) return;                    // workhorse.c:1100
+    const int rd0 = n0 + 1 + (best - (n2 + 1));                     // workhorse.c:1070
+    if (rl > MAXRL_FAST) { push_long(o, t.a0 + rd0, t.seg_end, 1, rl); return; }
+    const int idx = atomicAdd(&s.nrd, 1);
+    Rd q; q.pos = (uint16_t) rd0; q.rl = (uint16_t) rl; q.poff = 0;
+    q.flags = (p.seed_ok && rl >= p.min_seed_rl) ? 1 : 0;
+    s.rd[idx] = q;
 }
 
 } // namespace
@@ -426,27 +438,74 @@ __device__ __forceinline__ int byte_mismatches(const uint8_t *a, const uint8_t *
 // ---------------------------------------------------------------- seed positions -------------
 // Fixed read offsets probed against the all-offsets table T2: E+1 pieces of the whole read
 // (rule d), of its first minoverlap bases (rule b) and of its last minoverlap bases (rule a).
-__device__ __forceinline__ int build_p2(int rl, int O, int np, int max_sl, int *out)
+__device__ __forceinline__ int build_p2(const KvqParams &p, int rl, int *out)
 {
     int n = 0;
+    const int np = p.npieces, O = p.minoverlap;
 #define KVQ_ADD_P2(v) do { int _v = (v); bool dup = false; \
         for (int _i = 0; _i < n; _i++) dup |= (out[_i] == _v); if (!dup) out[n++] = _v; } while (0)
-    if (max_sl >= rl)
-        for (int j = 0; j < np; j++) KVQ_ADD_P2(j * rl / np);
+    if (p.max_seqlen >= rl)
+        for (int j = 0; j < np; j++) KVQ_ADD_P2((int) (((uint32_t) (j * rl) * p.div_magic) >> 16));
     if (rl > O) {
-        for (int j = 0; j < np; j++) KVQ_ADD_P2(j * O / np);
-        for (int j = 0; j < np; j++) KVQ_ADD_P2(rl - O + j * O / np);
+        for (int j = 0; j < np; j++) KVQ_ADD_P2(p.o_piece[j]);
+        for (int j = 0; j < np; j++) KVQ_ADD_P2(rl - O + p.o_piece[j]);
     }
 #undef KVQ_ADD_P2
     return n;
 }
 
-__device__ __forceinline__ bool read_seedable(const KvqParams &p, int rl)
+// P3a: per-read offsets into the packed area and the probe work list (one exclusive scan)
+__device__ void layout_reads(GroupSmem &s, const KvqOut &o, const TileCtx &t, int gid, int gt, int nrd,
+                             uint32_t &totw, uint32_t &totq)
 {
-    return p.seed_ok && (rl / p.npieces) >= KVQ_SEED_K;
+    uint32_t nw = 0, nq = 0; int rl = 0;
+    if (gt < nrd) {
+        rl = s.rd[gt].rl;
+        nw = (uint32_t) ((rl + 15) >> 4) + 1;
+        if (s.rd[gt].flags & 1) nq = (uint32_t) ((rl - KVQ_SEED_K + 16) >> 4);
+    }
+    uint32_t total;
+    const uint32_t ex = group_exscan(nw | (nq << 16), s.warp_tot, &total, gid, gt);
+    uint32_t pw = ex & 0xFFFFu, pq = ex >> 16;
+    if (gt < nrd) {
+        if (pw + nw > PACKW || pq + nq > QCAP) {
+            // does not fit this round's work lists: hand the read to the long-record kernel
+            push_long(o, t.a0 + s.rd[gt].pos, t.seg_end, 1, rl);
+            s.rd[gt].flags = 2;                                     // dead for the rest of the round
+        }
+        s.rd[gt].poff = (uint16_t) min(pw, (uint32_t) PACKW);
+        for (uint32_t j = 0; j < nw && pw + j < PACKW; j++) s.pitem[pw + j] = (uint8_t) gt;
+        for (uint32_t q = 0; q < nq && pq + q < QCAP; q++) s.qitem[pq + q] = (uint16_t) ((gt << 6) | q);
+    }
+    totw = min(total & 0xFFFFu, (uint32_t) PACKW);
+    totq = min(total >> 16, (uint32_t) QCAP);
+    group_sync(gid);
 }
 
-__device__ __forceinline__ void push_seeds(Smem &s, int r, int pbase, uint32_t mask, int kind)
+// P3b: 2-bit pack, one packed word (16 bases) per step
+__device__ void pack_reads(GroupSmem &s, int gt, int totw)
+{
+    const uint32_t *tw = reinterpret_cast<const uint32_t *>(s.tile);
+    for (int x = gt; x < totw; x += GT) {
+        const int r = s.pitem[x];
+        const Rd rd = s.rd[r];
+        if (rd.flags & 2) continue;                                 // dead read (prefix holes)
+        const int j = x - rd.poff;
+        const int nvalid = rd.rl - 16 * j;
+        uint32_t codes = 0;
+        if (nvalid > 0) {
+            const int pos = rd.pos + 16 * j;
+            const int a = pos >> 2; const uint32_t sh = (uint32_t) (pos & 3) << 3;
+            uint32_t w0 = tw[a], w1 = tw[a + 1], w2 = tw[a + 2], w3 = tw[a + 3], w4 = tw[a + 4];
+            codes = pack4(funnel_r(w0, w1, sh)) | (pack4(funnel_r(w1, w2, sh)) << 8)
+                  | (pack4(funnel_r(w2, w3, sh)) << 16) | (pack4(funnel_r(w3, w4, sh)) << 24);
+            if (nvalid < 16) codes &= (1u << (2 * nvalid)) - 1u;
+        }
+        s.packed[x] = codes;
+    }
+}
+
+__device__ __forceinline__ void push_seeds(GroupSmem &s, int r, int pbase, uint32_t mask, int kind)
 {
     int cnt = __popc(mask);
     int at = atomicAdd(&s.nseed, cnt);
@@ -458,49 +517,47 @@ __device__ __forceinline__ void push_seeds(Smem &s, int r, int pbase, uint32_t m
     }
 }
 
-// P5: probes.  T1: every read offset, 16 offsets per thread-step.  T2: a few fixed offsets.
-__device__ void probe_reads(Smem &s, const KvqParams &p, const KvqTemplates &t)
+// P4: probes.  T1: every read offset, 16 offsets per work item.  T2: a few fixed offsets per read.
+__device__ void probe_reads(GroupSmem &s, const Smem &sh, const KvqParams &p, int gt, int nrd, int totq)
 {
-    constexpr int MAXBLK = (MAXRL_FAST - KVQ_SEED_K + 16) / 16;
-    const int nrd = s.nrd;
-    for (int item = threadIdx.x; item < nrd * MAXBLK; item += THREADS) {
-        const int r = item / MAXBLK, q = item - r * MAXBLK;
-        const int rl = s.rd[r].rl;
-        const int npos = rl - KVQ_SEED_K + 1 - 16 * q;      // probe offsets left from 16q on
-        if (npos <= 0 || !read_seedable(p, rl)) continue;
-        const uint32_t *pk = s.packed + r * SLOTW + q;
+    for (int i = gt; i < totq; i += GT) {
+        const int it = s.qitem[i];
+        const int r = it >> 6, q = it & 63;
+        const Rd rd = s.rd[r];
+        if (rd.flags & 2) continue;
+        const int npos = rd.rl - KVQ_SEED_K + 1 - 16 * q;           // probe offsets left from 16q on
+        const uint32_t *pk = s.packed + rd.poff + q;
         const uint32_t lo = pk[0], hi = pk[1];
         uint32_t mask = 0;
 #pragma unroll
         for (int j = 0; j < 16; j++) {
             uint32_t key = funnel_r(lo, hi, 2 * j) & 0xFFFFu;
-            mask |= ((s.bm1[key >> 5] >> (key & 31)) & 1u) << j;
+            mask |= ((sh.bm1[key >> 5] >> (key & 31)) & 1u) << j;
         }
         if (npos < 16) mask &= (1u << npos) - 1u;
         if (mask) push_seeds(s, r, 16 * q, mask, 0);
     }
-    for (int r = threadIdx.x; r < nrd; r += THREADS) {
-        const int rl = s.rd[r].rl;
-        if (!read_seedable(p, rl)) continue;
+    if (gt < nrd && (s.rd[gt].flags & 1)) {
+        const Rd rd = s.rd[gt];
         int p2[MAXP2];
-        const int n2 = build_p2(rl, p.minoverlap, p.npieces, p.max_seqlen, p2);
-        const uint32_t *pk = s.packed + r * SLOTW;
+        const int n2 = build_p2(p, rd.rl, p2);
+        const uint32_t *pk = s.packed + rd.poff;
         for (int i = 0; i < n2; i++) {
             uint32_t key = extract16(pk, p2[i]) & 0xFFFFu;
-            if ((s.bm2[key >> 5] >> (key & 31)) & 1u) push_seeds(s, r, p2[i], 1u, 1);
+            if ((sh.bm2[key >> 5] >> (key & 31)) & 1u) push_seeds(s, gt, p2[i], 1u, 1);
         }
     }
 }
 
-// P6: walk the bucket of every seed and queue the diagonals the reference would evaluate
-__device__ void expand_seeds(Smem &s, const KvqParams &p, const KvqTemplates &t)
+// P5: walk the bucket of every seed and queue the diagonals the reference would evaluate
+__device__ void expand_seeds(GroupSmem &s, const KvqParams &p, const KvqTemplates &t, int gt)
 {
     const int nseed = s.nseed;
-    for (int i = threadIdx.x; i < nseed; i += THREADS) {
+    for (int i = gt; i < nseed; i += GT) {
         const uint32_t sd = s.seedq[i];
         const int r = sd >> 16, pos = (sd >> 1) & 0x7FFF, kind = sd & 1;
         const int rl = s.rd[r].rl;
-        const uint32_t key = extract16(s.packed + r * SLOTW, pos) & 0xFFFFu;
+        const uint32_t key = extract16(s.packed + s.rd[r].poff, pos) & 0xFFFFu;
         const uint32_t *off = kind ? t.t2_off : t.t1_off;
         const uint2 *ent = kind ? t.t2_ent : t.t1_ent;
         const uint32_t e0 = __ldg(off + key), e1 = __ldg(off + key + 1);
@@ -532,7 +589,7 @@ __device__ bool canonical_seed(const KvqParams &p, const uint32_t *rpk, const ui
             return kind == 0 && pos == pj;
     }
     int p2[MAXP2];
-    const int n2 = build_p2(rl, p.minoverlap, p.npieces, p.max_seqlen, p2);
+    const int n2 = build_p2(p, rl, p2);
     for (int i = 0; i < n2; i++) {
         const int toff = p2[i] + d;
         if (toff < 0 || toff > sl - KVQ_SEED_K) continue;
@@ -542,21 +599,22 @@ __device__ bool canonical_seed(const KvqParams &p, const uint32_t *rpk, const ui
     return false;
 }
 
-// P7: one thread per candidate diagonal
-__device__ void verify_candidates(Smem &s, const KvqBatch &b, const TileCtx &tc, const KvqParams &p,
-                                  const KvqTemplates &t, const KvqOut &o)
+// P6: one thread per candidate diagonal
+__device__ void verify_candidates(GroupSmem &s, const KvqBatch &b, const TileCtx &tc, const KvqParams &p,
+                                  const KvqTemplates &t, const KvqOut &o, int gt)
 {
     const uint8_t *tb = reinterpret_cast<const uint8_t *>(s.tile);
     const int ncand = s.ncand;
-    for (int i = threadIdx.x; i < ncand; i += THREADS) {
+    for (int i = gt; i < ncand; i += GT) {
         const unsigned long long c = s.candq[i];
         const int r = (int) (c & 0xFF), sq = (int) ((c >> 8) & 0xFFFFFF);
         const int d = (int) ((c >> 32) & 0xFFFF) - 32768;
         const int pos = (int) ((c >> 48) & 0x3FF), kind = (int) ((c >> 58) & 1);
-        const int rl = s.rd[r].rl, sl = __ldg(t.len + sq);
+        const Rd rd = s.rd[r];
+        const int rl = rd.rl, sl = __ldg(t.len + sq);
         int ro, to, L, rule;
         const int copies = diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule);
-        const uint32_t *rpk = s.packed + r * SLOTW;
+        const uint32_t *rpk = s.packed + rd.poff;
         const uint32_t *tpk = t.packed + __ldg(t.packed_off + sq);
         // Hamming distance in code space (a lower bound of the byte distance)
         int e = 0;
@@ -567,11 +625,11 @@ __device__ void verify_candidates(Smem &s, const KvqBatch &b, const TileCtx &tc,
             e += __popc(m);
         }
         if (e > p.maxerrors) continue;
-        const uint8_t *rd = tb + s.rd[r].pos;
+        const uint8_t *rdp = tb + rd.pos;
         const uint8_t *tp = t.bytes + __ldg(t.byte_off + sq);
-        if (byte_mismatches(rd + ro, tp + to, L, p.maxerrors) > p.maxerrors) continue;
+        if (byte_mismatches(rdp + ro, tp + to, L, p.maxerrors) > p.maxerrors) continue;
         if (!canonical_seed(p, rpk, tpk, rl, sl, d, kind, pos)) continue;
-        emit_hit(t, p, o, sq, d, ro, to, L, rl, b.base_fpos + tc.a0 + s.rd[r].pos, rd, tp, copies, rule);
+        emit_hit(t, p, o, sq, d, ro, to, L, rl, b.base_fpos + tc.a0 + rd.pos, rdp, tp, copies, rule);
     }
 }
 
@@ -596,130 +654,138 @@ __device__ void exhaustive_pair(const KvqParams &p, const KvqTemplates &t, const
 namespace {
 
 // One round = up to CAP owned records of the current tile.
-__device__ void run_round(Smem &s, const KvqBatch &b, const TileCtx &tc, const KvqParams &p,
-                          const KvqTemplates &t, const KvqOut &o, int off, int k0, int nrec, int kcomplete)
+__device__ void run_round(GroupSmem &s, Smem &sh, const KvqBatch &b, const TileCtx &tc, const KvqParams &p,
+                          const KvqTemplates &t, const KvqOut &o, int off, int k0, int nrec, int kcomplete,
+                          int gid, int gt, ThreadStats &ts)
 {
-    if (threadIdx.x == 0) {
-        s.nrd = 0; s.nseed = 0; s.ncand = 0; s.n_exh_reads = 0; s.n_seed_reads = 0; s.overflow = 0;
-    }
-    fill_records(s, tc, off, k0);
-    __syncthreads();
-    process_records(s, b, tc, p, o, k0, nrec, kcomplete);
-    __syncthreads();
+    if (gt == 0) { s.nrd = 0; s.nseed = 0; s.ncand = 0; s.n_exh_reads = 0; s.n_seed_reads = 0; }
+    group_sync(gid);
+    process_records(s, sh, b, tc, p, o, off, k0, nrec, kcomplete, gt, ts);
+    group_sync(gid);
     const int nrd = s.nrd;
-    __syncthreads();                            // everyone has read nrd before the next round resets it
-    if (nrd == 0) return;                       // uniform
+    group_sync(gid);                                // everyone has read nrd before it is reset
+    if (nrd == 0) return;                           // uniform
     const uint8_t *tb = reinterpret_cast<const uint8_t *>(s.tile);
     bool seeded = p.seed_ok && t.n_exh < t.nseqs;
     if (seeded) {
-        pack_reads(s);
-        __syncthreads();
-        probe_reads(s, p, t);
-        __syncthreads();
-        if (s.nseed > SEEDQ) seeded = false;    // uniform: queue overflow -> exhaustive round
+        uint32_t totw, totq;
+        layout_reads(s, o, tc, gid, gt, nrd, totw, totq);
+        pack_reads(s, gt, (int) totw);
+        group_sync(gid);
+        probe_reads(s, sh, p, gt, nrd, (int) totq);
+        group_sync(gid);
+        if (s.nseed > SEEDQ) seeded = false;        // uniform: queue overflow -> exhaustive round
         if (seeded) {
-            expand_seeds(s, p, t);
-            __syncthreads();
+            expand_seeds(s, p, t, gt);
+            group_sync(gid);
             if (s.ncand > CANDQ) seeded = false;
         }
         if (seeded) {
-            if (threadIdx.x == 0) s.cand_count += (unsigned long long) s.ncand;
-            verify_candidates(s, b, tc, p, t, o);
-        } else if (threadIdx.x == 0) {
+            if (gt == 0) ts.cands += (unsigned long long) s.ncand;
+            verify_candidates(s, b, tc, p, t, o, gt);
+        } else if (gt == 0) {
             atomicAdd(&o.ctr->overflow_rounds, 1u);
         }
     }
     // split the reads of the round: seeded ones still owe the non-seedable templates
-    for (int r = threadIdx.x; r < nrd; r += THREADS) {
-        if (seeded && read_seedable(p, s.rd[r].rl)) s.seed_reads[atomicAdd(&s.n_seed_reads, 1)] = (uint16_t) r;
-        else s.exh_reads[atomicAdd(&s.n_exh_reads, 1)] = (uint16_t) r;
+    if (gt < nrd) {
+        const int fl = s.rd[gt].flags;
+        if (!(fl & 2)) {
+            if (seeded && (fl & 1)) s.seed_reads[atomicAdd(&s.n_seed_reads, 1)] = (uint16_t) gt;
+            else s.exh_reads[atomicAdd(&s.n_exh_reads, 1)] = (uint16_t) gt;
+        }
     }
-    __syncthreads();
-    const int wid = threadIdx.x >> 5;
+    group_sync(gid);
+    const int wid = gt >> 5;
     const int ne = s.n_exh_reads, ns = s.n_seed_reads;
-    if (threadIdx.x == 0) s.exh_count += (unsigned long long) ne;
-    for (int pair = wid; pair < ne * t.nseqs; pair += NWARPS) {
+    if (gt == 0) ts.exh += (unsigned long long) ne;
+    for (int pair = wid; pair < ne * t.nseqs; pair += GW) {
         const int r = s.exh_reads[pair / t.nseqs], sq = pair % t.nseqs;
         exhaustive_pair(p, t, o, tb + s.rd[r].pos, s.rd[r].rl, b.base_fpos + tc.a0 + s.rd[r].pos, sq);
     }
-    for (int pair = wid; pair < ns * t.n_exh; pair += NWARPS) {
-        const int r = s.seed_reads[pair / t.n_exh], sq = __ldg(t.exh_list + pair % t.n_exh);
-        exhaustive_pair(p, t, o, tb + s.rd[r].pos, s.rd[r].rl, b.base_fpos + tc.a0 + s.rd[r].pos, sq);
-    }
-    __syncthreads();
+    if (t.n_exh > 0)
+        for (int pair = wid; pair < ns * t.n_exh; pair += GW) {
+            const int r = s.seed_reads[pair / t.n_exh], sq = __ldg(t.exh_list + pair % t.n_exh);
+            exhaustive_pair(p, t, o, tb + s.rd[r].pos, s.rd[r].rl, b.base_fpos + tc.a0 + s.rd[r].pos, sq);
+        }
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
 kvq_scan_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    Smem &s = *reinterpret_cast<Smem *>(smem_raw);
+    Smem &sh = *reinterpret_cast<Smem *>(smem_raw);
+    const int gid = threadIdx.x / GT, gt = threadIdx.x % GT;
+    GroupSmem &s = sh.g[gid];
 
     for (int i = threadIdx.x; i < KVQ_BITMAP_WORDS; i += THREADS) {
-        s.bm1[i] = __ldg(t.t1_bitmap + i);
-        s.bm2[i] = __ldg(t.t2_bitmap + i);
+        sh.bm1[i] = __ldg(t.t1_bitmap + i);
+        sh.bm2[i] = __ldg(t.t2_bitmap + i);
     }
-    for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS) s.hist[i] = 0;
-    if (threadIdx.x == 0) { s.records = 0; s.bases = 0; s.exh_count = 0; s.cand_count = 0; s.longest = -1; }
+    for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS) sh.hist[i] = 0;
+    if (threadIdx.x == 0) sh.longest = -1;
     __syncthreads();
+    ThreadStats ts{0, 0, 0, 0};
 
     for (;;) {
-        if (threadIdx.x == 0) s.seg_cur = (int) atomicAdd(&o.ctr->seg_next, 1u);
-        __syncthreads();
-        const int seg = s.seg_cur;
-        __syncthreads();
-        if (seg >= b.nseg) break;
-        const int64_t seg_beg = b.seg_off[seg], seg_end = b.seg_off[seg + 1];
-        int phase = 0;
-        for (int64_t t0 = seg_beg; t0 < seg_end; t0 += TILE) {
-            TileCtx tc;
-            tc.a0 = t0 & ~(int64_t) 15;
-            tc.shift = (int) (t0 - tc.a0);
-            const int64_t t1 = t0 + TILE < seg_end ? t0 + TILE : seg_end;
-            const int64_t g1 = t1 + MARGIN < seg_end ? t1 + MARGIN : seg_end;
-            tc.tile_end = (int) (t1 - tc.a0);
-            tc.reg_end = (int) (g1 - tc.a0);
-            tc.first = (t0 == seg_beg);
-            tc.at_seg_end = (g1 == seg_end);
-            tc.phase_in = phase;
-            tc.seg_end = seg_end;
-            const int n_all = (int) load_and_index(s, b, tc);
-            const int n_tile = (int) nl_before(s, tc.tile_end);
-            // newline rank -> record-relative numbering (see fill_records)
-            const int off = tc.first ? 0 : ((3 - phase) & 3) + 1;
-            const int vmax_tile = n_tile - 1 - off, vmax_all = n_all - 1 - off;
-            int nown = 0;
-            if (tc.first) nown = (vmax_tile + 1) / 4 + 1;
-            else if (vmax_tile >= -1) nown = (vmax_tile + 1) / 4 + 1;
-            // record k is complete iff its 4th newline v = 4k+3 is inside the region
-            const int kcomplete = vmax_all >= 3 ? (vmax_all - 3) / 4 : -1;
-            for (int k0 = 0; k0 < nown; k0 += CAP) {
-                const int nrec = nown - k0 < CAP ? nown - k0 : CAP;
-                run_round(s, b, tc, p, t, o, off, k0, nrec, kcomplete);
-            }
-            phase = (phase + n_tile) & 3;
-            __syncthreads();
+        if (gt == 0) s.tile_cur = (int) atomicAdd(&o.ctr->tile_next, 1u);
+        group_sync(gid);
+        const int tile = s.tile_cur;
+        if (tile >= b.ntiles) break;
+        const int seg = __ldg(b.tile_seg + tile);
+        const int64_t t0 = __ldg(b.tile_off + tile);
+        const int64_t seg_beg = __ldg(b.seg_off + seg), seg_end = __ldg(b.seg_off + seg + 1);
+        TileCtx tc;
+        tc.a0 = t0 & ~(int64_t) 31;
+        tc.shift = (int) (t0 - tc.a0);
+        const int64_t t1 = t0 + TILE < seg_end ? t0 + TILE : seg_end;
+        const int64_t g1 = t1 + MARGIN < seg_end ? t1 + MARGIN : seg_end;
+        tc.tile_end = (int) (t1 - tc.a0);
+        tc.reg_end = (int) (g1 - tc.a0);
+        tc.first = (t0 == seg_beg);
+        tc.at_seg_end = (g1 == seg_end);
+        tc.seg_end = seg_end;
+        const int n_all = (int) load_and_index(s, b, tc, gid, gt);
+        const int n_tile = (int) nl_before(s, tc.tile_end);
+        if (gt == 0) s.phase_in = resolve_phase(b, tile, tc.first, n_tile);
+        group_sync(gid);
+        const int phase = s.phase_in;
+        // newline rank -> record-relative numbering (see process_records)
+        const int off = tc.first ? 0 : ((3 - phase) & 3) + 1;
+        const int vmax_tile = n_tile - 1 - off, vmax_all = n_all - 1 - off;
+        int nown = 0;
+        if (tc.first || vmax_tile >= -1) nown = (vmax_tile + 1) / 4 + 1;
+        // record k is complete iff its 4th newline v = 4k+3 is inside the staged region
+        const int kcomplete = vmax_all >= 3 ? (vmax_all - 3) / 4 : -1;
+        for (int k0 = 0; k0 < nown; k0 += CAP) {
+            const int nrec = nown - k0 < CAP ? nown - k0 : CAP;
+            run_round(s, sh, b, tc, p, t, o, off, k0, nrec, kcomplete, gid, gt, ts);
         }
+        group_sync(gid);                            // tile buffers are reused by the next tile
     }
 
-    // flush the per-CTA statistics
-    for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS)
-        if (s.hist[i]) atomicAdd(&o.ctr->rls[i], (unsigned long long) s.hist[i]);
-    if (threadIdx.x == 0) {
-        atomicAdd(&o.ctr->records, s.records);
-        atomicAdd(&o.ctr->bases, s.bases);
-        atomicAdd(&o.ctr->exhaustive_reads, s.exh_count);
-        atomicAdd(&o.ctr->candidates, s.cand_count);
-        atomicMax(&o.ctr->longest, (long long) s.longest);
+    // flush the statistics: warp-reduce the per-thread counters, one atomic per warp
+#pragma unroll
+    for (int o2 = 16; o2 > 0; o2 >>= 1) {
+        ts.records += __shfl_down_sync(0xffffffffu, ts.records, o2);
+        ts.bases += __shfl_down_sync(0xffffffffu, ts.bases, o2);
+        ts.exh += __shfl_down_sync(0xffffffffu, ts.exh, o2);
+        ts.cands += __shfl_down_sync(0xffffffffu, ts.cands, o2);
     }
+    if ((threadIdx.x & 31) == 0) {
+        if (ts.records) atomicAdd(&o.ctr->records, ts.records);
+        if (ts.bases) atomicAdd(&o.ctr->bases, ts.bases);
+        if (ts.exh) atomicAdd(&o.ctr->exhaustive_reads, ts.exh);
+        if (ts.cands) atomicAdd(&o.ctr->candidates, ts.cands);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS)
+        if (sh.hist[i]) atomicAdd(&o.ctr->rls[i], (unsigned long long) sh.hist[i]);
+    if (threadIdx.x == 0) atomicMax(&o.ctr->longest, (long long) sh.longest);
 }
 
-} // namespace
-
-namespace {
-
-// Records that do not fit a tile's spill margin, or whose trimmed read exceeds the packed slot:
-// one warp per record straight from global memory, exhaustive matcher.  Rare by construction.
+// Records that do not fit a tile's spill margin, or whose trimmed read exceeds the packed work
+// lists: one warp per record straight from global memory, exhaustive matcher.  Rare by construction.
 __global__ void __launch_bounds__(256)
 kvq_long_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
 {
@@ -770,6 +836,7 @@ kvq_long_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
 } // namespace
 
 int kvq_scan_smem_bytes(void) { return (int) sizeof(Smem); }
+int kvq_scan_groups(void) { return G; }
 
 int kvq_launch_scan(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
                     int sm_count, void *stream)
@@ -781,7 +848,8 @@ int kvq_launch_scan(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p
         if (e != cudaSuccess) return (int) e;
         attr_set = true;
     }
-    int grid = b.nseg < sm_count ? b.nseg : sm_count;
+    int grid = (b.ntiles + G - 1) / G;
+    if (grid > sm_count) grid = sm_count;
     if (grid < 1) grid = 1;
     kvq_scan_kernel<<<grid, THREADS, sizeof(Smem), (cudaStream_t) stream>>>(b, t, p, o);
     return (int) cudaGetLastError();
