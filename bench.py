@@ -226,10 +226,10 @@ def main():
     sampler.start()
     barrier()
     t0 = time.perf_counter()
-    kernel_ms, launches, d2h = 0.0, 0, 0
+    kernel_ms, launches, d2h, call_ms = 0.0, 0, 0, 0.0
     for _ in range(args.steps):
         r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert=False)   # syncs the stream
-        kernel_ms += r.timing['kernel_ms']; launches += r.timing['launches']; d2h += r.timing['d2h_bytes']
+        kernel_ms += r.timing['kernel_ms']; launches += r.timing['launches']; d2h += r.timing['d2h_bytes']; call_ms += r.timing['wall_ms']
     barrier()
     dt = allmax(time.perf_counter() - t0)
     clocks = sampler.summary()
@@ -238,13 +238,13 @@ def main():
     total_bases = allsum(bases * args.steps)
     value = total_bases / dt / 1e9
     kms = allmax(kernel_ms / args.steps)
-    log('[rank %d] resident: %.3f ms/step wall, %.3f ms/step kernels, %d hits, %d records' %
-        (rank, 1e3 * dt / args.steps, kernel_ms / args.steps, r.nhits, r['stats']['records_parsed']))
+    log('[rank %d] resident: %.3f ms/step wall, %.3f ms/step inside the C call, %.3f ms/step kernels, %d hits, %d records' %
+        (rank, 1e3 * dt / args.steps, call_ms / args.steps, kernel_ms / args.steps, r.nhits, r['stats']['records_parsed']))
 
     # ---- one NCCL reduce of the per-template counters (north_star; not in the timed region) --
     if dist is not None:
         import torch
-        cov = torch.tensor(r.coverage + list(r['stats']['nseqhits']) + list(r['stats']['nseqbasehits']),
+        cov = torch.tensor(r.coverage.tolist() + list(r['stats']['nseqhits']) + list(r['stats']['nseqbasehits']),
                            dtype=torch.int64, device='cuda')
         dist.all_reduce(cov, op=dist.ReduceOp.SUM)
         log('[rank %d] NCCL all-reduce of %d counters: total coverage %d' % (rank, cov.numel(), int(cov[:len(r.coverage)].sum())))

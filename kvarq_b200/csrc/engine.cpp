@@ -375,15 +375,30 @@ struct TemplateSet {
     std::vector<int32_t> len;
     KvqTemplates dev{}; KvqParams par{};
     DevBuf d_bytes, d_boff, d_packed, d_poff, d_len, d_seedable, d_exh;
-    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff;
+    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2;
 
     static unsigned char comp(unsigned char c) {
         switch (c) { case 'A': return 'T'; case 'T': return 'A'; case 'C': return 'G'; case 'G': return 'C'; default: return c; }
     }
 
+    std::vector<char> cache_key;
+
     void build(const char *const *seqs, const int32_t *lens, int n, int np, const kvq_config_t &cfg)
     {
         if (n < 0 || (n > 0 && (!seqs || !lens))) throw KvqError(KVQ_ERR_TYPE, "seqlist must be sequence of strings");
+        {   // same templates and knobs as the previous scan: keep the device tables
+            std::vector<char> key;
+            auto put = [&](const void *q, size_t m) { key.insert(key.end(), (const char *) q, (const char *) q + m); };
+            put(&cfg, sizeof(cfg)); put(&n, sizeof(n)); put(&np, sizeof(np));
+            bool ok = true;
+            for (int i = 0; i < n && ok; i++) ok = lens[i] >= 0 && seqs[i];
+            if (ok) {
+                put(lens, sizeof(int32_t) * (size_t) n);
+                for (int i = 0; i < n; i++) put(seqs[i], (size_t) lens[i]);
+                if (key == cache_key && d_bytes.p) { par.want_hits = 1; par.accumulate = 1; return; }
+                cache_key.swap(key);
+            } else cache_key.clear();
+        }
         nseqs = n; nplus = np; len.assign(lens, lens + n);
         for (int i = 0; i < n; i++)
             if (lens[i] < 0 || !seqs[i]) throw KvqError(KVQ_ERR_TYPE, "seqlist must be list of strings");
@@ -453,6 +468,27 @@ struct TemplateSet {
             if ((int) (((uint32_t) x * par.div_magic) >> 16) != x / par.npieces)
                 throw KvqError(KVQ_ERR_RUNTIME, "internal: reciprocal division is inexact");
         for (int j = 0; j < KVQ_MAX_PIECES; j++) par.o_piece[j] = (int) ((int64_t) j * O / par.npieces);
+        par.n2max = 3 * par.npieces;
+        par.div_magic_n2 = (uint32_t) ((65536 + par.n2max - 1) / par.n2max);
+        for (int x = 0; x < 8192; x++)
+            if ((int) (((uint32_t) x * par.div_magic_n2) >> 16) != x / par.n2max)
+                throw KvqError(KVQ_ERR_RUNTIME, "internal: reciprocal division is inexact");
+        // Fixed read offsets probed against T2, per trimmed read length: E+1 pieces of the whole read
+        // (rule d, only if some template is at least as long), of its first minoverlap bases
+        // (rule b) and of its last minoverlap bases (rule a); duplicates removed.
+        std::vector<int16_t> p2((size_t) (KVQ_MAXRL_FAST + 1) * KVQ_P2W, (int16_t) -1);
+        if (seed_ok)
+            for (int rl = par.min_seed_rl; rl <= KVQ_MAXRL_FAST; rl++) {
+                int16_t *row = p2.data() + (size_t) rl * KVQ_P2W; int nn = 0;
+                auto add = [&](int v) { for (int i = 0; i < nn; i++) if (row[i] == v) return; row[nn++] = (int16_t) v; };
+                if (max_len >= rl) for (int j = 0; j < pieces; j++) add((int) ((int64_t) j * rl / pieces));
+                if (rl > O) {
+                    for (int j = 0; j < pieces; j++) add(par.o_piece[j]);
+                    for (int j = 0; j < pieces; j++) add(rl - O + par.o_piece[j]);
+                }
+            }
+        upload(d_p2, p2);
+        dev.p2_tab = d_p2.as<int16_t>();
     }
 };
 
@@ -510,8 +546,13 @@ struct Slot {                           // one batch in flight
     int64_t data_bytes = 0;
 };
 
-struct Accum {                          // device-wide accumulators of one scan
-    DevBuf d_seqhits, d_seqbase, d_cov, d_mut;
+struct Accum {                          // device-wide accumulators of one scan, one allocation:
+    DevBuf d_all; size_t ns = 0, nc = 0;    // [nseqhits ns][nseqbasehits ns][coverage nc][mutcount 6 nc]
+    unsigned long long *seqhits() const { return d_all.as<unsigned long long>(); }
+    unsigned long long *seqbase() const { return seqhits() + ns; }
+    unsigned long long *cov() const { return seqhits() + 2 * ns; }
+    unsigned long long *mut() const { return seqhits() + 2 * ns + nc; }
+    size_t words() const { return 2 * ns + 7 * nc; }
 };
 
 struct RawHit { KvqHitRec h; };
@@ -579,21 +620,19 @@ KvqOut make_out(kvq_engine *e, DevBuf &ctr, DevBuf &hits, size_t hit_cap, DevBuf
     o.hits = hits.as<KvqHitRec>(); o.hit_cap = hit_cap;
     o.blob = blob.as<uint8_t>(); o.blob_cap = blob_cap;
     o.longs = longs.as<KvqLongRec>(); o.long_cap = long_cap;
-    o.nseqhits = e->acc.d_seqhits.as<unsigned long long>();
-    o.nseqbasehits = e->acc.d_seqbase.as<unsigned long long>();
-    o.coverage = e->acc.d_cov.as<unsigned long long>();
-    o.mutcount = e->acc.d_mut.as<unsigned long long>();
+    o.nseqhits = e->acc.seqhits();
+    o.nseqbasehits = e->acc.seqbase();
+    o.coverage = e->acc.cov();
+    o.mutcount = e->acc.mut();
     return o;
 }
 
 void reset_accum(kvq_engine *e)
 {
     const TemplateSet &t = e->tpl;
-    const size_t ns = std::max(1, t.nseqs), nc = (size_t) std::max<int64_t>(1, t.cov_total);
-    e->acc.d_seqhits.ensure(ns * 8); e->acc.d_seqbase.ensure(ns * 8);
-    e->acc.d_cov.ensure(nc * 8); e->acc.d_mut.ensure(nc * 6 * 8);
-    CK(cudaMemset(e->acc.d_seqhits.p, 0, ns * 8)); CK(cudaMemset(e->acc.d_seqbase.p, 0, ns * 8));
-    CK(cudaMemset(e->acc.d_cov.p, 0, nc * 8)); CK(cudaMemset(e->acc.d_mut.p, 0, nc * 6 * 8));
+    e->acc.ns = (size_t) std::max(1, t.nseqs); e->acc.nc = (size_t) std::max<int64_t>(1, t.cov_total);
+    e->acc.d_all.ensure(e->acc.words() * 8);
+    CK(cudaMemset(e->acc.d_all.p, 0, e->acc.words() * 8));
 }
 
 // enqueue memset + scan + long-record kernels for one batch already resident on the device
@@ -677,10 +716,9 @@ void harvest_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
         collect_hits(e, b, s.d_ctr, s.d_hits, s.hit_cap, s.d_blob, s.blob_cap, s.d_longs, s.long_cap, c, s.stream, tot);
     // live per-template counters for engine.stats()
     if (e->tpl.nseqs > 0) {
-        std::vector<unsigned long long> a(e->tpl.nseqs), bb(e->tpl.nseqs);
-        CK(cudaMemcpy(a.data(), e->acc.d_seqhits.p, a.size() * 8, cudaMemcpyDeviceToHost));
-        CK(cudaMemcpy(bb.data(), e->acc.d_seqbase.p, bb.size() * 8, cudaMemcpyDeviceToHost));
-        for (int i = 0; i < e->tpl.nseqs; i++) { e->live.seqhits[i] = (int64_t) a[i]; e->live.seqbasehits[i] = (int64_t) bb[i]; }
+        std::vector<unsigned long long> a(2 * e->acc.ns);
+        CK(cudaMemcpy(a.data(), e->acc.d_all.p, a.size() * 8, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < e->tpl.nseqs; i++) { e->live.seqhits[i] = (int64_t) a[i]; e->live.seqbasehits[i] = (int64_t) a[e->acc.ns + i]; }
     }
 }
 
@@ -751,16 +789,20 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
     fill_stats(e, r->stats, tot.rls, tot.longest, tot.records);
     const int ns = e->tpl.nseqs; const int64_t nc = e->tpl.cov_total;
     r->nseqhits.assign(ns, 0); r->nseqbasehits.assign(ns, 0);
-    if (ns > 0) {
-        CK(cudaMemcpy(r->nseqhits.data(), e->acc.d_seqhits.p, (size_t) ns * 8, cudaMemcpyDeviceToHost));
-        CK(cudaMemcpy(r->nseqbasehits.data(), e->acc.d_seqbase.p, (size_t) ns * 8, cudaMemcpyDeviceToHost));
-        for (int i = 0; i < ns; i++) { e->live.seqhits[i] = r->nseqhits[i]; e->live.seqbasehits[i] = r->nseqbasehits[i]; }
-    }
-    if (e->tpl.nplus > 0 && nc > 0) {
-        r->coverage.resize(nc); r->mutcount.resize(nc * 6);
-        CK(cudaMemcpy(r->coverage.data(), e->acc.d_cov.p, (size_t) nc * 8, cudaMemcpyDeviceToHost));
-        CK(cudaMemcpy(r->mutcount.data(), e->acc.d_mut.p, (size_t) nc * 48, cudaMemcpyDeviceToHost));
-        tot.d2h += nc * 56;
+    {
+        const bool want_cov = e->tpl.nplus > 0 && nc > 0;
+        const size_t words = want_cov ? e->acc.words() : 2 * e->acc.ns;
+        std::vector<int64_t> all(words);
+        CK(cudaMemcpy(all.data(), e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < ns; i++) {
+            r->nseqhits[i] = all[i]; r->nseqbasehits[i] = all[e->acc.ns + i];
+            e->live.seqhits[i] = all[i]; e->live.seqbasehits[i] = all[e->acc.ns + i];
+        }
+        if (want_cov) {
+            r->coverage.assign(all.begin() + 2 * e->acc.ns, all.begin() + 2 * e->acc.ns + nc);
+            r->mutcount.assign(all.begin() + 2 * e->acc.ns + e->acc.nc, all.begin() + 2 * e->acc.ns + e->acc.nc + 6 * nc);
+            tot.d2h += nc * 56;
+        }
     }
     tot.d2h += (int64_t) ns * 16;
     r->timing.kernel_ms = tot.kernel_ms; r->timing.wall_ms = wall_ms; r->timing.launches = tot.launches;

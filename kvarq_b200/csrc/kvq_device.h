@@ -9,6 +9,8 @@
 #define KVQ_MAX_PIECES 8                // seeded path needs maxerrors+1 <= 8
 #define KVQ_MAX_SEEDED_SEQLEN 32000     // diagonal must fit the candidate encoding
 #define KVQ_HIST 1024                   // MAX_READLENGTH, workhorse.c:105
+#define KVQ_MAXRL_FAST 512              // longer trimmed reads take the long-record kernel
+#define KVQ_P2W (3 * KVQ_MAX_PIECES)     // fixed read offsets probed against T2, per read length
 #define KVQ_TILE 32768                  // bytes of a segment owned by one tile (host builds the tile table)
 
 // 2-bit code of a raw byte: A->0 C->1 T->2 G->3; any other byte maps to *some* code.  Equal
@@ -26,6 +28,8 @@ struct KvqParams {
     int32_t min_seed_rl;                // KVQ_SEED_K * npieces: shortest read the seed scheme covers
     uint32_t div_magic;                 // floor(x / npieces) == (x * div_magic) >> 16 for x < 8192
     int32_t o_piece[KVQ_MAX_PIECES];    // floor(j * minoverlap / npieces)
+    int32_t n2max;                      // 3 * npieces: T2 probe slots per read
+    uint32_t div_magic_n2;              // floor(x / n2max) == (x * div_magic_n2) >> 16 for x < 8192
     int32_t accumulate;                 // 0: re-run after a buffer overflow, counters already taken
 };
 
@@ -40,6 +44,7 @@ struct KvqTemplates {
     int32_t nseqs, n_exh;
     const uint32_t *t1_bitmap, *t1_off; const uint2 *t1_ent;   // template-piece seeds   (seq, toff)
     const uint32_t *t2_bitmap, *t2_off; const uint2 *t2_ent;   // every template offset  (seq, toff)
+    const int16_t *p2_tab;              // [KVQ_MAXRL_FAST+1][KVQ_P2W] T2 probe offsets per read length, -1 = unused
     const uint32_t *cov_off;            // [nplus+1] offset of each plus template in coverage[]
     int32_t nplus;                      // 0 = no fused coverage
 };

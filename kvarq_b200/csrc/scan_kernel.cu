@@ -32,12 +32,12 @@ constexpr int LOADMAX = TILE + MARGIN + 32; // + alignment slack of the first 32
 constexpr int NLW = LOADMAX / 32 + 1;       // newline bitmap words (32 bytes each)
 constexpr int WPT = (NLW + GT - 1) / GT;    // bitmap words per thread in the prefix scan
 constexpr int CAP = GT;                     // records per round (one thread per record)
-constexpr int MAXRL_FAST = 512;             // longer trimmed reads go to the long-record kernel
+constexpr int MAXRL_FAST = KVQ_MAXRL_FAST;   // longer trimmed reads go to the long-record kernel
 constexpr int PACKW = 4096;                 // packed words per round (16 bases each)
 constexpr int QCAP = 4096;                  // T1 probe items per round (16 read offsets each)
 constexpr int SEEDQ = 2048;
 constexpr int CANDQ = 1536;
-constexpr int MAXP2 = 3 * KVQ_MAX_PIECES;
+constexpr int ACCQ = 256;                   // code-space survivors per round (warp-cooperative confirm)
 
 struct Rd { uint16_t pos, rl, poff, flags; };   // flags bit0: seedable
 
@@ -53,8 +53,9 @@ struct GroupSmem {
     unsigned long long candq[CANDQ];
     uint16_t exh_reads[CAP];
     uint16_t seed_reads[CAP];
+    uint16_t accq[ACCQ];
     uint32_t warp_tot[GW];
-    int nrd, nseed, ncand, n_exh_reads, n_seed_reads;
+    int nrd, nseed, ncand, nacc, n_exh_reads, n_seed_reads;
     int tile_cur, phase_in;
 };
 
@@ -207,12 +208,21 @@ __device__ uint32_t load_and_index(GroupSmem &s, const KvqBatch &b, const TileCt
 {
     const int nwords = (t.reg_end + 31) >> 5;
     const uint4 *src = reinterpret_cast<const uint4 *>(b.data + t.a0);
-    for (int w = gt; w < NLW + 1; w += GT) {
+    constexpr int NI = (NLW + 1 + GT - 1) / GT;
+    uint4 va[NI], vb[NI];
+#pragma unroll
+    for (int i = 0; i < NI; i++) {                  // every load of the tile in flight at once
+        const int w = gt + i * GT;
+        if (w < nwords) { va[i] = __ldg(src + 2 * w); vb[i] = __ldg(src + 2 * w + 1); }
+    }
+#pragma unroll
+    for (int i = 0; i < NI; i++) {
+        const int w = gt + i * GT;
+        if (w >= NLW + 1) break;
         uint32_t m = 0;
         if (w < nwords) {
-            uint4 va = __ldg(src + 2 * w), vb = __ldg(src + 2 * w + 1);
-            s.tile[2 * w] = va; s.tile[2 * w + 1] = vb;
-            m = nl_mask32(va, vb);
+            s.tile[2 * w] = va[i]; s.tile[2 * w + 1] = vb[i];
+            m = nl_mask32(va[i], vb[i]);
             const int lo = t.shift - (w << 5), hi = t.reg_end - (w << 5);
             if (lo > 0) m &= lo >= 32 ? 0u : (0xFFFFFFFFu << lo);
             if (hi < 32) m &= hi <= 0 ? 0u : ((1u << hi) - 1u);
@@ -435,25 +445,6 @@ __device__ __forceinline__ int byte_mismatches(const uint8_t *a, const uint8_t *
     return e;
 }
 
-// ---------------------------------------------------------------- seed positions -------------
-// Fixed read offsets probed against the all-offsets table T2: E+1 pieces of the whole read
-// (rule d), of its first minoverlap bases (rule b) and of its last minoverlap bases (rule a).
-__device__ __forceinline__ int build_p2(const KvqParams &p, int rl, int *out)
-{
-    int n = 0;
-    const int np = p.npieces, O = p.minoverlap;
-#define KVQ_ADD_P2(v) do { int _v = (v); bool dup = false; \
-        for (int _i = 0; _i < n; _i++) dup |= (out[_i] == _v); if (!dup) out[n++] = _v; } while (0)
-    if (p.max_seqlen >= rl)
-        for (int j = 0; j < np; j++) KVQ_ADD_P2((int) (((uint32_t) (j * rl) * p.div_magic) >> 16));
-    if (rl > O) {
-        for (int j = 0; j < np; j++) KVQ_ADD_P2(p.o_piece[j]);
-        for (int j = 0; j < np; j++) KVQ_ADD_P2(rl - O + p.o_piece[j]);
-    }
-#undef KVQ_ADD_P2
-    return n;
-}
-
 // P3a: per-read offsets into the packed area and the probe work list (one exclusive scan)
 __device__ void layout_reads(GroupSmem &s, const KvqOut &o, const TileCtx &t, int gid, int gt, int nrd,
                              uint32_t &totw, uint32_t &totq)
@@ -518,7 +509,8 @@ __device__ __forceinline__ void push_seeds(GroupSmem &s, int r, int pbase, uint3
 }
 
 // P4: probes.  T1: every read offset, 16 offsets per work item.  T2: a few fixed offsets per read.
-__device__ void probe_reads(GroupSmem &s, const Smem &sh, const KvqParams &p, int gt, int nrd, int totq)
+__device__ void probe_reads(GroupSmem &s, const Smem &sh, const KvqParams &p, const KvqTemplates &t,
+                            int gt, int nrd, int totq)
 {
     for (int i = gt; i < totq; i += GT) {
         const int it = s.qitem[i];
@@ -537,15 +529,16 @@ __device__ void probe_reads(GroupSmem &s, const Smem &sh, const KvqParams &p, in
         if (npos < 16) mask &= (1u << npos) - 1u;
         if (mask) push_seeds(s, r, 16 * q, mask, 0);
     }
-    if (gt < nrd && (s.rd[gt].flags & 1)) {
-        const Rd rd = s.rd[gt];
-        int p2[MAXP2];
-        const int n2 = build_p2(p, rd.rl, p2);
-        const uint32_t *pk = s.packed + rd.poff;
-        for (int i = 0; i < n2; i++) {
-            uint32_t key = extract16(pk, p2[i]) & 0xFFFFu;
-            if ((sh.bm2[key >> 5] >> (key & 31)) & 1u) push_seeds(s, gt, p2[i], 1u, 1);
-        }
+    // T2: a few fixed offsets per read (whole-read / head / tail pieces), table per read length
+    const int n2 = p.n2max;
+    for (int x = gt; x < nrd * n2; x += GT) {
+        const int r = (int) (((uint32_t) x * p.div_magic_n2) >> 16), i = x - r * n2;
+        const Rd rd = s.rd[r];
+        if ((rd.flags & 3) != 1) continue;
+        const int pos = __ldg(t.p2_tab + rd.rl * KVQ_P2W + i);
+        if (pos < 0) continue;
+        const uint32_t key = extract16(s.packed + rd.poff, pos) & 0xFFFFu;
+        if ((sh.bm2[key >> 5] >> (key & 31)) & 1u) push_seeds(s, r, pos, 1u, 1);
     }
 }
 
@@ -578,7 +571,7 @@ __device__ void expand_seeds(GroupSmem &s, const KvqParams &p, const KvqTemplate
 
 // Is (kind, pos) the first seed, in the fixed order T1 pieces then T2 offsets, that fires on
 // diagonal d of (read, seq)?  Every firing seed queues the same diagonal; only this one emits.
-__device__ bool canonical_seed(const KvqParams &p, const uint32_t *rpk, const uint32_t *tpk,
+__device__ bool canonical_seed(const KvqParams &p, const KvqTemplates &t, const uint32_t *rpk, const uint32_t *tpk,
                                int rl, int sl, int d, int kind, int pos)
 {
     for (int j = 0; j < p.npieces; j++) {
@@ -588,35 +581,81 @@ __device__ bool canonical_seed(const KvqParams &p, const uint32_t *rpk, const ui
         if (((extract16(rpk, pj) ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
             return kind == 0 && pos == pj;
     }
-    int p2[MAXP2];
-    const int n2 = build_p2(p, rl, p2);
-    for (int i = 0; i < n2; i++) {
-        const int toff = p2[i] + d;
+    const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
+    for (int i = 0; i < p.n2max; i++) {
+        const int pp = __ldg(p2 + i);
+        if (pp < 0) continue;
+        const int toff = pp + d;
         if (toff < 0 || toff > sl - KVQ_SEED_K) continue;
-        if (((extract16(rpk, p2[i]) ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
-            return kind == 1 && pos == p2[i];
+        if (((extract16(rpk, pp) ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
+            return kind == 1 && pos == pp;
     }
     return false;
 }
 
-// P6: one thread per candidate diagonal
-__device__ void verify_candidates(GroupSmem &s, const KvqBatch &b, const TileCtx &tc, const KvqParams &p,
-                                  const KvqTemplates &t, const KvqOut &o, int gt)
+// Warp-cooperative add_hit + Coverage.apply_hit: lane 0 reserves the output slots, all lanes copy
+// the hitseq bytes and update the coverage arrays.
+__device__ void emit_hit_warp(const KvqTemplates &t, const KvqParams &p, const KvqOut &o, int seq, int d,
+                              int ro, int to, int L, int rl, int64_t file_pos, const uint8_t *rd,
+                              const uint8_t *tp, int copies, int rule)
 {
-    const uint8_t *tb = reinterpret_cast<const uint8_t *>(s.tile);
+    const int lane = threadIdx.x & 31;
+    unsigned long long slot = 0, boff = 0;
+    if (lane == 0) {
+        if (p.accumulate) {
+            atomicAdd(&o.nseqhits[seq], (unsigned long long) copies);
+            atomicAdd(&o.nseqbasehits[seq], (unsigned long long) copies * (unsigned long long) L);
+        }
+        slot = atomicAdd(&o.ctr->hit_count, (unsigned long long) copies);
+        if (p.want_hits) boff = atomicAdd(&o.ctr->blob_used, (unsigned long long) copies * (unsigned long long) L);
+    }
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    boff = __shfl_sync(0xffffffffu, boff, 0);
+    if (p.want_hits) {
+        for (int c = 0; c < copies; c++) {
+            if (lane == 0 && slot + c < o.hit_cap) {
+                KvqHitRec h;
+                h.seq_nr = seq; h.seq_pos = d; h.file_pos = file_pos; h.length = L; h.readlength = rl;
+                h.blob_off = (long long) (boff + (unsigned long long) c * L);
+                h.rule = (copies == 2) ? (c == 0 ? 1 : 2) : rule; h.pad = 0;
+                o.hits[slot + c] = h;
+            }
+            if (boff + (unsigned long long) (c + 1) * L <= o.blob_cap)
+                for (int j = lane; j < L; j += 32) o.blob[boff + (unsigned long long) c * L + j] = rd[ro + j];
+        }
+    }
+    if (t.nplus > 0 && p.accumulate) {
+        const bool plus = seq < t.nplus;
+        const int tpl = plus ? seq : seq - t.nplus;
+        const int sl = __ldg(t.len + seq);
+        const unsigned long long cb = __ldg(t.cov_off + tpl);
+        for (int j = lane; j < L; j += 32) {
+            const int sidx = to + j;
+            const unsigned long long pidx = cb + (unsigned long long) (plus ? sidx : sl - 1 - sidx);
+            atomicAdd(&o.coverage[pidx], (unsigned long long) copies);
+            const uint8_t hb = rd[ro + j];
+            if (hb != tp[sidx])
+                atomicAdd(&o.mutcount[pidx * 6 + base_column(plus ? hb : complement(hb))],
+                          (unsigned long long) copies);
+        }
+    }
+}
+
+// P6a: one thread per candidate diagonal: Hamming distance in code space (XOR/popc on packed
+// words), a lower bound of the byte distance.  Survivors are queued for P6b.
+__device__ void filter_candidates(GroupSmem &s, const KvqParams &p, const KvqTemplates &t, int gt)
+{
     const int ncand = s.ncand;
     for (int i = gt; i < ncand; i += GT) {
         const unsigned long long c = s.candq[i];
         const int r = (int) (c & 0xFF), sq = (int) ((c >> 8) & 0xFFFFFF);
         const int d = (int) ((c >> 32) & 0xFFFF) - 32768;
-        const int pos = (int) ((c >> 48) & 0x3FF), kind = (int) ((c >> 58) & 1);
         const Rd rd = s.rd[r];
         const int rl = rd.rl, sl = __ldg(t.len + sq);
         int ro, to, L, rule;
-        const int copies = diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule);
+        diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule);
         const uint32_t *rpk = s.packed + rd.poff;
         const uint32_t *tpk = t.packed + __ldg(t.packed_off + sq);
-        // Hamming distance in code space (a lower bound of the byte distance)
         int e = 0;
         for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
             uint32_t x = extract16(rpk, ro + j) ^ extract16_g(tpk, to + j);
@@ -625,11 +664,37 @@ __device__ void verify_candidates(GroupSmem &s, const KvqBatch &b, const TileCtx
             e += __popc(m);
         }
         if (e > p.maxerrors) continue;
+        const int at = atomicAdd(&s.nacc, 1);
+        if (at < ACCQ) s.accq[at] = (uint16_t) i;
+    }
+}
+
+// P6b: one warp per survivor: byte-exact confirm, canonical-seed dedupe, emission
+__device__ void confirm_candidates(GroupSmem &s, const KvqBatch &b, const TileCtx &tc, const KvqParams &p,
+                                   const KvqTemplates &t, const KvqOut &o, int gt)
+{
+    const uint8_t *tb = reinterpret_cast<const uint8_t *>(s.tile);
+    const int lane = gt & 31;
+    const int nacc = s.nacc < ACCQ ? s.nacc : ACCQ;
+    for (int a = gt >> 5; a < nacc; a += GW) {
+        const unsigned long long c = s.candq[s.accq[a]];
+        const int r = (int) (c & 0xFF), sq = (int) ((c >> 8) & 0xFFFFFF);
+        const int d = (int) ((c >> 32) & 0xFFFF) - 32768;
+        const int pos = (int) ((c >> 48) & 0x3FF), kind = (int) ((c >> 58) & 1);
+        const Rd rd = s.rd[r];
+        const int rl = rd.rl, sl = __ldg(t.len + sq);
+        int ro, to, L, rule;
+        const int copies = diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule);
         const uint8_t *rdp = tb + rd.pos;
         const uint8_t *tp = t.bytes + __ldg(t.byte_off + sq);
-        if (byte_mismatches(rdp + ro, tp + to, L, p.maxerrors) > p.maxerrors) continue;
-        if (!canonical_seed(p, rpk, tpk, rl, sl, d, kind, pos)) continue;
-        emit_hit(t, p, o, sq, d, ro, to, L, rl, b.base_fpos + tc.a0 + rd.pos, rdp, tp, copies, rule);
+        int e = 0;
+        for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
+        e = __reduce_add_sync(0xffffffffu, e);
+        if (e > p.maxerrors) continue;
+        const uint32_t *rpk = s.packed + rd.poff;
+        const uint32_t *tpk = t.packed + __ldg(t.packed_off + sq);
+        if (!canonical_seed(p, t, rpk, tpk, rl, sl, d, kind, pos)) continue;      // warp-uniform
+        emit_hit_warp(t, p, o, sq, d, ro, to, L, rl, b.base_fpos + tc.a0 + rd.pos, rdp, tp, copies, rule);
     }
 }
 
@@ -658,7 +723,7 @@ __device__ void run_round(GroupSmem &s, Smem &sh, const KvqBatch &b, const TileC
                           const KvqTemplates &t, const KvqOut &o, int off, int k0, int nrec, int kcomplete,
                           int gid, int gt, ThreadStats &ts)
 {
-    if (gt == 0) { s.nrd = 0; s.nseed = 0; s.ncand = 0; s.n_exh_reads = 0; s.n_seed_reads = 0; }
+    if (gt == 0) { s.nrd = 0; s.nseed = 0; s.ncand = 0; s.nacc = 0; s.n_exh_reads = 0; s.n_seed_reads = 0; }
     group_sync(gid);
     process_records(s, sh, b, tc, p, o, off, k0, nrec, kcomplete, gt, ts);
     group_sync(gid);
@@ -672,7 +737,7 @@ __device__ void run_round(GroupSmem &s, Smem &sh, const KvqBatch &b, const TileC
         layout_reads(s, o, tc, gid, gt, nrd, totw, totq);
         pack_reads(s, gt, (int) totw);
         group_sync(gid);
-        probe_reads(s, sh, p, gt, nrd, (int) totq);
+        probe_reads(s, sh, p, t, gt, nrd, (int) totq);
         group_sync(gid);
         if (s.nseed > SEEDQ) seeded = false;        // uniform: queue overflow -> exhaustive round
         if (seeded) {
@@ -681,8 +746,13 @@ __device__ void run_round(GroupSmem &s, Smem &sh, const KvqBatch &b, const TileC
             if (s.ncand > CANDQ) seeded = false;
         }
         if (seeded) {
+            filter_candidates(s, p, t, gt);
+            group_sync(gid);
+            if (s.nacc > ACCQ) seeded = false;      // uniform: too many survivors -> exhaustive round
+        }
+        if (seeded) {
             if (gt == 0) ts.cands += (unsigned long long) s.ncand;
-            verify_candidates(s, b, tc, p, t, o, gt);
+            confirm_candidates(s, b, tc, p, t, o, gt);
         } else if (gt == 0) {
             atomicAdd(&o.ctr->overflow_rounds, 1u);
         }

@@ -45,7 +45,9 @@ def _as_char(v):
 
 
 class Result(dict):
-    """The dict findseqs returns, plus the fused outputs as attributes."""
+    """The dict findseqs returns, plus the fused outputs as attributes: ``coverage`` (int64
+    numpy array over the concatenated plus templates) and ``mutcount`` ([..][6] alternate-base
+    counts A,C,G,T,N,other), ``timing``, ``nhits``."""
     coverage = None
     mutcount = None
     timing = None
@@ -150,9 +152,10 @@ class Engine(object):
             cn = C.c_int64()
             cov = lib.kvq_result_coverage(res, C.byref(cn))
             if cov and cn.value:
-                out.coverage = [cov[i] for i in range(cn.value)]
+                import numpy as np
+                out.coverage = np.ctypeslib.as_array(cov, shape=(cn.value,)).copy()
                 mut = lib.kvq_result_mutcount(res, C.byref(cn))
-                out.mutcount = [[mut[6 * i + j] for j in range(6)] for i in range(cn.value // 6)]
+                out.mutcount = np.ctypeslib.as_array(mut, shape=(cn.value // 6, 6)).copy()
             t = lib.kvq_result_timing(res).contents
             out.timing = {k: getattr(t, k) for k, _ in L.Timing._fields_}
             out.nhits = n
