@@ -99,10 +99,17 @@ int kvq_findseqs(kvq_engine *e, const char *const *fnames, int nfiles,
                  const char *const *seqs, const int32_t *seqlens, int nseqs, int nplus,
                  kvq_result **out);
 
-/* Same scan over in-memory FastQ "files" (host buffers; plain, already inflated). */
+/* Same scan over in-memory FastQ "files" (host buffers; plain, already inflated).  The buffers
+ * are scanned in place: batches are DMA'd from the caller's memory (fast when it is page-locked,
+ * see kvq_host_alloc) and must stay valid until the call returns. */
 int kvq_findseqs_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens, int nbufs,
                      const char *const *seqs, const int32_t *seqlens, int nseqs, int nplus,
                      kvq_result **out);
+
+/* Page-locked host memory for kvq_findseqs_mem inputs: buffers allocated here are copied to the
+ * GPU by DMA straight from where they lie (no staging copy on the host). */
+void *kvq_host_alloc(int64_t nbytes);
+void kvq_host_free(void *p);
 
 /* Device-resident variant: stage once (host->HBM, not timed), scan many times. */
 int kvq_stage_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens, int nbufs,

@@ -53,6 +53,8 @@ SIGNATURES = {
     'kvq_scan_staged': (C.c_int, [VP, VP, P(C.c_char_p), P(C.c_int32), C.c_int, C.c_int, C.c_int,
                                   P(VP)]),
     'kvq_staged_free': (None, [VP]),
+    'kvq_host_alloc': (VP, [C.c_int64]),
+    'kvq_host_free': (None, [VP]),
     'kvq_result_nhits': (C.c_int64, [VP]),
     'kvq_result_hits': (P(HitRec), [VP]),
     'kvq_result_hitseq_blob': (VP, [VP]),

@@ -56,6 +56,7 @@ struct Source {
     virtual int64_t disk_size() const = 0;          // on-disk (compressed) size
     virtual int64_t disk_pos() const = 0;           // ftell() of the reference at this point
     virtual bool compressed() const = 0;
+    virtual const char *direct() const { return nullptr; }   // next unread byte, if the source is memory
 };
 
 struct MemSource : Source {
@@ -63,13 +64,15 @@ struct MemSource : Source {
     MemSource(const char *p_, int64_t n_) : p(p_), n(n_), at(0) {}
     int64_t fill(char *dst, int64_t cap, bool *filled) override {
         int64_t m = std::min(cap, n - at);
-        memcpy(dst, p + at, m); at += m;
+        if (dst != p + at) memcpy(dst, p + at, m);      // zero-copy batches alias the caller's buffer
+        at += m;
         *filled = (m == cap);
         return m;
     }
     int64_t disk_size() const override { return n; }
     int64_t disk_pos() const override { return at; }
     bool compressed() const override { return false; }
+    const char *direct() const override { return p + at; }
 };
 
 struct PlainFileSource : Source {
@@ -206,7 +209,9 @@ struct LiveStats {                      // what engine.stats() may read while a 
 };
 
 struct HostBatch {
-    char *data = nullptr;               // pinned, BATCH_BYTES + BATCH_PAD
+    char *own = nullptr;                // the slot's pinned buffer, BATCH_BYTES + BATCH_PAD
+    bool borrowed = false;              // data aliases the caller's memory (in-memory sources): no host copy
+    char *data = nullptr;               // own, or a pointer into the caller's buffer
     int64_t nbytes = 0;
     int64_t base_fpos = 0;
     std::vector<int64_t> cuts;          // segment boundaries, cuts[0] == 0, cuts.back() == nbytes
@@ -241,14 +246,23 @@ public:
     {
         b.cuts.clear(); b.cuts.push_back(0); b.nbytes = 0;
         int64_t left = (int64_t) carry_.size();
-        if (left) memcpy(b.data, carry_.data(), left);
+        if (!finished_ && at_eof_ && next_file_ < nfiles_) { open_next(); at_eof_ = false; }
+        // in-memory sources are scanned in place: the deferred tail sits right before the next
+        // unread byte of the same buffer (it is empty at a file switch)
+        const char *direct = src_ ? src_->direct() : nullptr;
+        b.borrowed = direct != nullptr;
+        b.data = b.borrowed ? const_cast<char *>(direct) - left : b.own;
+        if (left && !b.borrowed) memcpy(b.data, carry_.data(), left);
         carry_.clear();
         b.base_fpos = fpos_ - left;
         int64_t win = 0;
         while (!finished_) {
             if (stop.load(std::memory_order_relaxed)) { finished_ = true; left = 0; break; }
             if (win + REF_CHUNK > BATCH_BYTES) break;                       // batch full
-            if (at_eof_ && next_file_ < nfiles_) open_next();               // :749-753
+            if (at_eof_ && next_file_ < nfiles_) {                          // :749-753
+                if (b.borrowed) break;                                      // next buffer = next batch
+                open_next();
+            }
             at_eof_ = false;
             bool filled = false;
             const int64_t got = src_->fill(b.data + win + left, REF_CHUNK - left, &filled);
@@ -277,7 +291,7 @@ public:
         }
         if (left) carry_.assign(b.data + win, b.data + win + left);
         b.nbytes = win;
-        memset(b.data + win, 0, BATCH_PAD);
+        if (!b.borrowed) memset(b.data + win, 0, BATCH_PAD);
         return win > 0;
     }
 
@@ -589,7 +603,7 @@ void init_slots(kvq_engine *e)
     if (e->slots_ready) return;
     for (auto &s : e->slots) {
         s.pin.ensure(BATCH_BYTES + BATCH_PAD);
-        s.hb.data = s.pin.as<char>();
+        s.hb.own = s.pin.as<char>(); s.hb.data = s.hb.own;
         s.d_data.ensure(BATCH_BYTES + BATCH_PAD);
         const size_t nseg_max = (size_t) (BATCH_BYTES / 4096) + 64;     // cuts are >= 1 byte apart; see launch
         s.d_seg.ensure(nseg_max * sizeof(int64_t)); s.h_seg.ensure(nseg_max * sizeof(int64_t));
@@ -655,7 +669,12 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     const int nseg = (int) hb.cuts.size() - 1;
     s.d_seg.ensure(hb.cuts.size() * 8); s.h_seg.ensure(hb.cuts.size() * 8);
     memcpy(s.h_seg.p, hb.cuts.data(), hb.cuts.size() * 8);
-    CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes + BATCH_PAD, cudaMemcpyHostToDevice, s.stream));
+    if (hb.borrowed) {
+        CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes, cudaMemcpyHostToDevice, s.stream));
+        CK(cudaMemsetAsync(s.d_data.as<char>() + hb.nbytes, 0, BATCH_PAD, s.stream));
+    } else {
+        CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes + BATCH_PAD, cudaMemcpyHostToDevice, s.stream));
+    }
     CK(cudaMemcpyAsync(s.d_seg.p, s.h_seg.p, hb.cuts.size() * 8, cudaMemcpyHostToDevice, s.stream));
     std::vector<int64_t> toff; std::vector<int32_t> tseg;
     build_tiles(hb.cuts, toff, tseg);
@@ -1066,7 +1085,7 @@ int kvq_stage_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens
         LiveStats live; live.reset(0);
         StreamCutter cutter(std::vector<std::string>(), std::move(mems), &live);
         std::vector<char> tmp((size_t) (BATCH_BYTES + BATCH_PAD));
-        HostBatch hb; hb.data = tmp.data();
+        HostBatch hb; hb.own = tmp.data(); hb.data = hb.own;
         std::vector<int64_t> cuts; cuts.push_back(0);
         std::atomic<int> nostop{0};
         int64_t at = 0; bool first = true;
@@ -1134,5 +1153,14 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
 }
 
 void kvq_staged_free(kvq_staged *st) { delete st; }
+
+void *kvq_host_alloc(int64_t nbytes)
+{
+    void *p = nullptr;
+    if (nbytes <= 0 || cudaHostAlloc(&p, (size_t) nbytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+
+void kvq_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 } // extern "C"

@@ -105,8 +105,18 @@ class Engine(object):
                 'Amin': cfg.Amin.decode('latin-1'), 'Azero': cfg.Azero.decode('latin-1')}
 
     # -- helpers ---------------------------------------------------------------------------
+    def _seq_args(self, seqlist):
+        key = tuple(seqlist) if isinstance(seqlist, (list, tuple)) else None
+        cached = getattr(self, '_seq_cache', None)
+        if key is not None and cached is not None and cached[0] == key:
+            return cached[1]
+        out = self._seq_args_build(seqlist)
+        if key is not None:
+            self._seq_cache = (key, out)
+        return out
+
     @staticmethod
-    def _seq_args(seqlist):
+    def _seq_args_build(seqlist):
         try:
             iter(seqlist)
             n = len(seqlist)
@@ -202,6 +212,25 @@ class Engine(object):
         ptrs = (C.c_void_p * max(1, len(arrs)))(*[a.ctypes.data if a.size else None for a in arrs])
         lens64 = (C.c_int64 * max(1, len(arrs)))(*[a.size for a in arrs])
         return arrs, ptrs, lens64
+
+    def pinned_copy(self, data):
+        """Copy `data` (bytes / uint8 array) into page-locked host memory (kvq_host_alloc) and
+        return it as a numpy uint8 array; free with release_pinned()."""
+        import numpy as np
+        src = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data.reshape(-1).view(np.uint8)
+        ptr = self._lib.kvq_host_alloc(max(1, src.size))
+        if not ptr:
+            raise MemoryError('kvq_host_alloc failed')
+        arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(max(1, src.size),))[:src.size]
+        arr[:] = src
+        self._pinned = getattr(self, '_pinned', {})
+        self._pinned[arr.ctypes.data] = ptr
+        return arr
+
+    def release_pinned(self, arr):
+        ptr = getattr(self, '_pinned', {}).pop(arr.ctypes.data, None)
+        if ptr:
+            self._lib.kvq_host_free(ptr)
 
     def stage(self, buffers):
         """Copy FastQ buffers into HBM once; returns a handle for scan_staged()."""
