@@ -374,10 +374,11 @@ uint32_t kmer_key(const unsigned char *s)            // KVQ_SEED_K bases, base 0
 }
 
 struct SeedTable {
-    std::vector<uint32_t> bitmap, off; std::vector<uint2> ent;
-    void build(std::vector<std::pair<uint32_t, uint2>> &items) {
+    std::vector<uint32_t> bitmap, off; std::vector<uint4> ent; std::vector<uint8_t> present;
+    void build(std::vector<std::pair<uint32_t, uint4>> &items) {
         bitmap.assign(KVQ_BITMAP_WORDS, 0); off.assign(KVQ_NKEYS + 1, 0); ent.resize(items.size());
-        for (auto &it : items) { off[it.first + 1]++; bitmap[it.first >> 5] |= 1u << (it.first & 31); }
+        present.assign(KVQ_NKEYS, 0);
+        for (auto &it : items) { off[it.first + 1]++; bitmap[it.first >> 5] |= 1u << (it.first & 31); present[it.first] = 1; }
         for (int k = 0; k < KVQ_NKEYS; k++) off[k + 1] += off[k];
         std::vector<uint32_t> at(off.begin(), off.end() - 1);
         for (auto &it : items) ent[at[it.first]++] = it.second;
@@ -431,7 +432,7 @@ struct TemplateSet {
 
         std::vector<uint8_t> bytes; std::vector<uint32_t> boff(n + 1, 0), packed, poff(n + 1, 0);
         std::vector<uint8_t> seedable(n, 0); std::vector<int32_t> exh;
-        std::vector<std::pair<uint32_t, uint2>> it1, it2;
+        std::vector<std::pair<uint32_t, uint4>> it1, it2;
         int max_len = 0;
         for (int i = 0; i < n; i++) {
             const unsigned char *s = (const unsigned char *) seqs[i]; const int sl = lens[i];
@@ -444,12 +445,14 @@ struct TemplateSet {
             const bool ok = seed_ok && sl / pieces >= KVQ_SEED_K && sl <= KVQ_MAX_SEEDED_SEQLEN;
             seedable[i] = ok;
             if (!ok) { exh.push_back(i); continue; }
+            // entry = {seq, toff | len << 16, offset of the packed codes, offset of the raw bytes}
+            auto entry = [&](int toff) { return make_uint4((unsigned) i, (unsigned) toff | ((unsigned) sl << 16), poff[i], boff[i]); };
             for (int j = 0; j < pieces; j++) {
                 const int toff = (int) ((int64_t) j * sl / pieces);
-                it1.push_back({kmer_key(s + toff), make_uint2((unsigned) i, (unsigned) toff)});
+                it1.push_back({kmer_key(s + toff), entry(toff)});
             }
             for (int toff = 0; toff + KVQ_SEED_K <= sl; toff++)
-                it2.push_back({kmer_key(s + toff), make_uint2((unsigned) i, (unsigned) toff)});
+                it2.push_back({kmer_key(s + toff), entry(toff)});
         }
         boff[n] = (uint32_t) bytes.size(); poff[n] = (uint32_t) packed.size();
         bytes.resize(bytes.size() + 64, 0);
@@ -460,7 +463,7 @@ struct TemplateSet {
 
         upload(d_bytes, bytes); upload(d_boff, boff); upload(d_packed, packed, 4); upload(d_poff, poff);
         upload(d_len, len); upload(d_seedable, seedable); upload(d_exh, exh);
-        upload(d_bm1, t1.bitmap); upload(d_off1, t1.off); upload(d_ent1, t1.ent);
+        upload(d_bm1, t1.present); upload(d_off1, t1.off); upload(d_ent1, t1.ent);
         upload(d_bm2, t2.bitmap); upload(d_off2, t2.off); upload(d_ent2, t2.ent);
         upload(d_covoff, covoff);
 
@@ -468,8 +471,8 @@ struct TemplateSet {
         dev.packed = d_packed.as<uint32_t>(); dev.packed_off = d_poff.as<uint32_t>();
         dev.len = d_len.as<int32_t>(); dev.seedable = d_seedable.as<uint8_t>();
         dev.exh_list = d_exh.as<int32_t>(); dev.nseqs = n; dev.n_exh = (int) exh.size();
-        dev.t1_bitmap = d_bm1.as<uint32_t>(); dev.t1_off = d_off1.as<uint32_t>(); dev.t1_ent = d_ent1.as<uint2>();
-        dev.t2_bitmap = d_bm2.as<uint32_t>(); dev.t2_off = d_off2.as<uint32_t>(); dev.t2_ent = d_ent2.as<uint2>();
+        dev.t1_present = d_bm1.as<uint8_t>(); dev.t1_off = d_off1.as<uint32_t>(); dev.t1_ent = d_ent1.as<uint4>();
+        dev.t2_bitmap = d_bm2.as<uint32_t>(); dev.t2_off = d_off2.as<uint32_t>(); dev.t2_ent = d_ent2.as<uint4>();
         dev.cov_off = d_covoff.as<uint32_t>(); dev.nplus = np;
 
         par.maxerrors = E; par.minoverlap = O; par.minreadlength = cfg.minreadlength;

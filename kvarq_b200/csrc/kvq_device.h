@@ -11,7 +11,9 @@
 #define KVQ_HIST 1024                   // MAX_READLENGTH, workhorse.c:105
 #define KVQ_MAXRL_FAST 512              // longer trimmed reads take the long-record kernel
 #define KVQ_P2W (3 * KVQ_MAX_PIECES)     // fixed read offsets probed against T2, per read length
-#define KVQ_TILE 32768                  // bytes of a segment owned by one tile (host builds the tile table)
+#define KVQ_ROW 1024                    // bytes one warp loads per step (32 lanes x 32 bytes)
+#define KVQ_OWN_ROWS 8
+#define KVQ_TILE (KVQ_OWN_ROWS * KVQ_ROW) // bytes of a segment owned by one tile (host builds the tile table)
 
 // 2-bit code of a raw byte: A->0 C->1 T->2 G->3; any other byte maps to *some* code.  Equal
 // bytes always give equal codes, so exact-match seeds found in code space are complete; every
@@ -42,8 +44,10 @@ struct KvqTemplates {
     const uint8_t *seedable;            // [nseqs]
     const int32_t *exh_list;            // indices of non-seedable seqs
     int32_t nseqs, n_exh;
-    const uint32_t *t1_bitmap, *t1_off; const uint2 *t1_ent;   // template-piece seeds   (seq, toff)
-    const uint32_t *t2_bitmap, *t2_off; const uint2 *t2_ent;   // every template offset  (seq, toff)
+    // seed tables: presence per 16-bit key (T1: one byte per key, T2: one bit per key), CSR
+    // offsets per key and entries {seq, toff | len << 16, packed_off, byte_off}
+    const uint8_t *t1_present; const uint32_t *t1_off; const uint4 *t1_ent;   // template-piece seeds
+    const uint32_t *t2_bitmap, *t2_off; const uint4 *t2_ent;                  // every template offset
     const int16_t *p2_tab;              // [KVQ_MAXRL_FAST+1][KVQ_P2W] T2 probe offsets per read length, -1 = unused
     const uint32_t *cov_off;            // [nplus+1] offset of each plus template in coverage[]
     int32_t nplus;                      // 0 = no fused coverage

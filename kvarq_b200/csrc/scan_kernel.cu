@@ -1,19 +1,22 @@
 // sm_100a kernels of the KvarQ read-scanning path (reference: csrc/workhorse.c:976-1197).
 //
-// Persistent kernel, one CTA per SM.  A CTA holds G independent warp groups; every group claims
-// 32 KiB tiles of the FastQ stream in stream order from a global queue and runs the whole path
-// on its tile in shared memory, synchronising only inside the group (named barriers):
-//   P1  stage tile (+ spill margin) with 128-bit loads, SWAR newline bitmap, group prefix scan;
-//       the tile's newline count is published and the line phase of the tile (newlines of its
-//       segment before it, mod 4) resolved by decoupled look-back      [workhorse.c:1018-1030]
-//   P2  one thread per record: select its 4 newlines from the bitmap, '@' / '+' sanity checks,
-//       Phred trim (first longest run >= Amin), histogram, length filter [workhorse.c:1037-1103]
-//   P3  2-bit packing of the trimmed reads (dense work lists, 16 bases per step)
-//   P4  seed probes against bitmaps in shared memory: every read offset vs the template-piece
-//       table T1, a few fixed read offsets vs the all-offsets table T2
-//   P5  bucket expansion (tables in L2) -> candidate diagonals
-//   P6  XOR/popc Hamming verify on packed words, byte-exact confirm, canonical-seed dedupe,
-//       hit emission through atomics, fused coverage            [workhorse.c:1107-1175,408-443]
+// Persistent kernel, one CTA per SM, every WARP an independent worker (no block-wide barrier in
+// the steady state).  A warp claims 8 KiB tiles of the FastQ stream in stream order from a global
+// queue and runs the whole path on its tile:
+//   P1  coalesced 128-bit loads, 32 bytes per lane; straight from registers every 32-byte word
+//       is reduced to three bit planes kept in shared memory: newline mask, quality-pass mask
+//       (byte >= Amin) and 2-bit base codes.  The raw bytes are never staged.  A warp prefix scan
+//       ranks the newlines and scatters their positions; the tile's newline count is published
+//       and the line phase of the tile (newlines of its segment before it, mod 4) resolved by a
+//       lane-parallel decoupled look-back                                [workhorse.c:1018-1030]
+//   P2  one lane per record: its 4 newlines, '@' / '+' sanity checks, Phred trim (first longest
+//       run >= Amin) on the quality-pass plane, histogram, length filter  [workhorse.c:1037-1103]
+//   P3  seed probes on the code plane: every read offset against the byte-per-key table T1
+//       (template pieces) in shared memory, a few fixed read offsets against the bitmap T2 (all
+//       template offsets); seeds go to a small per-warp stack that is drained 32 at a time
+//   P4  bucket walk (tables in L2), XOR/popc Hamming verify on packed words, then warp-wide
+//       byte-exact confirm, canonical-seed dedupe, hit emission through atomics and the fused
+//       coverage update                                       [workhorse.c:1107-1175,408-443]
 // Reads or templates the seed scheme cannot cover take the exhaustive matcher (same acceptance
 // rule, every diagonal).  Acceptance rule: SURVEY.md Appendix B / workhorse.c:1112-1174.
 #include <cuda_runtime.h>
@@ -22,116 +25,78 @@
 
 namespace {
 
-constexpr int G = 2;                        // warp groups per CTA
-constexpr int GT = 256;                     // threads per group
-constexpr int THREADS = G * GT;
-constexpr int GW = GT / 32;                 // warps per group
-constexpr int TILE = KVQ_TILE;
-constexpr int MARGIN = 3072;                // spill: records starting in the tile may end here
-constexpr int LOADMAX = TILE + MARGIN + 32; // + alignment slack of the first 32-byte word
-constexpr int NLW = LOADMAX / 32 + 1;       // newline bitmap words (32 bytes each)
-constexpr int WPT = (NLW + GT - 1) / GT;    // bitmap words per thread in the prefix scan
-constexpr int CAP = GT;                     // records per round (one thread per record)
-constexpr int MAXRL_FAST = KVQ_MAXRL_FAST;   // longer trimmed reads go to the long-record kernel
-constexpr int PACKW = 4096;                 // packed words per round (16 bases each)
-constexpr int QCAP = 4096;                  // T1 probe items per round (16 read offsets each)
-constexpr int SEEDQ = 2048;
-constexpr int CANDQ = 1536;
-constexpr int ACCQ = 256;                   // code-space survivors per round (warp-cooperative confirm)
+constexpr int NWARPS = 20;                  // warps per CTA (shared memory bound)
+constexpr int THREADS = NWARPS * 32;
+constexpr int OWN_ROWS = KVQ_OWN_ROWS;
+constexpr int EXTRA_ROWS = 3;               // spill: records starting in the tile may end here
+constexpr int MAX_ROWS = OWN_ROWS + EXTRA_ROWS;
+constexpr int NWORDS = MAX_ROWS * 32;       // 32-byte words of the staged region
+constexpr int NLCAP = 144;                  // newline positions kept per round (32 records + slack)
+constexpr int MAXRL_FAST = KVQ_MAXRL_FAST;  // longer trimmed reads go to the long-record kernel
+constexpr int SEEDQ = 64;
 
-struct Rd { uint16_t pos, rl, poff, flags; };   // flags bit0: seedable
-
-struct GroupSmem {
-    uint4 tile[LOADMAX / 16 + 4];           // + slack for word-aligned over-reads
-    uint32_t nlmask[NLW + 1];
-    uint32_t nlpref[NLW + 1];
-    Rd rd[CAP];
-    uint32_t packed[PACKW + 2];
-    uint8_t pitem[PACKW];                   // packed word -> read
-    uint16_t qitem[QCAP];                   // probe item -> read << 6 | block
+struct WarpSmem {
+    uint32_t nl[NWORDS + 1];                // newline plane, bit j of word w <=> byte 32 w + j is '\n'
+    uint32_t ge[NWORDS + 1];                // quality plane, byte >= Amin
+    uint32_t pk[2 * NWORDS + 4];            // code plane: 2 bits per byte, contiguous stream
+    uint16_t nlpos[NLCAP];                  // positions of the newlines ranked [base, base + NLCAP)
+    uint32_t rd[32];                        // reads of the round: start | length << 16 (0 = none)
     uint32_t seedq[SEEDQ];
-    unsigned long long candq[CANDQ];
-    uint16_t exh_reads[CAP];
-    uint16_t seed_reads[CAP];
-    uint16_t accq[ACCQ];
-    uint32_t warp_tot[GW];
-    int nrd, nseed, ncand, nacc, n_exh_reads, n_seed_reads;
-    int tile_cur, phase_in;
 };
 
 struct Smem {
-    uint32_t bm1[KVQ_BITMAP_WORDS];
-    uint32_t bm2[KVQ_BITMAP_WORDS];
+    uint8_t t1[KVQ_NKEYS];                  // T1 presence, one byte per key
+    uint32_t bm2[KVQ_BITMAP_WORDS];         // T2 presence, one bit per key
     uint32_t hist[KVQ_HIST];
     int longest;
-    GroupSmem g[G];
+    int pad[3];
+    WarpSmem w[NWARPS];
 };
 static_assert(sizeof(Smem) <= 232448, "shared memory budget (227 KB) exceeded");
 
 struct ThreadStats { unsigned long long records, bases, exh, cands; };
-
-__device__ __forceinline__ void group_sync(int gid)
-{
-    asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "r"(GT) : "memory");
-}
 
 __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t s)
 {
     return __funnelshift_r(lo, hi, s);
 }
 
-// bit7 of every byte of w that equals '\n' (other bits 0)
+// ---- byte planes: 4 bytes -> flags in bit 7 of every byte, gathered with dot products -------
+// bit7 of every byte of w that equals '\n'
 __device__ __forceinline__ uint32_t nl_bits(uint32_t w)
 {
-    uint32_t t = w ^ 0x0A0A0A0Au;
-    uint32_t z = ((t & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | t;     // bit7 set <=> byte != 0
-    return ~z & 0x80808080u;
+    uint32_t s = ((w ^ 0x0A0A0A0Au) & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;   // bit7: low 7 bits differ from '\n'
+    return ~(s | w) & 0x80808080u;
 }
-// bits 7,15,23,31 -> 4-bit value in the top nibble (no carries: all partial products distinct)
-__device__ __forceinline__ uint32_t top_nibble(uint32_t e) { return e * 0x00204081u; }
-
-// 32-bit newline mask of 32 bytes
-__device__ __forceinline__ uint32_t nl_mask32(uint4 a, uint4 b)
+// bit7 of every byte b of w with (signed char) b >= amin, amin >= 0.  cl = amin * 0x01010101
+__device__ __forceinline__ uint32_t ge_bits_pos(uint32_t w, uint32_t cl)
 {
-    uint32_t m = top_nibble(nl_bits(a.x)) >> 28;
-    m |= (top_nibble(nl_bits(a.y)) >> 24) & 0x000000F0u;
-    m |= (top_nibble(nl_bits(a.z)) >> 20) & 0x00000F00u;
-    m |= (top_nibble(nl_bits(a.w)) >> 16) & 0x0000F000u;
-    m |= (top_nibble(nl_bits(b.x)) >> 12) & 0x000F0000u;
-    m |= (top_nibble(nl_bits(b.y)) >> 8) & 0x00F00000u;
-    m |= (top_nibble(nl_bits(b.z)) >> 4) & 0x0F000000u;
-    m |= top_nibble(nl_bits(b.w)) & 0xF0000000u;
-    return m;
+    uint32_t t = (w | 0x80808080u) - cl;            // bit7: low 7 bits of b >= amin
+    return ~w & t & 0x80808080u;
 }
-
-// bit7 of every byte b of w with (signed char) b >= amin.  cl = (amin & 0x7f) * 0x01010101,
-// chi = amin is negative.  Compares (b ^ 0x80) >= (amin ^ 0x80) as unsigned bytes.
-__device__ __forceinline__ uint32_t ge_bits(uint32_t w, uint32_t cl, bool chi)
+// amin < 0: cl = (amin & 0x7f) * 0x01010101; bytes 0..127 always pass
+__device__ __forceinline__ uint32_t ge_bits_neg(uint32_t w, uint32_t cl)
 {
-    uint32_t t = (w | 0x80808080u) - cl;            // bit7: low 7 bits of b >= low 7 bits of amin
-    uint32_t uhi = ~w;                              // bit7 of (b ^ 0x80)
-    return (chi ? (uhi | t) : (uhi & t)) & 0x80808080u;
+    uint32_t t = (w | 0x80808080u) - cl;
+    return (~w | t) & 0x80808080u;
 }
-__device__ __forceinline__ uint32_t ge_mask32(uint4 a, uint4 b, uint32_t cl, bool chi)
+// 8 flag bytes (0x80 / 0x00) of two words -> 8 mask bits at [7, 15)
+__device__ __forceinline__ uint32_t gather2(uint32_t e0, uint32_t e1)
 {
-    uint32_t m = top_nibble(ge_bits(a.x, cl, chi)) >> 28;
-    m |= (top_nibble(ge_bits(a.y, cl, chi)) >> 24) & 0x000000F0u;
-    m |= (top_nibble(ge_bits(a.z, cl, chi)) >> 20) & 0x00000F00u;
-    m |= (top_nibble(ge_bits(a.w, cl, chi)) >> 16) & 0x0000F000u;
-    m |= (top_nibble(ge_bits(b.x, cl, chi)) >> 12) & 0x000F0000u;
-    m |= (top_nibble(ge_bits(b.y, cl, chi)) >> 8) & 0x00F00000u;
-    m |= (top_nibble(ge_bits(b.z, cl, chi)) >> 4) & 0x0F000000u;
-    m |= top_nibble(ge_bits(b.w, cl, chi)) & 0xF0000000u;
-    return m;
+    return __dp4a(e0, 0x08040201u, __dp4a(e1, 0x80402010u, 0u));
+}
+__device__ __forceinline__ uint32_t gather32(uint32_t p0, uint32_t p1, uint32_t p2, uint32_t p3)
+{
+    return (p0 >> 7) | (p1 << 1) | (p2 << 9) | (p3 << 17);
+}
+// 8 bases (two words) -> 16 bits of 2-bit codes, base 0 in the low bits.  Code = (byte >> 1) & 3.
+__device__ __forceinline__ uint32_t pack8(uint32_t w0, uint32_t w1)
+{
+    uint32_t d = __dp4a(w0 & 0x06060606u, 0x40100401u, 0u) + (__dp4a(w1 & 0x06060606u, 0x40100401u, 0u) << 8);
+    return d >> 1;
 }
 
-// 4 bases (bytes of w) -> 8 bits of 2-bit codes, base 0 in the low bits
-__device__ __forceinline__ uint32_t pack4(uint32_t w)
-{
-    return (((w >> 1) & 0x03030303u) * 0x01041040u) >> 24;
-}
-
-// 16 bases starting at base offset `b` of a packed array (needs word b/16+1 readable)
+// 16 bases starting at base offset `b` of a packed stream (needs word b/16+1 readable)
 __device__ __forceinline__ uint32_t extract16(const uint32_t *pk, int b)
 {
     int w = b >> 4;
@@ -164,122 +129,14 @@ __device__ __forceinline__ int diag_rule(int d, int rl, int sl, int O, int &ro, 
     return 0;
 }
 
-} // namespace
-
-namespace {
-
 struct TileCtx {
-    int64_t a0;          // batch offset of smem byte 0 (32-byte aligned)
-    int shift;           // smem coordinate of the first byte of the tile
-    int tile_end;        // smem coordinate one past the bytes owned by the tile
-    int reg_end;         // smem coordinate one past the staged region
+    int64_t a0;          // batch offset of plane coordinate 0 (32-byte aligned)
+    int shift;           // coordinate of the first byte of the tile
+    int tile_end;        // coordinate one past the bytes owned by the tile
+    int lim;             // coordinate one past the last byte of the segment (clamped to the planes)
     int first;           // first tile of its segment
-    int at_seg_end;      // the region reaches the end of the segment
     int64_t seg_end;     // batch offset of the segment end
 };
-
-// group-wide exclusive scan of one value per thread; returns the exclusive prefix, *total = sum
-__device__ __forceinline__ uint32_t group_exscan(uint32_t v, uint32_t *warp_tot, uint32_t *total, int gid, int gt)
-{
-    const int lane = gt & 31, wid = gt >> 5;
-    uint32_t inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += n;
-    }
-    if (lane == 31) warp_tot[wid] = inc;
-    group_sync(gid);
-    uint32_t base = 0, tot = 0;
-#pragma unroll
-    for (int w = 0; w < GW; w++) {
-        uint32_t t = warp_tot[w];
-        if (w < wid) base += t;
-        tot += t;
-    }
-    group_sync(gid);
-    *total = tot;
-    return base + inc - v;
-}
-
-// P1: stage the region in shared memory, build the newline bitmap + prefix counts.
-// Returns (to every thread of the group) the number of newlines in the whole region.
-__device__ uint32_t load_and_index(GroupSmem &s, const KvqBatch &b, const TileCtx &t, int gid, int gt)
-{
-    const int nwords = (t.reg_end + 31) >> 5;
-    const uint4 *src = reinterpret_cast<const uint4 *>(b.data + t.a0);
-    constexpr int NI = (NLW + 1 + GT - 1) / GT;
-    uint4 va[NI], vb[NI];
-#pragma unroll
-    for (int i = 0; i < NI; i++) {                  // every load of the tile in flight at once
-        const int w = gt + i * GT;
-        if (w < nwords) { va[i] = __ldg(src + 2 * w); vb[i] = __ldg(src + 2 * w + 1); }
-    }
-#pragma unroll
-    for (int i = 0; i < NI; i++) {
-        const int w = gt + i * GT;
-        if (w >= NLW + 1) break;
-        uint32_t m = 0;
-        if (w < nwords) {
-            s.tile[2 * w] = va[i]; s.tile[2 * w + 1] = vb[i];
-            m = nl_mask32(va[i], vb[i]);
-            const int lo = t.shift - (w << 5), hi = t.reg_end - (w << 5);
-            if (lo > 0) m &= lo >= 32 ? 0u : (0xFFFFFFFFu << lo);
-            if (hi < 32) m &= hi <= 0 ? 0u : ((1u << hi) - 1u);
-        }
-        s.nlmask[w] = m;
-    }
-    group_sync(gid);
-    const int w0 = gt * WPT;
-    uint32_t c[WPT]; uint32_t sum = 0;
-#pragma unroll
-    for (int i = 0; i < WPT; i++) {
-        c[i] = (w0 + i < NLW) ? __popc(s.nlmask[w0 + i]) : 0;
-        sum += c[i];
-    }
-    uint32_t total;
-    uint32_t ex = group_exscan(sum, s.warp_tot, &total, gid, gt);
-#pragma unroll
-    for (int i = 0; i < WPT; i++) {
-        if (w0 + i < NLW) s.nlpref[w0 + i] = ex;
-        ex += c[i];
-    }
-    if (gt == 0) s.nlpref[NLW] = total;
-    group_sync(gid);
-    return total;
-}
-
-// newlines at smem coordinates < pos
-__device__ __forceinline__ uint32_t nl_before(const GroupSmem &s, int pos)
-{
-    int w = pos >> 5;
-    uint32_t m = s.nlmask[w] & ((1u << (pos & 31)) - 1u);
-    return s.nlpref[w] + __popc(m);
-}
-
-// Decoupled look-back over the tiles of one segment: every tile publishes its newline count
-// (mod 4); a tile's phase is the sum over its predecessors.  Status word: bit3 = inclusive
-// prefix, bit2 = tile aggregate, bits 1:0 = value.  Tiles are claimed in stream order, so a
-// predecessor is always resident or finished.
-__device__ int resolve_phase(const KvqBatch &b, int tile, int first, int n_tile)
-{
-    volatile uint32_t *st = b.tile_status;
-    if (first) {
-        st[tile] = 8u | (uint32_t) (n_tile & 3);
-        return 0;
-    }
-    st[tile] = 4u | (uint32_t) (n_tile & 3);
-    int acc = 0;
-    for (int j = tile - 1;; j--) {
-        uint32_t v;
-        while ((v = st[j]) == 0) __nanosleep(20);
-        acc += (int) (v & 3);
-        if (v & 8u) break;
-    }
-    acc &= 3;
-    st[tile] = 8u | (uint32_t) ((acc + n_tile) & 3);
-    return acc;
-}
 
 // format-error key: smaller = earlier in the stream.  [63:22] stream offset of the record start,
 // [21] 0 = bad '@' / 1 = bad '+', [20:0] payload (the offending byte, or plus_pos - record_start)
@@ -299,90 +156,142 @@ __device__ __forceinline__ void push_long(const KvqOut &o, int64_t start, int64_
     }
 }
 
+} // namespace
+
+namespace {
+
+// ---- P1 ---------------------------------------------------------------------------------------
+struct Row { uint4 a, b; };
+
+__device__ __forceinline__ Row load_row(const KvqBatch &b, const TileCtx &t, int row, int lane)
+{
+    Row r;
+    const int w = row * 32 + lane;
+    if ((w << 5) < t.lim) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(b.data + t.a0) + 2 * w;
+        r.a = __ldg(src); r.b = __ldg(src + 1);
+    } else {
+        r.a = make_uint4(0, 0, 0, 0); r.b = r.a;
+    }
+    return r;
+}
+
+// Reduce one 32-byte word per lane to the three planes, rank its newlines (exclusive prefix of
+// the lane returned, running total in `nl_total`) and scatter the first NLCAP positions.
+template <bool NEG>
+__device__ __forceinline__ uint32_t reduce_row(WarpSmem &s, const TileCtx &t, const Row &r, int row, int lane,
+                                               uint32_t cl, uint32_t &nl_total, uint32_t &nl_owned)
+{
+    const int w = row * 32 + lane;
+    uint32_t nl = gather32(gather2(nl_bits(r.a.x), nl_bits(r.a.y)), gather2(nl_bits(r.a.z), nl_bits(r.a.w)),
+                           gather2(nl_bits(r.b.x), nl_bits(r.b.y)), gather2(nl_bits(r.b.z), nl_bits(r.b.w)));
+    uint32_t ge;
+    if (NEG)
+        ge = gather32(gather2(ge_bits_neg(r.a.x, cl), ge_bits_neg(r.a.y, cl)), gather2(ge_bits_neg(r.a.z, cl), ge_bits_neg(r.a.w, cl)),
+                      gather2(ge_bits_neg(r.b.x, cl), ge_bits_neg(r.b.y, cl)), gather2(ge_bits_neg(r.b.z, cl), ge_bits_neg(r.b.w, cl)));
+    else
+        ge = gather32(gather2(ge_bits_pos(r.a.x, cl), ge_bits_pos(r.a.y, cl)), gather2(ge_bits_pos(r.a.z, cl), ge_bits_pos(r.a.w, cl)),
+                      gather2(ge_bits_pos(r.b.x, cl), ge_bits_pos(r.b.y, cl)), gather2(ge_bits_pos(r.b.z, cl), ge_bits_pos(r.b.w, cl)));
+    uint2 pk;
+    pk.x = pack8(r.a.x, r.a.y) | (pack8(r.a.z, r.a.w) << 16);
+    pk.y = pack8(r.b.x, r.b.y) | (pack8(r.b.z, r.b.w) << 16);
+    // newlines outside [shift, lim) belong to other tiles' segments
+    const int lo = t.shift - (w << 5), hi = t.lim - (w << 5);
+    if (lo > 0) nl &= lo >= 32 ? 0u : (0xFFFFFFFFu << lo);
+    if (hi < 32) nl &= hi <= 0 ? 0u : ((1u << hi) - 1u);
+    s.nl[w] = nl; s.ge[w] = ge;
+    reinterpret_cast<uint2 *>(s.pk)[w] = pk;
+    const int own = t.tile_end - (w << 5);
+    nl_owned += __popc(own >= 32 ? nl : own <= 0 ? 0u : (nl & ((1u << own) - 1u)));
+    const uint32_t cnt = __popc(nl);
+    uint32_t inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    const uint32_t ex = nl_total + inc - cnt;
+    nl_total += __shfl_sync(0xffffffffu, inc, 31);
+    uint32_t m = nl, rank = ex;
+    while (m && rank < NLCAP) {
+        s.nlpos[rank++] = (uint16_t) ((w << 5) + __ffs(m) - 1);
+        m &= m - 1;
+    }
+    return ex;
+}
+
+// positions of the newlines ranked [base, base + NLCAP), from the plane (rounds after the first)
+__device__ __forceinline__ void rescatter(WarpSmem &s, const uint32_t *pre, int nrows, int base, int lane)
+{
+#pragma unroll
+    for (int row = 0; row < MAX_ROWS; row++) {
+        if (row >= nrows) break;
+        const int w = row * 32 + lane;
+        uint32_t m = s.nl[w];
+        int rank = (int) pre[row] - base;
+        while (m && rank < NLCAP) {
+            if (rank >= 0) s.nlpos[rank] = (uint16_t) ((w << 5) + __ffs(m) - 1);
+            rank++;
+            m &= m - 1;
+        }
+    }
+}
+
+// Decoupled look-back over the tiles of one segment, 32 predecessors per step.  Status word:
+// bit3 = inclusive prefix, bit2 = tile aggregate, bits 1:0 = newline count mod 4.  Tiles are
+// claimed in stream order, so a predecessor is always resident or finished.
+__device__ __forceinline__ int resolve_phase(const KvqBatch &b, int tile, int first, int n_tile, int lane)
+{
+    volatile uint32_t *st = b.tile_status;
+    if (first) {
+        if (lane == 0) st[tile] = 8u | (uint32_t) (n_tile & 3);
+        return 0;
+    }
+    if (lane == 0) st[tile] = 4u | (uint32_t) (n_tile & 3);
+    int acc = 0;
+    for (int j = tile - 1;;) {
+        const int i = j - lane;
+        const uint32_t v = i >= 0 ? st[i] : 8u;
+        const uint32_t incl = __ballot_sync(0xffffffffu, (v & 8u) != 0);
+        const uint32_t zero = __ballot_sync(0xffffffffu, v == 0);
+        const uint32_t upto = incl ? ((2u << (__ffs(incl) - 1)) - 1u) : 0xFFFFFFFFu;    // lanes up to the nearest prefix
+        if (zero & upto) { __nanosleep(40); continue; }
+        acc += __reduce_add_sync(0xffffffffu, ((upto >> lane) & 1u) ? (v & 3u) : 0u);
+        if (incl) break;
+        j -= 32;
+    }
+    acc &= 3;
+    if (lane == 0) st[tile] = 8u | (uint32_t) ((acc + n_tile) & 3);
+    return acc;
+}
+
+// ---- P2 ---------------------------------------------------------------------------------------
 // Phred trim of the quality line [qs, qe] (qe = its '\n'), workhorse.c:1055-1068: the first
 // longest run of bytes >= Amin that is closed by a byte < Amin at or before qe.
-__device__ __forceinline__ void phred_trim(const GroupSmem &s, int qs, int qe, uint32_t cl, bool chi,
-                                           int &rl, int &best)
+__device__ __forceinline__ void phred_trim(const WarpSmem &s, int qs, int qe, int &rl, int &best)
 {
     int runstart = qs;
     rl = 0; best = qs;
-    for (int gb = qs & ~31; gb <= qe; gb += 32) {
-        uint32_t bad = ~ge_mask32(s.tile[gb >> 4], s.tile[(gb >> 4) + 1], cl, chi);
+    for (int w = qs >> 5; w <= (qe >> 5); w++) {
+        uint32_t bad = ~s.ge[w];
+        const int gb = w << 5;
         if (gb < qs) bad &= 0xFFFFFFFFu << (qs - gb);
         if (qe - gb < 31) bad &= (2u << (qe - gb)) - 1u;
         while (bad) {
-            int z = gb + __ffs(bad) - 1;
+            const int z = gb + __ffs(bad) - 1;
             bad &= bad - 1;
-            int len = z - runstart;
+            const int len = z - runstart;
             if (len > rl) { rl = len; best = runstart; }
             runstart = z + 1;
         }
     }
 }
 
-// P2: one thread per record of the round.  Newline ranks are record-relative: newline
-// v = rank - off is line (v & 3) of record (v >> 2); the byte after newline 4k-1 starts record k.
-__device__ void process_records(GroupSmem &s, Smem &sh, const KvqBatch &b, const TileCtx &t,
-                                const KvqParams &p, const KvqOut &o, int off, int k0, int nrec,
-                                int kcomplete, int gt, ThreadStats &ts)
-{
-    if (gt >= nrec) return;
-    const uint8_t *tb = reinterpret_cast<const uint8_t *>(s.tile);
-    const int k = k0 + gt;
-    // locate the newline that precedes the record (or the record's first newline for k == 0
-    // of a segment's first tile) by binary search over the per-word prefix counts
-    const bool has_prev = !(t.first && k == 0);
-    const int r0 = 4 * k + off - (has_prev ? 1 : 0);        // rank of the first newline we need
-    int lo = 0, hi = NLW;                                   // largest w with nlpref[w] <= r0
-    while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if ((int) s.nlpref[mid] <= r0) lo = mid; else hi = mid;
-    }
-    int w = lo;
-    uint32_t m = s.nlmask[w];
-    for (int skip = r0 - (int) s.nlpref[w]; skip > 0; skip--) m &= m - 1;
-    // walk to the next newline of the bitmap
-    auto next_nl = [&]() -> int {
-        while (m == 0) m = s.nlmask[++w];
-        const int pos = (w << 5) + __ffs(m) - 1;
-        m &= m - 1;
-        return pos;
-    };
-    int S = t.shift;
-    if (has_prev) S = next_nl() + 1;
-    if (k > kcomplete) {
-        // the record runs past the staged region: a partial record at the end of the segment
-        // is dropped (workhorse.c:1033), anything else is a long record
-        if (!t.at_seg_end) push_long(o, t.a0 + S, t.seg_end, 0, 0);
-        return;
-    }
-    const int n0 = next_nl(), n1 = next_nl(), n2 = next_nl(), n3 = next_nl();
-    if (tb[S] != '@')
-        report_format_error(o, b.base_fpos + t.a0 + S, 0, tb[S]);
-    else if (tb[n1 + 1] != '+')
-        report_format_error(o, b.base_fpos + t.a0 + S, 1, (uint32_t) (n1 + 1 - S));
-    ts.records++;
-    ts.bases += (unsigned long long) (n1 - n0 - 1);
-    const uint32_t cl = (uint32_t) (p.amin & 0x7F) * 0x01010101u;
-    const bool chi = (p.amin & 0x80) != 0;
-    int rl, best;
-    phred_trim(s, n2 + 1, n3, cl, chi, rl, best);
-    if (rl < KVQ_HIST) atomicAdd(&sh.hist[rl], 1u);                 // add_rl, workhorse.c:394-402
-    atomicMax(&sh.longest, rl);
-    if (rl < p.minreadlength || rl == 0) return;                    // workhorse.c:1100
-    const int rd0 = n0 + 1 + (best - (n2 + 1));                     // workhorse.c:1070
-    if (rl > MAXRL_FAST) { push_long(o, t.a0 + rd0, t.seg_end, 1, rl); return; }
-    const int idx = atomicAdd(&s.nrd, 1);
-    Rd q; q.pos = (uint16_t) rd0; q.rl = (uint16_t) rl; q.poff = 0;
-    q.flags = (p.seed_ok && rl >= p.min_seed_rl) ? 1 : 0;
-    s.rd[idx] = q;
-}
-
 } // namespace
 
 namespace {
 
-// ---------------------------------------------------------------- emission / coverage --------
+// ---- emission / coverage ----------------------------------------------------------------------
 __device__ __forceinline__ int base_column(uint8_t c)
 {
     return c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : c == 'N' ? 4 : 5;
@@ -392,8 +301,8 @@ __device__ __forceinline__ uint8_t complement(uint8_t c)     // Sequence.pairs, 
     return c == 'A' ? 'T' : c == 'T' ? 'A' : c == 'C' ? 'G' : c == 'G' ? 'C' : c;
 }
 
-// add_hit (workhorse.c:408-443) + Coverage.apply_hit (kvarq/analyse.py:57-78).
-// `rd` points at the trimmed read's bytes (shared or global), `tp` at the template's bytes.
+// add_hit (workhorse.c:408-443) + Coverage.apply_hit (kvarq/analyse.py:57-78), one thread.
+// `rd` points at the trimmed read's bytes, `tp` at the template's bytes (both global).
 __device__ void emit_hit(const KvqTemplates &t, const KvqParams &p, const KvqOut &o, int seq, int d,
                          int ro, int to, int L, int rl, int64_t file_pos, const uint8_t *rd,
                          const uint8_t *tp, int copies, int rule)
@@ -435,171 +344,12 @@ __device__ void emit_hit(const KvqTemplates &t, const KvqParams &p, const KvqOut
     }
 }
 
-__device__ __forceinline__ int byte_mismatches(const uint8_t *a, const uint8_t *b, int n, int maxerr)
-{
-    int e = 0;
-    for (int j = 0; j < n; j++) {
-        e += (a[j] != b[j]);
-        if (e > maxerr) break;
-    }
-    return e;
-}
-
-// P3a: per-read offsets into the packed area and the probe work list (one exclusive scan)
-__device__ void layout_reads(GroupSmem &s, const KvqOut &o, const TileCtx &t, int gid, int gt, int nrd,
-                             uint32_t &totw, uint32_t &totq)
-{
-    uint32_t nw = 0, nq = 0; int rl = 0;
-    if (gt < nrd) {
-        rl = s.rd[gt].rl;
-        nw = (uint32_t) ((rl + 15) >> 4) + 1;
-        if (s.rd[gt].flags & 1) nq = (uint32_t) ((rl - KVQ_SEED_K + 16) >> 4);
-    }
-    uint32_t total;
-    const uint32_t ex = group_exscan(nw | (nq << 16), s.warp_tot, &total, gid, gt);
-    uint32_t pw = ex & 0xFFFFu, pq = ex >> 16;
-    if (gt < nrd) {
-        if (pw + nw > PACKW || pq + nq > QCAP) {
-            // does not fit this round's work lists: hand the read to the long-record kernel
-            push_long(o, t.a0 + s.rd[gt].pos, t.seg_end, 1, rl);
-            s.rd[gt].flags = 2;                                     // dead for the rest of the round
-        }
-        s.rd[gt].poff = (uint16_t) min(pw, (uint32_t) PACKW);
-        for (uint32_t j = 0; j < nw && pw + j < PACKW; j++) s.pitem[pw + j] = (uint8_t) gt;
-        for (uint32_t q = 0; q < nq && pq + q < QCAP; q++) s.qitem[pq + q] = (uint16_t) ((gt << 6) | q);
-    }
-    totw = min(total & 0xFFFFu, (uint32_t) PACKW);
-    totq = min(total >> 16, (uint32_t) QCAP);
-    group_sync(gid);
-}
-
-// P3b: 2-bit pack, one packed word (16 bases) per step
-__device__ void pack_reads(GroupSmem &s, int gt, int totw)
-{
-    const uint32_t *tw = reinterpret_cast<const uint32_t *>(s.tile);
-    for (int x = gt; x < totw; x += GT) {
-        const int r = s.pitem[x];
-        const Rd rd = s.rd[r];
-        if (rd.flags & 2) continue;                                 // dead read (prefix holes)
-        const int j = x - rd.poff;
-        const int nvalid = rd.rl - 16 * j;
-        uint32_t codes = 0;
-        if (nvalid > 0) {
-            const int pos = rd.pos + 16 * j;
-            const int a = pos >> 2; const uint32_t sh = (uint32_t) (pos & 3) << 3;
-            uint32_t w0 = tw[a], w1 = tw[a + 1], w2 = tw[a + 2], w3 = tw[a + 3], w4 = tw[a + 4];
-            codes = pack4(funnel_r(w0, w1, sh)) | (pack4(funnel_r(w1, w2, sh)) << 8)
-                  | (pack4(funnel_r(w2, w3, sh)) << 16) | (pack4(funnel_r(w3, w4, sh)) << 24);
-            if (nvalid < 16) codes &= (1u << (2 * nvalid)) - 1u;
-        }
-        s.packed[x] = codes;
-    }
-}
-
-__device__ __forceinline__ void push_seeds(GroupSmem &s, int r, int pbase, uint32_t mask, int kind)
-{
-    int cnt = __popc(mask);
-    int at = atomicAdd(&s.nseed, cnt);
-    while (mask) {
-        int j = __ffs(mask) - 1;
-        mask &= mask - 1;
-        if (at < SEEDQ) s.seedq[at] = ((uint32_t) r << 16) | ((uint32_t) (pbase + j) << 1) | (uint32_t) kind;
-        at++;
-    }
-}
-
-// P4: probes.  T1: every read offset, 16 offsets per work item.  T2: a few fixed offsets per read.
-__device__ void probe_reads(GroupSmem &s, const Smem &sh, const KvqParams &p, const KvqTemplates &t,
-                            int gt, int nrd, int totq)
-{
-    for (int i = gt; i < totq; i += GT) {
-        const int it = s.qitem[i];
-        const int r = it >> 6, q = it & 63;
-        const Rd rd = s.rd[r];
-        if (rd.flags & 2) continue;
-        const int npos = rd.rl - KVQ_SEED_K + 1 - 16 * q;           // probe offsets left from 16q on
-        const uint32_t *pk = s.packed + rd.poff + q;
-        const uint32_t lo = pk[0], hi = pk[1];
-        uint32_t mask = 0;
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-            uint32_t key = funnel_r(lo, hi, 2 * j) & 0xFFFFu;
-            mask |= ((sh.bm1[key >> 5] >> (key & 31)) & 1u) << j;
-        }
-        if (npos < 16) mask &= (1u << npos) - 1u;
-        if (mask) push_seeds(s, r, 16 * q, mask, 0);
-    }
-    // T2: a few fixed offsets per read (whole-read / head / tail pieces), table per read length
-    const int n2 = p.n2max;
-    for (int x = gt; x < nrd * n2; x += GT) {
-        const int r = (int) (((uint32_t) x * p.div_magic_n2) >> 16), i = x - r * n2;
-        const Rd rd = s.rd[r];
-        if ((rd.flags & 3) != 1) continue;
-        const int pos = __ldg(t.p2_tab + rd.rl * KVQ_P2W + i);
-        if (pos < 0) continue;
-        const uint32_t key = extract16(s.packed + rd.poff, pos) & 0xFFFFu;
-        if ((sh.bm2[key >> 5] >> (key & 31)) & 1u) push_seeds(s, r, pos, 1u, 1);
-    }
-}
-
-// P5: walk the bucket of every seed and queue the diagonals the reference would evaluate
-__device__ void expand_seeds(GroupSmem &s, const KvqParams &p, const KvqTemplates &t, int gt)
-{
-    const int nseed = s.nseed;
-    for (int i = gt; i < nseed; i += GT) {
-        const uint32_t sd = s.seedq[i];
-        const int r = sd >> 16, pos = (sd >> 1) & 0x7FFF, kind = sd & 1;
-        const int rl = s.rd[r].rl;
-        const uint32_t key = extract16(s.packed + s.rd[r].poff, pos) & 0xFFFFu;
-        const uint32_t *off = kind ? t.t2_off : t.t1_off;
-        const uint2 *ent = kind ? t.t2_ent : t.t1_ent;
-        const uint32_t e0 = __ldg(off + key), e1 = __ldg(off + key + 1);
-        for (uint32_t e = e0; e < e1; e++) {
-            const uint2 en = __ldg(ent + e);
-            const int sq = (int) en.x, toff = (int) en.y;
-            const int d = toff - pos;
-            int ro, to, L, rule;
-            if (!diag_rule(d, rl, __ldg(t.len + sq), p.minoverlap, ro, to, L, rule)) continue;
-            int at = atomicAdd(&s.ncand, 1);
-            if (at < CANDQ)
-                s.candq[at] = (unsigned long long) r | ((unsigned long long) sq << 8)
-                            | ((unsigned long long) (d + 32768) << 32)
-                            | ((unsigned long long) pos << 48) | ((unsigned long long) kind << 58);
-        }
-    }
-}
-
-// Is (kind, pos) the first seed, in the fixed order T1 pieces then T2 offsets, that fires on
-// diagonal d of (read, seq)?  Every firing seed queues the same diagonal; only this one emits.
-__device__ bool canonical_seed(const KvqParams &p, const KvqTemplates &t, const uint32_t *rpk, const uint32_t *tpk,
-                               int rl, int sl, int d, int kind, int pos)
-{
-    for (int j = 0; j < p.npieces; j++) {
-        const int toff = j * sl / p.npieces;
-        const int pj = toff - d;
-        if (pj < 0 || pj > rl - KVQ_SEED_K) continue;
-        if (((extract16(rpk, pj) ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
-            return kind == 0 && pos == pj;
-    }
-    const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
-    for (int i = 0; i < p.n2max; i++) {
-        const int pp = __ldg(p2 + i);
-        if (pp < 0) continue;
-        const int toff = pp + d;
-        if (toff < 0 || toff > sl - KVQ_SEED_K) continue;
-        if (((extract16(rpk, pp) ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
-            return kind == 1 && pos == pp;
-    }
-    return false;
-}
-
-// Warp-cooperative add_hit + Coverage.apply_hit: lane 0 reserves the output slots, all lanes copy
-// the hitseq bytes and update the coverage arrays.
+// Warp-cooperative variant: lane 0 reserves the output slots, all lanes copy the hitseq bytes
+// and update the coverage arrays.
 __device__ void emit_hit_warp(const KvqTemplates &t, const KvqParams &p, const KvqOut &o, int seq, int d,
-                              int ro, int to, int L, int rl, int64_t file_pos, const uint8_t *rd,
-                              const uint8_t *tp, int copies, int rule)
+                              int ro, int to, int L, int rl, int sl, int64_t file_pos, const uint8_t *rd,
+                              const uint8_t *tp, int copies, int rule, int lane)
 {
-    const int lane = threadIdx.x & 31;
     unsigned long long slot = 0, boff = 0;
     if (lane == 0) {
         if (p.accumulate) {
@@ -627,7 +377,6 @@ __device__ void emit_hit_warp(const KvqTemplates &t, const KvqParams &p, const K
     if (t.nplus > 0 && p.accumulate) {
         const bool plus = seq < t.nplus;
         const int tpl = plus ? seq : seq - t.nplus;
-        const int sl = __ldg(t.len + seq);
         const unsigned long long cb = __ldg(t.cov_off + tpl);
         for (int j = lane; j < L; j += 32) {
             const int sidx = to + j;
@@ -641,68 +390,20 @@ __device__ void emit_hit_warp(const KvqTemplates &t, const KvqParams &p, const K
     }
 }
 
-// P6a: one thread per candidate diagonal: Hamming distance in code space (XOR/popc on packed
-// words), a lower bound of the byte distance.  Survivors are queued for P6b.
-__device__ void filter_candidates(GroupSmem &s, const KvqParams &p, const KvqTemplates &t, int gt)
+__device__ __forceinline__ int byte_mismatches(const uint8_t *a, const uint8_t *b, int n, int maxerr)
 {
-    const int ncand = s.ncand;
-    for (int i = gt; i < ncand; i += GT) {
-        const unsigned long long c = s.candq[i];
-        const int r = (int) (c & 0xFF), sq = (int) ((c >> 8) & 0xFFFFFF);
-        const int d = (int) ((c >> 32) & 0xFFFF) - 32768;
-        const Rd rd = s.rd[r];
-        const int rl = rd.rl, sl = __ldg(t.len + sq);
-        int ro, to, L, rule;
-        diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule);
-        const uint32_t *rpk = s.packed + rd.poff;
-        const uint32_t *tpk = t.packed + __ldg(t.packed_off + sq);
-        int e = 0;
-        for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
-            uint32_t x = extract16(rpk, ro + j) ^ extract16_g(tpk, to + j);
-            uint32_t m = (x | (x >> 1)) & 0x55555555u;
-            if (L - j < 16) m &= (1u << (2 * (L - j))) - 1u;
-            e += __popc(m);
-        }
-        if (e > p.maxerrors) continue;
-        const int at = atomicAdd(&s.nacc, 1);
-        if (at < ACCQ) s.accq[at] = (uint16_t) i;
+    int e = 0;
+    for (int j = 0; j < n; j++) {
+        e += (a[j] != b[j]);
+        if (e > maxerr) break;
     }
+    return e;
 }
 
-// P6b: one warp per survivor: byte-exact confirm, canonical-seed dedupe, emission
-__device__ void confirm_candidates(GroupSmem &s, const KvqBatch &b, const TileCtx &tc, const KvqParams &p,
-                                   const KvqTemplates &t, const KvqOut &o, int gt)
-{
-    const uint8_t *tb = reinterpret_cast<const uint8_t *>(s.tile);
-    const int lane = gt & 31;
-    const int nacc = s.nacc < ACCQ ? s.nacc : ACCQ;
-    for (int a = gt >> 5; a < nacc; a += GW) {
-        const unsigned long long c = s.candq[s.accq[a]];
-        const int r = (int) (c & 0xFF), sq = (int) ((c >> 8) & 0xFFFFFF);
-        const int d = (int) ((c >> 32) & 0xFFFF) - 32768;
-        const int pos = (int) ((c >> 48) & 0x3FF), kind = (int) ((c >> 58) & 1);
-        const Rd rd = s.rd[r];
-        const int rl = rd.rl, sl = __ldg(t.len + sq);
-        int ro, to, L, rule;
-        const int copies = diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule);
-        const uint8_t *rdp = tb + rd.pos;
-        const uint8_t *tp = t.bytes + __ldg(t.byte_off + sq);
-        int e = 0;
-        for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
-        e = __reduce_add_sync(0xffffffffu, e);
-        if (e > p.maxerrors) continue;
-        const uint32_t *rpk = s.packed + rd.poff;
-        const uint32_t *tpk = t.packed + __ldg(t.packed_off + sq);
-        if (!canonical_seed(p, t, rpk, tpk, rl, sl, d, kind, pos)) continue;      // warp-uniform
-        emit_hit_warp(t, p, o, sq, d, ro, to, L, rl, b.base_fpos + tc.a0 + rd.pos, rdp, tp, copies, rule);
-    }
-}
-
-// Exhaustive matcher: one warp per (read, seq) pair, lanes over all diagonals.
+// Exhaustive matcher: one warp per (read, seq) pair, lanes over all diagonals, raw bytes.
 __device__ void exhaustive_pair(const KvqParams &p, const KvqTemplates &t, const KvqOut &o,
-                                const uint8_t *rd, int rl, int64_t file_pos, int sq)
+                                const uint8_t *rd, int rl, int64_t file_pos, int sq, int lane)
 {
-    const int lane = threadIdx.x & 31;
     const int sl = __ldg(t.len + sq);
     const uint8_t *tp = t.bytes + __ldg(t.byte_off + sq);
     for (int d = -(rl - 1) + lane; d <= sl - 1; d += 32) {
@@ -714,93 +415,302 @@ __device__ void exhaustive_pair(const KvqParams &p, const KvqTemplates &t, const
     }
 }
 
+// Is (kind, pos) the first seed, in the fixed order T1 pieces then T2 offsets, that fires on
+// diagonal d of (read, seq)?  Every firing seed reaches the same diagonal; only this one emits.
+// rpk = code plane, rb = base offset of the read in it.
+__device__ bool canonical_seed(const KvqParams &p, const KvqTemplates &t, const uint32_t *rpk, int rb,
+                               const uint32_t *tpk, int rl, int sl, int d, int kind, int pos)
+{
+    for (int j = 0; j < p.npieces; j++) {
+        const int toff = j * sl / p.npieces;
+        const int pj = toff - d;
+        if (pj < 0 || pj > rl - KVQ_SEED_K) continue;
+        if (((extract16(rpk, rb + pj) ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
+            return kind == 0 && pos == pj;
+    }
+    const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
+    for (int i = 0; i < p.n2max; i++) {
+        const int pp = __ldg(p2 + i);
+        if (pp < 0) continue;
+        const int toff = pp + d;
+        if (toff < 0 || toff > sl - KVQ_SEED_K) continue;
+        if (((extract16(rpk, rb + pp) ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
+            return kind == 1 && pos == pp;
+    }
+    return false;
+}
+
 } // namespace
 
 namespace {
 
-// One round = up to CAP owned records of the current tile.
-__device__ void run_round(GroupSmem &s, Smem &sh, const KvqBatch &b, const TileCtx &tc, const KvqParams &p,
-                          const KvqTemplates &t, const KvqOut &o, int off, int k0, int nrec, int kcomplete,
-                          int gid, int gt, ThreadStats &ts)
+struct Ctx {
+    const KvqBatch &b; const KvqTemplates &t; const KvqParams &p; const KvqOut &o; const TileCtx &tc;
+};
+
+// ---- P4: seeds -> bucket entries -> code-space verify -> confirm + emit ------------------------
+// Seeds s.seedq[base, base + n), one per lane.  Seed = read | pos << 5 | kind << 15.
+__device__ void drain_seeds(WarpSmem &s, const Ctx &c, int base, int n, int lane, ThreadStats &ts)
 {
-    if (gt == 0) { s.nrd = 0; s.nseed = 0; s.ncand = 0; s.nacc = 0; s.n_exh_reads = 0; s.n_seed_reads = 0; }
-    group_sync(gid);
-    process_records(s, sh, b, tc, p, o, off, k0, nrec, kcomplete, gt, ts);
-    group_sync(gid);
-    const int nrd = s.nrd;
-    group_sync(gid);                                // everyone has read nrd before it is reset
-    if (nrd == 0) return;                           // uniform
-    const uint8_t *tb = reinterpret_cast<const uint8_t *>(s.tile);
-    bool seeded = p.seed_ok && t.n_exh < t.nseqs;
-    if (seeded) {
-        uint32_t totw, totq;
-        layout_reads(s, o, tc, gid, gt, nrd, totw, totq);
-        pack_reads(s, gt, (int) totw);
-        group_sync(gid);
-        probe_reads(s, sh, p, t, gt, nrd, (int) totq);
-        group_sync(gid);
-        if (s.nseed > SEEDQ) seeded = false;        // uniform: queue overflow -> exhaustive round
-        if (seeded) {
-            expand_seeds(s, p, t, gt);
-            group_sync(gid);
-            if (s.ncand > CANDQ) seeded = false;
+    const KvqTemplates &t = c.t; const KvqParams &p = c.p;
+    uint32_t e0 = 0, e1 = 0;
+    int pos = 0, kind = 0, rd0 = 0, rl = 0;
+    if (lane < n) {
+        const uint32_t sd = s.seedq[base + lane];
+        const uint32_t rdv = s.rd[sd & 31];
+        pos = (int) ((sd >> 5) & 1023); kind = (int) (sd >> 15);
+        rd0 = (int) (rdv & 0xFFFFu); rl = (int) (rdv >> 16);
+        const uint32_t key = extract16(s.pk, rd0 + pos) & 0xFFFFu;
+        const uint32_t *off = kind ? t.t2_off : t.t1_off;
+        e0 = __ldg(off + key); e1 = __ldg(off + key + 1);
+    }
+    __syncwarp();
+    const uint4 *ent = kind ? t.t2_ent : t.t1_ent;
+    for (;;) {
+        const bool has = e0 < e1;
+        if (!__any_sync(0xffffffffu, has)) break;
+        bool surv = false;
+        uint4 en = make_uint4(0, 0, 0, 0);
+        int d = 0;
+        if (has) {
+            en = __ldg(ent + e0); e0++;
+            const int sl = (int) (en.y >> 16);
+            d = (int) (en.y & 0xFFFFu) - pos;
+            int ro, to, L, rule;
+            if (diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule)) {
+                const uint32_t *tpk = t.packed + en.z;
+                int e = 0;
+                for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
+                    uint32_t x = extract16(s.pk, rd0 + ro + j) ^ extract16_g(tpk, to + j);
+                    uint32_t m = (x | (x >> 1)) & 0x55555555u;
+                    if (L - j < 16) m &= (1u << (2 * (L - j))) - 1u;
+                    e += __popc(m);
+                }
+                surv = e <= p.maxerrors;
+            }
+            ts.cands++;
         }
-        if (seeded) {
-            filter_candidates(s, p, t, gt);
-            group_sync(gid);
-            if (s.nacc > ACCQ) seeded = false;      // uniform: too many survivors -> exhaustive round
-        }
-        if (seeded) {
-            if (gt == 0) ts.cands += (unsigned long long) s.ncand;
-            confirm_candidates(s, b, tc, p, t, o, gt);
-        } else if (gt == 0) {
-            atomicAdd(&o.ctr->overflow_rounds, 1u);
+        uint32_t m = __ballot_sync(0xffffffffu, surv);
+        while (m) {                                 // warp-wide: byte-exact confirm, dedupe, emit
+            const int src = __ffs(m) - 1;
+            m &= m - 1;
+            const int sq = (int) __shfl_sync(0xffffffffu, en.x, src);
+            const uint32_t y = __shfl_sync(0xffffffffu, en.y, src);
+            const uint32_t poff = __shfl_sync(0xffffffffu, en.z, src);
+            const uint32_t boff = __shfl_sync(0xffffffffu, en.w, src);
+            const int dd = __shfl_sync(0xffffffffu, d, src);
+            const int bpos = __shfl_sync(0xffffffffu, pos, src), bkind = __shfl_sync(0xffffffffu, kind, src);
+            const int brd0 = __shfl_sync(0xffffffffu, rd0, src), brl = __shfl_sync(0xffffffffu, rl, src);
+            const int sl = (int) (y >> 16);
+            int ro, to, L, rule;
+            const int copies = diag_rule(dd, brl, sl, p.minoverlap, ro, to, L, rule);
+            const uint8_t *rdp = c.b.data + c.tc.a0 + brd0;
+            const uint8_t *tp = t.bytes + boff;
+            int e = 0;
+            for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
+            e = __reduce_add_sync(0xffffffffu, e);
+            if (e > p.maxerrors) continue;
+            if (!canonical_seed(p, t, s.pk, brd0, t.packed + poff, brl, sl, dd, bkind, bpos)) continue;
+            emit_hit_warp(t, p, c.o, sq, dd, ro, to, L, brl, sl, c.b.base_fpos + c.tc.a0 + brd0, rdp, tp,
+                          copies, rule, lane);
         }
     }
-    // split the reads of the round: seeded ones still owe the non-seedable templates
-    if (gt < nrd) {
-        const int fl = s.rd[gt].flags;
-        if (!(fl & 2)) {
-            if (seeded && (fl & 1)) s.seed_reads[atomicAdd(&s.n_seed_reads, 1)] = (uint16_t) gt;
-            else s.exh_reads[atomicAdd(&s.n_exh_reads, 1)] = (uint16_t) gt;
-        }
-    }
-    group_sync(gid);
-    const int wid = gt >> 5;
-    const int ne = s.n_exh_reads, ns = s.n_seed_reads;
-    if (gt == 0) ts.exh += (unsigned long long) ne;
-    for (int pair = wid; pair < ne * t.nseqs; pair += GW) {
-        const int r = s.exh_reads[pair / t.nseqs], sq = pair % t.nseqs;
-        exhaustive_pair(p, t, o, tb + s.rd[r].pos, s.rd[r].rl, b.base_fpos + tc.a0 + s.rd[r].pos, sq);
-    }
-    if (t.n_exh > 0)
-        for (int pair = wid; pair < ns * t.n_exh; pair += GW) {
-            const int r = s.seed_reads[pair / t.n_exh], sq = __ldg(t.exh_list + pair % t.n_exh);
-            exhaustive_pair(p, t, o, tb + s.rd[r].pos, s.rd[r].rl, b.base_fpos + tc.a0 + s.rd[r].pos, sq);
-        }
 }
 
+// Push the set bits of every lane's `hits` (bit j = read offset posbase + j) on the seed stack;
+// whenever 32 seeds are waiting they are drained with all lanes busy.
+__device__ __forceinline__ void push_seeds(WarpSmem &s, const Ctx &c, int &qn, uint32_t hits, uint32_t tag,
+                                           int posbase, int lane, ThreadStats &ts)
+{
+    for (;;) {
+        const uint32_t any = __ballot_sync(0xffffffffu, hits != 0);
+        if (!any) break;
+        if (hits) {
+            const int j = __ffs(hits) - 1;
+            hits &= hits - 1;
+            s.seedq[qn + __popc(any & ((1u << lane) - 1u))] = tag | ((uint32_t) (posbase + j) << 5);
+        }
+        qn += __popc(any);
+        __syncwarp();
+        if (qn >= 32) {
+            drain_seeds(s, c, qn - 32, 32, lane, ts);
+            qn -= 32;
+        }
+    }
+}
+
+// ---- P3: T1 probes of one 32-byte word: bit j <=> the 8-mer at base offset j is a template piece
+__device__ __forceinline__ uint32_t probe_word(const uint8_t *t1, uint32_t x0, uint32_t x1, uint32_t x2)
+{
+    uint32_t hits = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const uint32_t sa = j ? funnel_r(x0, x1, 2 * j) : x0;       // bases j .. j+15
+        const uint32_t sb = j ? funnel_r(x1, x2, 2 * j) : x1;       // bases 16+j .. 31+j
+        hits += (uint32_t) t1[sa & 0xFFFFu] << j;
+        hits += (uint32_t) t1[sa >> 16] << (j + 8);
+        hits += (uint32_t) t1[sb & 0xFFFFu] << (j + 16);
+        hits += (uint32_t) t1[sb >> 16] << (j + 24);
+    }
+    return hits;
+}
+
+} // namespace
+
+namespace {
+
+// ---- P2: one lane per record of the round.  Newline ranks are record-relative: newline
+// v = rank - off is line (v & 3) of record (v >> 2); the byte after newline 4k-1 starts record k.
+// Returns start | length << 16 of the lane's trimmed read if it is to be matched here, else 0.
+__device__ __forceinline__ uint32_t parse_record(WarpSmem &s, Smem &sh, const Ctx &c, int k, int idx, bool act,
+                                                 int n_all, int off, bool at_seg_end, int lane, ThreadStats &ts)
+{
+    const TileCtx &tc = c.tc; const KvqParams &p = c.p;
+    int S = tc.shift, rl = -1;
+    uint32_t rdv = 0;
+    if (act) {
+        if (!(tc.first && k == 0)) S = (int) s.nlpos[idx] + 1;
+        if (4 * k + 3 + off >= n_all) {
+            // the record runs past the staged region: a partial record at the end of the segment
+            // is dropped (workhorse.c:1033), anything else is a long record
+            if (!at_seg_end) push_long(c.o, tc.a0 + S, tc.seg_end, 0, 0);
+            act = false;
+        }
+    }
+    if (act) {
+        const int n0 = s.nlpos[idx + 1], n1 = s.nlpos[idx + 2], n2 = s.nlpos[idx + 3], n3 = s.nlpos[idx + 4];
+        const uint8_t *rec = c.b.data + tc.a0;
+        const uint8_t c0 = __ldg(rec + S), c2 = __ldg(rec + n1 + 1);
+        if (c0 != '@')
+            report_format_error(c.o, c.b.base_fpos + tc.a0 + S, 0, c0);
+        else if (c2 != '+')
+            report_format_error(c.o, c.b.base_fpos + tc.a0 + S, 1, (uint32_t) (n1 + 1 - S));
+        ts.records++;
+        ts.bases += (unsigned long long) (n1 - n0 - 1);
+        int best;
+        phred_trim(s, n2 + 1, n3, rl, best);
+        if (rl >= p.minreadlength && rl > 0) {                          // workhorse.c:1100
+            const int rd0 = n0 + 1 + (best - (n2 + 1));                 // workhorse.c:1070
+            if (rl > MAXRL_FAST) push_long(c.o, tc.a0 + rd0, tc.seg_end, 1, rl);
+            else rdv = (uint32_t) rd0 | ((uint32_t) rl << 16);
+        }
+    }
+    // add_rl (workhorse.c:394-402); reads of one round mostly share their length
+    const uint32_t m = __ballot_sync(0xffffffffu, rl >= 0);
+    if (m) {
+        const int leader = __ffs(m) - 1;
+        const int rl0 = __shfl_sync(0xffffffffu, rl, leader);
+        if (__ballot_sync(0xffffffffu, rl == rl0) == m) {
+            if (lane == leader) {
+                if (rl0 < KVQ_HIST) atomicAdd(&sh.hist[rl0], (uint32_t) __popc(m));
+                atomicMax(&sh.longest, rl0);
+            }
+        } else if (rl >= 0) {
+            if (rl < KVQ_HIST) atomicAdd(&sh.hist[rl], 1u);
+            atomicMax(&sh.longest, rl);
+        }
+    }
+    return rdv;
+}
+
+// One round = up to 32 owned records of the tile, one per lane.
+__device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown, int base, int n_all, int off,
+                          bool at_seg_end, int lane, ThreadStats &ts)
+{
+    const KvqTemplates &t = c.t; const KvqParams &p = c.p; const TileCtx &tc = c.tc;
+    const int k = k0 + lane;
+    const uint32_t rdv = parse_record(s, sh, c, k, 4 * k + off - 1 - base, k < nown, n_all, off, at_seg_end, lane, ts);
+    s.rd[lane] = rdv;
+    __syncwarp();
+    if (!__any_sync(0xffffffffu, rdv != 0)) return;
+    const int rd0 = (int) (rdv & 0xFFFFu), rl = (int) (rdv >> 16);
+    const bool seeded = p.seed_ok && t.n_exh < t.nseqs;
+    const bool seedable = seeded && rdv != 0 && rl >= p.min_seed_rl;
+    if (seeded) {
+        int qn = 0;
+        // T1: every read offset rd0 .. rd0 + rl - 8, one 32-byte word of the code plane per step
+        const int w0 = rd0 >> 5, plast = rd0 + rl - KVQ_SEED_K;
+        const int nw = seedable ? (plast >> 5) - w0 + 1 : 0;
+        const int maxnw = __reduce_max_sync(0xffffffffu, nw);
+        for (int q = 0; q < maxnw; q++) {
+            uint32_t hits = 0;
+            const int w = w0 + q;
+            if (q < nw) {
+                const uint2 x = reinterpret_cast<const uint2 *>(s.pk)[w];
+                hits = probe_word(sh.t1, x.x, x.y, s.pk[2 * w + 2]);
+                const int lo = rd0 - (w << 5), hi = plast - (w << 5);
+                if (lo > 0) hits &= 0xFFFFFFFFu << lo;
+                if (hi < 31) hits &= (2u << hi) - 1u;
+            }
+            push_seeds(s, c, qn, hits, (uint32_t) lane, (w << 5) - rd0, lane, ts);
+        }
+        // T2: a few fixed offsets per read (whole-read / head / tail pieces), table per read length
+        for (int i = 0; i < p.n2max; i++) {
+            uint32_t hit = 0; int pos = 0;
+            if (seedable) {
+                pos = __ldg(t.p2_tab + rl * KVQ_P2W + i);
+                if (pos >= 0) {
+                    const uint32_t key = extract16(s.pk, rd0 + pos) & 0xFFFFu;
+                    hit = (sh.bm2[key >> 5] >> (key & 31)) & 1u;
+                }
+            }
+            push_seeds(s, c, qn, hit, (uint32_t) lane | (1u << 15), pos, lane, ts);
+        }
+        if (qn) drain_seeds(s, c, 0, qn, lane, ts);
+    }
+    // exhaustive matcher: reads the seed scheme does not cover against every template, the
+    // others against the templates it does not cover
+    const uint8_t *data = c.b.data + tc.a0;
+    uint32_t m = __ballot_sync(0xffffffffu, rdv != 0 && !seedable);
+    ts.exh += (unsigned long long) (rdv != 0 && !seedable);
+    while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1;
+        const int brd0 = __shfl_sync(0xffffffffu, rd0, src), brl = __shfl_sync(0xffffffffu, rl, src);
+        for (int sq = 0; sq < t.nseqs; sq++)
+            exhaustive_pair(p, t, c.o, data + brd0, brl, c.b.base_fpos + tc.a0 + brd0, sq, lane);
+    }
+    if (t.n_exh > 0) {
+        m = __ballot_sync(0xffffffffu, seedable);
+        while (m) {
+            const int src = __ffs(m) - 1;
+            m &= m - 1;
+            const int brd0 = __shfl_sync(0xffffffffu, rd0, src), brl = __shfl_sync(0xffffffffu, rl, src);
+            for (int i = 0; i < t.n_exh; i++)
+                exhaustive_pair(p, t, c.o, data + brd0, brl, c.b.base_fpos + tc.a0 + brd0, __ldg(t.exh_list + i), lane);
+        }
+    }
+}
+
+} // namespace
+
+namespace {
+
+template <bool NEG>
 __global__ void __launch_bounds__(THREADS, 1)
 kvq_scan_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem &sh = *reinterpret_cast<Smem *>(smem_raw);
-    const int gid = threadIdx.x / GT, gt = threadIdx.x % GT;
-    GroupSmem &s = sh.g[gid];
+    const int lane = threadIdx.x & 31;
+    WarpSmem &s = sh.w[threadIdx.x >> 5];
 
-    for (int i = threadIdx.x; i < KVQ_BITMAP_WORDS; i += THREADS) {
-        sh.bm1[i] = __ldg(t.t1_bitmap + i);
-        sh.bm2[i] = __ldg(t.t2_bitmap + i);
+    {   // tables: T1 presence bytes, T2 bitmap
+        const uint4 *src = reinterpret_cast<const uint4 *>(t.t1_present);
+        uint4 *dst = reinterpret_cast<uint4 *>(sh.t1);
+        for (int i = threadIdx.x; i < KVQ_NKEYS / 16; i += THREADS) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < KVQ_BITMAP_WORDS; i += THREADS) sh.bm2[i] = __ldg(t.t2_bitmap + i);
+        for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS) sh.hist[i] = 0;
+        if (threadIdx.x == 0) sh.longest = -1;
     }
-    for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS) sh.hist[i] = 0;
-    if (threadIdx.x == 0) sh.longest = -1;
     __syncthreads();
     ThreadStats ts{0, 0, 0, 0};
+    const uint32_t cl = (uint32_t) (p.amin & 0x7F) * 0x01010101u;
 
     for (;;) {
-        if (gt == 0) s.tile_cur = (int) atomicAdd(&o.ctr->tile_next, 1u);
-        group_sync(gid);
-        const int tile = s.tile_cur;
+        int tile = 0;
+        if (lane == 0) tile = (int) atomicAdd(&o.ctr->tile_next, 1u);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
         if (tile >= b.ntiles) break;
         const int seg = __ldg(b.tile_seg + tile);
         const int64_t t0 = __ldg(b.tile_off + tile);
@@ -808,30 +718,58 @@ kvq_scan_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
         TileCtx tc;
         tc.a0 = t0 & ~(int64_t) 31;
         tc.shift = (int) (t0 - tc.a0);
-        const int64_t t1 = t0 + TILE < seg_end ? t0 + TILE : seg_end;
-        const int64_t g1 = t1 + MARGIN < seg_end ? t1 + MARGIN : seg_end;
+        const int64_t t1 = t0 + KVQ_TILE < seg_end ? t0 + KVQ_TILE : seg_end;
         tc.tile_end = (int) (t1 - tc.a0);
-        tc.reg_end = (int) (g1 - tc.a0);
+        const int64_t lim = seg_end - tc.a0;
+        tc.lim = lim < (int64_t) MAX_ROWS * KVQ_ROW ? (int) lim : MAX_ROWS * KVQ_ROW;
         tc.first = (t0 == seg_beg);
-        tc.at_seg_end = (g1 == seg_end);
         tc.seg_end = seg_end;
-        const int n_all = (int) load_and_index(s, b, tc, gid, gt);
-        const int n_tile = (int) nl_before(s, tc.tile_end);
-        if (gt == 0) s.phase_in = resolve_phase(b, tile, tc.first, n_tile);
-        group_sync(gid);
-        const int phase = s.phase_in;
-        // newline rank -> record-relative numbering (see process_records)
+        const Ctx c{b, t, p, o, tc};
+
+        // P1: rows 0 .. OWN_ROWS (the tile plus one row of spill), two rows of loads in flight
+        uint32_t pre[MAX_ROWS];
+        uint32_t n_all = 0, n_own = 0;
+        {
+            Row r0 = load_row(b, tc, 0, lane), r1 = load_row(b, tc, 1, lane);
+#pragma unroll
+            for (int row = 0; row <= OWN_ROWS; row++) {
+                Row r2;
+                if (row + 2 <= OWN_ROWS) r2 = load_row(b, tc, row + 2, lane);
+                pre[row] = reduce_row<NEG>(s, tc, r0, row, lane, cl, n_all, n_own);
+                r0 = r1; r1 = r2;
+            }
+        }
+        const int n_tile = (int) __reduce_add_sync(0xffffffffu, n_own);
+        const int phase = resolve_phase(b, tile, tc.first, n_tile, lane);
+        // newline rank -> record-relative numbering (see parse_record)
         const int off = tc.first ? 0 : ((3 - phase) & 3) + 1;
-        const int vmax_tile = n_tile - 1 - off, vmax_all = n_all - 1 - off;
+        const int vmax_tile = n_tile - 1 - off;
         int nown = 0;
         if (tc.first || vmax_tile >= -1) nown = (vmax_tile + 1) / 4 + 1;
-        // record k is complete iff its 4th newline v = 4k+3 is inside the staged region
-        const int kcomplete = vmax_all >= 3 ? (vmax_all - 3) / 4 : -1;
-        for (int k0 = 0; k0 < nown; k0 += CAP) {
-            const int nrec = nown - k0 < CAP ? nown - k0 : CAP;
-            run_round(s, sh, b, tc, p, t, o, off, k0, nrec, kcomplete, gid, gt, ts);
+        // spill rows while the last owned record is incomplete and the segment goes on
+        int nrows = OWN_ROWS + 1;
+#pragma unroll
+        for (int row = OWN_ROWS + 1; row < MAX_ROWS; row++) {
+            pre[row] = 0;
+            if (nown > 0 && 4 * (nown - 1) + 3 + off >= (int) n_all && row * KVQ_ROW < tc.lim) {
+                const Row r = load_row(b, tc, row, lane);
+                pre[row] = reduce_row<NEG>(s, tc, r, row, lane, cl, n_all, n_own);
+                nrows = row + 1;
+            }
         }
-        group_sync(gid);                            // tile buffers are reused by the next tile
+        const bool at_seg_end = tc.a0 + (int64_t) nrows * KVQ_ROW >= seg_end;
+        __syncwarp();
+        for (int k0 = 0; k0 < nown; k0 += 32) {
+            int base = 0;
+            if (k0 > 0) {
+                base = 4 * k0 + off - 1;
+                __syncwarp();
+                rescatter(s, pre, nrows, base, lane);
+                __syncwarp();
+            }
+            run_round(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
+        }
+        __syncwarp();                               // planes are reused by the next tile
     }
 
     // flush the statistics: warp-reduce the per-thread counters, one atomic per warp
@@ -842,7 +780,7 @@ kvq_scan_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
         ts.exh += __shfl_down_sync(0xffffffffu, ts.exh, o2);
         ts.cands += __shfl_down_sync(0xffffffffu, ts.cands, o2);
     }
-    if ((threadIdx.x & 31) == 0) {
+    if (lane == 0) {
         if (ts.records) atomicAdd(&o.ctr->records, ts.records);
         if (ts.bases) atomicAdd(&o.ctr->bases, ts.bases);
         if (ts.exh) atomicAdd(&o.ctr->exhaustive_reads, ts.exh);
@@ -854,8 +792,13 @@ kvq_scan_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
     if (threadIdx.x == 0) atomicMax(&o.ctr->longest, (long long) sh.longest);
 }
 
-// Records that do not fit a tile's spill margin, or whose trimmed read exceeds the packed work
-// lists: one warp per record straight from global memory, exhaustive matcher.  Rare by construction.
+} // namespace
+
+namespace {
+
+// Records that do not fit a tile's spill rows, or whose trimmed read is longer than the fast
+// path handles: one warp per record straight from global memory, exhaustive matcher.  Rare by
+// construction (such a record is longer than 1 KiB).
 __global__ void __launch_bounds__(256)
 kvq_long_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
 {
@@ -899,29 +842,29 @@ kvq_long_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
         }
         if (lane == 0) atomicAdd(&o.ctr->exhaustive_reads, 1ULL);
         for (int sq = 0; sq < t.nseqs; sq++)
-            exhaustive_pair(p, t, o, b.data + rd0, rl, b.base_fpos + rd0, sq);
+            exhaustive_pair(p, t, o, b.data + rd0, rl, b.base_fpos + rd0, sq, lane);
     }
 }
 
 } // namespace
 
 int kvq_scan_smem_bytes(void) { return (int) sizeof(Smem); }
-int kvq_scan_groups(void) { return G; }
+int kvq_scan_groups(void) { return NWARPS; }
 
 int kvq_launch_scan(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
                     int sm_count, void *stream)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kvq_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int) sizeof(Smem));
-        if (e != cudaSuccess) return (int) e;
-        attr_set = true;
-    }
-    int grid = (b.ntiles + G - 1) / G;
+    cudaError_t e = p.amin < 0
+        ? cudaFuncSetAttribute(kvq_scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(Smem))
+        : cudaFuncSetAttribute(kvq_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(Smem));
+    if (e != cudaSuccess) return (int) e;
+    int grid = (b.ntiles + NWARPS - 1) / NWARPS;
     if (grid > sm_count) grid = sm_count;
     if (grid < 1) grid = 1;
-    kvq_scan_kernel<<<grid, THREADS, sizeof(Smem), (cudaStream_t) stream>>>(b, t, p, o);
+    if (p.amin < 0)
+        kvq_scan_kernel<true><<<grid, THREADS, sizeof(Smem), (cudaStream_t) stream>>>(b, t, p, o);
+    else
+        kvq_scan_kernel<false><<<grid, THREADS, sizeof(Smem), (cudaStream_t) stream>>>(b, t, p, o);
     return (int) cudaGetLastError();
 }
 
