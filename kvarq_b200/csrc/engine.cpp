@@ -468,7 +468,7 @@ struct TemplateSet {
         upload(d_covoff, covoff);
 
         dev.bytes = d_bytes.as<uint8_t>(); dev.byte_off = d_boff.as<uint32_t>();
-        dev.packed = d_packed.as<uint32_t>(); dev.packed_off = d_poff.as<uint32_t>();
+        dev.packed = d_packed.as<uint32_t>(); dev.packed_off = d_poff.as<uint32_t>(); dev.packed_words = (int32_t) packed.size();
         dev.len = d_len.as<int32_t>(); dev.seedable = d_seedable.as<uint8_t>();
         dev.exh_list = d_exh.as<int32_t>(); dev.nseqs = n; dev.n_exh = (int) exh.size();
         dev.t1_present = d_bm1.as<uint8_t>(); dev.t1_off = d_off1.as<uint32_t>(); dev.t1_ent = d_ent1.as<uint4>();

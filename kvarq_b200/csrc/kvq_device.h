@@ -13,6 +13,7 @@
 #define KVQ_P2W (3 * KVQ_MAX_PIECES)     // fixed read offsets probed against T2, per read length
 #define KVQ_ROW 1024                    // bytes one warp loads per step (32 lanes x 32 bytes)
 #define KVQ_OWN_ROWS 8
+#define KVQ_TPK_SMEM_WORDS 2048          // packed template codes up to this size are staged in shared memory
 #define KVQ_TILE (KVQ_OWN_ROWS * KVQ_ROW) // bytes of a segment owned by one tile (host builds the tile table)
 
 // 2-bit code of a raw byte: A->0 C->1 T->2 G->3; any other byte maps to *some* code.  Equal
@@ -40,6 +41,7 @@ struct KvqTemplates {
     const uint32_t *byte_off;           // [nseqs+1]
     const uint32_t *packed;             // 2-bit codes, 16 bases per word, 2 zero pad words per seq
     const uint32_t *packed_off;         // [nseqs+1] word offsets
+    int32_t packed_words;               // words in packed[]
     const int32_t *len;                 // [nseqs]
     const uint8_t *seedable;            // [nseqs]
     const int32_t *exh_list;            // indices of non-seedable seqs

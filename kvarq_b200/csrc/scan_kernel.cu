@@ -39,6 +39,7 @@ struct WarpSmem {
     uint32_t nl[NWORDS + 1];                // newline plane, bit j of word w <=> byte 32 w + j is '\n'
     uint32_t ge[NWORDS + 1];                // quality plane, byte >= Amin
     uint32_t pk[2 * NWORDS + 4];            // code plane: 2 bits per byte, contiguous stream
+    uint16_t pre[NWORDS];                   // newlines of the region before word w
     uint16_t nlpos[NLCAP];                  // positions of the newlines ranked [base, base + NLCAP)
     uint32_t rd[32];                        // reads of the round: start | length << 16 (0 = none)
     uint32_t seedq[SEEDQ];
@@ -48,6 +49,7 @@ struct Smem {
     uint8_t t1[KVQ_NKEYS];                  // T1 presence, one byte per key
     uint32_t bm2[KVQ_BITMAP_WORDS];         // T2 presence, one bit per key
     uint32_t hist[KVQ_HIST];
+    uint32_t tpk[KVQ_TPK_SMEM_WORDS];       // packed template codes when they fit (else read through L1/L2)
     int longest;
     int pad[3];
     WarpSmem w[NWARPS];
@@ -176,11 +178,11 @@ __device__ __forceinline__ Row load_row(const KvqBatch &b, const TileCtx &t, int
     return r;
 }
 
-// Reduce one 32-byte word per lane to the three planes, rank its newlines (exclusive prefix of
-// the lane returned, running total in `nl_total`) and scatter the first NLCAP positions.
+// Reduce one 32-byte word per lane to the three planes and rank its newlines (exclusive prefix
+// kept per word, running total in `nl_total`, those owned by the tile in `nl_owned`).
 template <bool NEG>
-__device__ __forceinline__ uint32_t reduce_row(WarpSmem &s, const TileCtx &t, const Row &r, int row, int lane,
-                                               uint32_t cl, uint32_t &nl_total, uint32_t &nl_owned)
+__device__ __forceinline__ void reduce_row(WarpSmem &s, const TileCtx &t, const Row &r, int row, int lane,
+                                           uint32_t cl, uint32_t &nl_total, uint32_t &nl_owned)
 {
     const int w = row * 32 + lane;
     uint32_t nl = gather32(gather2(nl_bits(r.a.x), nl_bits(r.a.y)), gather2(nl_bits(r.a.z), nl_bits(r.a.w)),
@@ -195,40 +197,55 @@ __device__ __forceinline__ uint32_t reduce_row(WarpSmem &s, const TileCtx &t, co
     uint2 pk;
     pk.x = pack8(r.a.x, r.a.y) | (pack8(r.a.z, r.a.w) << 16);
     pk.y = pack8(r.b.x, r.b.y) | (pack8(r.b.z, r.b.w) << 16);
-    // newlines outside [shift, lim) belong to other tiles' segments
-    const int lo = t.shift - (w << 5), hi = t.lim - (w << 5);
-    if (lo > 0) nl &= lo >= 32 ? 0u : (0xFFFFFFFFu << lo);
-    if (hi < 32) nl &= hi <= 0 ? 0u : ((1u << hi) - 1u);
+    uint32_t cnt;
+    const int end = t.lim < t.tile_end ? t.lim : t.tile_end;
+    if (row > 0 && (row + 1) * KVQ_ROW <= end) {    // warp-uniform: every byte of the row is owned
+        cnt = __popc(nl);
+        nl_owned += cnt;
+    } else {
+        // newlines outside [shift, lim) belong to other tiles' segments
+        const int lo = t.shift - (w << 5), hi = t.lim - (w << 5);
+        if (lo > 0) nl &= lo >= 32 ? 0u : (0xFFFFFFFFu << lo);
+        if (hi < 32) nl &= hi <= 0 ? 0u : ((1u << hi) - 1u);
+        const int own = t.tile_end - (w << 5);
+        nl_owned += __popc(own >= 32 ? nl : own <= 0 ? 0u : (nl & ((1u << own) - 1u)));
+        cnt = __popc(nl);
+    }
     s.nl[w] = nl; s.ge[w] = ge;
     reinterpret_cast<uint2 *>(s.pk)[w] = pk;
-    const int own = t.tile_end - (w << 5);
-    nl_owned += __popc(own >= 32 ? nl : own <= 0 ? 0u : (nl & ((1u << own) - 1u)));
-    const uint32_t cnt = __popc(nl);
     uint32_t inc = cnt;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
         if (lane >= o) inc += n;
     }
-    const uint32_t ex = nl_total + inc - cnt;
+    s.pre[w] = (uint16_t) (nl_total + inc - cnt);
     nl_total += __shfl_sync(0xffffffffu, inc, 31);
-    uint32_t m = nl, rank = ex;
-    while (m && rank < NLCAP) {
-        s.nlpos[rank++] = (uint16_t) ((w << 5) + __ffs(m) - 1);
-        m &= m - 1;
-    }
-    return ex;
 }
 
-// positions of the newlines ranked [base, base + NLCAP), from the plane (rounds after the first)
-__device__ __forceinline__ void rescatter(WarpSmem &s, const uint32_t *pre, int nrows, int base, int lane)
+// P1 over rows [row0, row1): two rows of loads in flight
+template <bool NEG>
+__device__ __forceinline__ void stage_rows(WarpSmem &s, const KvqBatch &b, const TileCtx &t, int row0, int row1, int lane,
+                                           uint32_t cl, uint32_t &nl_total, uint32_t &nl_owned)
 {
-#pragma unroll
-    for (int row = 0; row < MAX_ROWS; row++) {
-        if (row >= nrows) break;
+    Row r0 = load_row(b, t, row0, lane), r1 = load_row(b, t, row0 + 1, lane);
+#pragma unroll 1
+    for (int row = row0; row < row1; row++) {
+        Row r2 = r1;
+        if (row + 2 < row1) r2 = load_row(b, t, row + 2, lane);
+        reduce_row<NEG>(s, t, r0, row, lane, cl, nl_total, nl_owned);
+        r0 = r1; r1 = r2;
+    }
+}
+
+// positions of the newlines ranked [base, base + NLCAP), from the plane
+__device__ __forceinline__ void scatter_newlines(WarpSmem &s, int nrows, int base, int lane)
+{
+#pragma unroll 1
+    for (int row = 0; row < nrows; row++) {
         const int w = row * 32 + lane;
         uint32_t m = s.nl[w];
-        int rank = (int) pre[row] - base;
+        int rank = (int) s.pre[w] - base;
         while (m && rank < NLCAP) {
             if (rank >= 0) s.nlpos[rank] = (uint16_t) ((w << 5) + __ffs(m) - 1);
             rank++;
@@ -237,17 +254,35 @@ __device__ __forceinline__ void rescatter(WarpSmem &s, const uint32_t *pre, int 
     }
 }
 
+// Newlines of the bytes a tile owns, from global memory (the look-ahead pass: the count of tile
+// N+1 is published before tile N is processed, so nobody ever waits long in the look-back).
+__device__ __forceinline__ int count_owned_newlines(const KvqBatch &b, int64_t a0, int shift, int tile_end, int lane)
+{
+    uint32_t cnt = 0;
+    const uint4 *src = reinterpret_cast<const uint4 *>(b.data + a0);
+#pragma unroll 3
+    for (int row = 0; row <= OWN_ROWS; row++) {
+        const int w = row * 32 + lane;
+        if ((w << 5) < tile_end) {
+            const uint4 a = __ldg(src + 2 * w), c = __ldg(src + 2 * w + 1);
+            uint32_t nl = gather32(gather2(nl_bits(a.x), nl_bits(a.y)), gather2(nl_bits(a.z), nl_bits(a.w)),
+                                   gather2(nl_bits(c.x), nl_bits(c.y)), gather2(nl_bits(c.z), nl_bits(c.w)));
+            const int lo = shift - (w << 5), hi = tile_end - (w << 5);
+            if (lo > 0) nl &= 0xFFFFFFFFu << lo;
+            if (hi < 32) nl &= (1u << hi) - 1u;
+            cnt += __popc(nl);
+        }
+    }
+    return (int) __reduce_add_sync(0xffffffffu, cnt);
+}
+
 // Decoupled look-back over the tiles of one segment, 32 predecessors per step.  Status word:
 // bit3 = inclusive prefix, bit2 = tile aggregate, bits 1:0 = newline count mod 4.  Tiles are
 // claimed in stream order, so a predecessor is always resident or finished.
 __device__ __forceinline__ int resolve_phase(const KvqBatch &b, int tile, int first, int n_tile, int lane)
 {
     volatile uint32_t *st = b.tile_status;
-    if (first) {
-        if (lane == 0) st[tile] = 8u | (uint32_t) (n_tile & 3);
-        return 0;
-    }
-    if (lane == 0) st[tile] = 4u | (uint32_t) (n_tile & 3);
+    if (first) return 0;                            // published as an inclusive prefix by the look-ahead
     int acc = 0;
     for (int j = tile - 1;;) {
         const int i = j - lane;
@@ -303,7 +338,7 @@ __device__ __forceinline__ uint8_t complement(uint8_t c)     // Sequence.pairs, 
 
 // add_hit (workhorse.c:408-443) + Coverage.apply_hit (kvarq/analyse.py:57-78), one thread.
 // `rd` points at the trimmed read's bytes, `tp` at the template's bytes (both global).
-__device__ void emit_hit(const KvqTemplates &t, const KvqParams &p, const KvqOut &o, int seq, int d,
+__device__ __noinline__ void emit_hit(const KvqTemplates &t, const KvqParams &p, const KvqOut &o, int seq, int d,
                          int ro, int to, int L, int rl, int64_t file_pos, const uint8_t *rd,
                          const uint8_t *tp, int copies, int rule)
 {
@@ -346,7 +381,7 @@ __device__ void emit_hit(const KvqTemplates &t, const KvqParams &p, const KvqOut
 
 // Warp-cooperative variant: lane 0 reserves the output slots, all lanes copy the hitseq bytes
 // and update the coverage arrays.
-__device__ void emit_hit_warp(const KvqTemplates &t, const KvqParams &p, const KvqOut &o, int seq, int d,
+__device__ __noinline__ void emit_hit_warp(const KvqTemplates &t, const KvqParams &p, const KvqOut &o, int seq, int d,
                               int ro, int to, int L, int rl, int sl, int64_t file_pos, const uint8_t *rd,
                               const uint8_t *tp, int copies, int rule, int lane)
 {
@@ -418,7 +453,7 @@ __device__ void exhaustive_pair(const KvqParams &p, const KvqTemplates &t, const
 // Is (kind, pos) the first seed, in the fixed order T1 pieces then T2 offsets, that fires on
 // diagonal d of (read, seq)?  Every firing seed reaches the same diagonal; only this one emits.
 // rpk = code plane, rb = base offset of the read in it.
-__device__ bool canonical_seed(const KvqParams &p, const KvqTemplates &t, const uint32_t *rpk, int rb,
+__device__ __noinline__ bool canonical_seed(const KvqParams &p, const KvqTemplates &t, const uint32_t *rpk, int rb,
                                const uint32_t *tpk, int rl, int sl, int d, int kind, int pos)
 {
     for (int j = 0; j < p.npieces; j++) {
@@ -446,7 +481,14 @@ namespace {
 
 struct Ctx {
     const KvqBatch &b; const KvqTemplates &t; const KvqParams &p; const KvqOut &o; const TileCtx &tc;
+    const uint32_t *tpk;                    // packed template codes: shared copy when they fit, else global
 };
+
+__device__ __forceinline__ uint32_t extract16_t(const uint32_t *pk, int b)      // generic address space
+{
+    int w = b >> 4;
+    return funnel_r(pk[w], pk[w + 1], (uint32_t) ((b & 15) << 1));
+}
 
 // ---- P4: seeds -> bucket entries -> code-space verify -> confirm + emit ------------------------
 // Seeds s.seedq[base, base + n), one per lane.  Seed = read | pos << 5 | kind << 15.
@@ -460,6 +502,7 @@ __device__ void drain_seeds(WarpSmem &s, const Ctx &c, int base, int n, int lane
         const uint32_t rdv = s.rd[sd & 31];
         pos = (int) ((sd >> 5) & 1023); kind = (int) (sd >> 15);
         rd0 = (int) (rdv & 0xFFFFu); rl = (int) (rdv >> 16);
+        if (kind) pos = __ldg(t.p2_tab + rl * KVQ_P2W + pos);      // T2 seeds carry their probe slot
         const uint32_t key = extract16(s.pk, rd0 + pos) & 0xFFFFu;
         const uint32_t *off = kind ? t.t2_off : t.t1_off;
         e0 = __ldg(off + key); e1 = __ldg(off + key + 1);
@@ -476,17 +519,21 @@ __device__ void drain_seeds(WarpSmem &s, const Ctx &c, int base, int n, int lane
             en = __ldg(ent + e0); e0++;
             const int sl = (int) (en.y >> 16);
             d = (int) (en.y & 0xFFFFu) - pos;
-            int ro, to, L, rule;
-            if (diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule)) {
-                const uint32_t *tpk = t.packed + en.z;
-                int e = 0;
-                for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
-                    uint32_t x = extract16(s.pk, rd0 + ro + j) ^ extract16_g(tpk, to + j);
-                    uint32_t m = (x | (x >> 1)) & 0x55555555u;
-                    if (L - j < 16) m &= (1u << (2 * (L - j))) - 1u;
-                    e += __popc(m);
-                }
-                surv = e <= p.maxerrors;
+            // overlap of the diagonal; Hamming distance in code space first (a lower bound of the
+            // byte distance, most candidates die on the first word), the acceptance rule after
+            const int ro = d < 0 ? -d : 0, to = d > 0 ? d : 0;
+            const int L = min(rl - ro, sl - to);
+            const uint32_t *tpk = c.tpk + en.z;
+            int e = 0;
+            for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
+                uint32_t x = extract16(s.pk, rd0 + ro + j) ^ extract16_t(tpk, to + j);
+                uint32_t m = (x | (x >> 1)) & 0x55555555u;
+                if (L - j < 16) m &= (1u << (2 * (L - j))) - 1u;
+                e += __popc(m);
+            }
+            if (e <= p.maxerrors) {
+                int ro2, to2, L2, rule;
+                surv = diag_rule(d, rl, sl, p.minoverlap, ro2, to2, L2, rule) != 0;
             }
             ts.cands++;
         }
@@ -645,17 +692,17 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
             push_seeds(s, c, qn, hits, (uint32_t) lane, (w << 5) - rd0, lane, ts);
         }
         // T2: a few fixed offsets per read (whole-read / head / tail pieces), table per read length
-        for (int i = 0; i < p.n2max; i++) {
-            uint32_t hit = 0; int pos = 0;
-            if (seedable) {
-                pos = __ldg(t.p2_tab + rl * KVQ_P2W + i);
-                if (pos >= 0) {
-                    const uint32_t key = extract16(s.pk, rd0 + pos) & 0xFFFFu;
-                    hit = (sh.bm2[key >> 5] >> (key & 31)) & 1u;
-                }
+        uint32_t hit2 = 0;
+        if (seedable) {
+            const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
+            for (int i = 0; i < p.n2max; i++) {
+                const int pos = __ldg(p2 + i);
+                if (pos < 0) continue;
+                const uint32_t key = extract16(s.pk, rd0 + pos) & 0xFFFFu;
+                hit2 |= ((sh.bm2[key >> 5] >> (key & 31)) & 1u) << i;
             }
-            push_seeds(s, c, qn, hit, (uint32_t) lane | (1u << 15), pos, lane, ts);
         }
+        push_seeds(s, c, qn, hit2, (uint32_t) lane | (1u << 15), 0, lane, ts);
         if (qn) drain_seeds(s, c, 0, qn, lane, ts);
     }
     // exhaustive matcher: reads the seed scheme does not cover against every template, the
@@ -688,7 +735,8 @@ namespace {
 
 template <bool NEG>
 __global__ void __launch_bounds__(THREADS, 1)
-kvq_scan_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
+kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqTemplates t,
+                const __grid_constant__ KvqParams p, const __grid_constant__ KvqOut o)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem &sh = *reinterpret_cast<Smem *>(smem_raw);
@@ -701,17 +749,38 @@ kvq_scan_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
         for (int i = threadIdx.x; i < KVQ_NKEYS / 16; i += THREADS) dst[i] = __ldg(src + i);
         for (int i = threadIdx.x; i < KVQ_BITMAP_WORDS; i += THREADS) sh.bm2[i] = __ldg(t.t2_bitmap + i);
         for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS) sh.hist[i] = 0;
+        if (t.packed_words <= KVQ_TPK_SMEM_WORDS)
+            for (int i = threadIdx.x; i < t.packed_words; i += THREADS) sh.tpk[i] = __ldg(t.packed + i);
         if (threadIdx.x == 0) sh.longest = -1;
     }
     __syncthreads();
     ThreadStats ts{0, 0, 0, 0};
     const uint32_t cl = (uint32_t) (p.amin & 0x7F) * 0x01010101u;
+    const uint32_t *tpk = t.packed_words <= KVQ_TPK_SMEM_WORDS ? sh.tpk : t.packed;
 
-    for (;;) {
+    // Tile geometry + look-ahead: claim the next tile, count the newlines of the bytes it owns
+    // and publish them (status word, see resolve_phase) before the current tile is processed.
+    struct Claim { int tile; int n_tile; };
+    auto claim = [&]() -> Claim {
         int tile = 0;
         if (lane == 0) tile = (int) atomicAdd(&o.ctr->tile_next, 1u);
         tile = __shfl_sync(0xffffffffu, tile, 0);
-        if (tile >= b.ntiles) break;
+        if (tile >= b.ntiles) return Claim{-1, 0};
+        const int seg = __ldg(b.tile_seg + tile);
+        const int64_t t0 = __ldg(b.tile_off + tile);
+        const int64_t seg_beg = __ldg(b.seg_off + seg), seg_end = __ldg(b.seg_off + seg + 1);
+        const int64_t a0 = t0 & ~(int64_t) 31;
+        const int64_t t1 = t0 + KVQ_TILE < seg_end ? t0 + KVQ_TILE : seg_end;
+        const int n = count_owned_newlines(b, a0, (int) (t0 - a0), (int) (t1 - a0), lane);
+        if (lane == 0)
+            ((volatile uint32_t *) b.tile_status)[tile] = (t0 == seg_beg ? 8u : 4u) | (uint32_t) (n & 3);
+        return Claim{tile, n};
+    };
+
+    Claim cur = claim();
+    while (cur.tile >= 0) {
+        const Claim nxt = claim();
+        const int tile = cur.tile;
         const int seg = __ldg(b.tile_seg + tile);
         const int64_t t0 = __ldg(b.tile_off + tile);
         const int64_t seg_beg = __ldg(b.seg_off + seg), seg_end = __ldg(b.seg_off + seg + 1);
@@ -724,22 +793,13 @@ kvq_scan_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
         tc.lim = lim < (int64_t) MAX_ROWS * KVQ_ROW ? (int) lim : MAX_ROWS * KVQ_ROW;
         tc.first = (t0 == seg_beg);
         tc.seg_end = seg_end;
-        const Ctx c{b, t, p, o, tc};
+        const Ctx c{b, t, p, o, tc, tpk};
 
-        // P1: rows 0 .. OWN_ROWS (the tile plus one row of spill), two rows of loads in flight
-        uint32_t pre[MAX_ROWS];
+        // P1: rows 0 .. OWN_ROWS (the tile plus one row of spill)
         uint32_t n_all = 0, n_own = 0;
-        {
-            Row r0 = load_row(b, tc, 0, lane), r1 = load_row(b, tc, 1, lane);
-#pragma unroll
-            for (int row = 0; row <= OWN_ROWS; row++) {
-                Row r2;
-                if (row + 2 <= OWN_ROWS) r2 = load_row(b, tc, row + 2, lane);
-                pre[row] = reduce_row<NEG>(s, tc, r0, row, lane, cl, n_all, n_own);
-                r0 = r1; r1 = r2;
-            }
-        }
-        const int n_tile = (int) __reduce_add_sync(0xffffffffu, n_own);
+        int nrows = OWN_ROWS + 1;
+        stage_rows<NEG>(s, b, tc, 0, nrows, lane, cl, n_all, n_own);
+        const int n_tile = cur.n_tile;
         const int phase = resolve_phase(b, tile, tc.first, n_tile, lane);
         // newline rank -> record-relative numbering (see parse_record)
         const int off = tc.first ? 0 : ((3 - phase) & 3) + 1;
@@ -747,29 +807,20 @@ kvq_scan_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
         int nown = 0;
         if (tc.first || vmax_tile >= -1) nown = (vmax_tile + 1) / 4 + 1;
         // spill rows while the last owned record is incomplete and the segment goes on
-        int nrows = OWN_ROWS + 1;
-#pragma unroll
-        for (int row = OWN_ROWS + 1; row < MAX_ROWS; row++) {
-            pre[row] = 0;
-            if (nown > 0 && 4 * (nown - 1) + 3 + off >= (int) n_all && row * KVQ_ROW < tc.lim) {
-                const Row r = load_row(b, tc, row, lane);
-                pre[row] = reduce_row<NEG>(s, tc, r, row, lane, cl, n_all, n_own);
-                nrows = row + 1;
-            }
+        while (nrows < MAX_ROWS && nown > 0 && 4 * (nown - 1) + 3 + off >= (int) n_all && nrows * KVQ_ROW < tc.lim) {
+            stage_rows<NEG>(s, b, tc, nrows, nrows + 1, lane, cl, n_all, n_own);
+            nrows++;
         }
         const bool at_seg_end = tc.a0 + (int64_t) nrows * KVQ_ROW >= seg_end;
-        __syncwarp();
         for (int k0 = 0; k0 < nown; k0 += 32) {
-            int base = 0;
-            if (k0 > 0) {
-                base = 4 * k0 + off - 1;
-                __syncwarp();
-                rescatter(s, pre, nrows, base, lane);
-                __syncwarp();
-            }
+            const int base = k0 > 0 ? 4 * k0 + off - 1 : 0;
+            __syncwarp();
+            scatter_newlines(s, nrows, base, lane);
+            __syncwarp();
             run_round(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
         }
         __syncwarp();                               // planes are reused by the next tile
+        cur = nxt;
     }
 
     // flush the statistics: warp-reduce the per-thread counters, one atomic per warp
@@ -800,7 +851,8 @@ namespace {
 // path handles: one warp per record straight from global memory, exhaustive matcher.  Rare by
 // construction (such a record is longer than 1 KiB).
 __global__ void __launch_bounds__(256)
-kvq_long_kernel(KvqBatch b, KvqTemplates t, KvqParams p, KvqOut o)
+kvq_long_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqTemplates t,
+                const __grid_constant__ KvqParams p, const __grid_constant__ KvqOut o)
 {
     const int lane = threadIdx.x & 31;
     const unsigned long long n = o.ctr->long_count < o.long_cap ? o.ctr->long_count : o.long_cap;
