@@ -228,11 +228,14 @@ def main():
     t0 = time.perf_counter()
     kernel_ms, launches, d2h, call_ms = 0.0, 0, 0, 0.0
     for _ in range(args.steps):
-        r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert=False)   # syncs the stream
+        r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert='timing')   # syncs the stream
         kernel_ms += r.timing['kernel_ms']; launches += r.timing['launches']; d2h += r.timing['d2h_bytes']; call_ms += r.timing['wall_ms']
     barrier()
     dt = allmax(time.perf_counter() - t0)
     clocks = sampler.summary()
+    nhits_timed, nrec_timed = r.nhits, r['stats']['records_parsed']
+    r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert=False)   # full result for the reduce below
+    assert r.nhits == nhits_timed and r['stats']['records_parsed'] == nrec_timed
     bases = r.timing['bases']
     stream_bytes = r.timing['stream_bytes']
     total_bases = allsum(bases * args.steps)

@@ -144,6 +144,13 @@ class Engine(object):
         lib = self._lib
         try:
             n = lib.kvq_result_nhits(res)
+            if want_hits == 'timing':           # bench loop: no Python objects beyond the counters
+                out = Result(hits=(), stats={'records_parsed': lib.kvq_result_stats(res).contents.records_parsed},
+                             hitseqs=[])
+                t = lib.kvq_result_timing(res).contents
+                out.timing = {k: getattr(t, k) for k, _ in L.Timing._fields_}
+                out.nhits = n
+                return out
             hits, hitseqs = (), []
             if want_hits and n:
                 recs = lib.kvq_result_hits(res)
@@ -243,7 +250,8 @@ class Engine(object):
 
     def scan_staged(self, staged, seqlist, nplus=0, want_hits=True, convert=None):
         """want_hits=False: the kernels only count hits (no hit records / hitseqs written);
-        convert=False: hits are produced and copied back but not turned into Python tuples."""
+        convert=False: hits are produced and copied back but not turned into Python tuples;
+        convert='timing': only nhits, records_parsed and the timing block are read."""
         _, arr, lens, n = self._seq_args(seqlist)
         res = C.c_void_p()
         rc = self._lib.kvq_scan_staged(self._h, staged._h, arr, lens, n, nplus, 1 if want_hits else 0,
