@@ -23,7 +23,6 @@ import json
 import os
 import subprocess
 import sys
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -46,39 +45,60 @@ def peaks():
         return 6650.0, 'fallback (B200_PROFILING.md)'
 
 
-class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
-    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
+class ClockSampler(object):
+    """nvidia-smi clocks + throttle reasons during the timed regions (B200_PROFILING.md).  A separate
+    process (`nvidia-smi -lms`) so that sampling never competes with the timed loop for the GIL;
+    only samples stamped inside [mark_begin, mark_end] windows are used."""
+    Q = ('timestamp,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
          'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
          'clocks_event_reasons.sw_power_cap')
 
     def __init__(self, index):
-        threading.Thread.__init__(self, daemon=True)
-        self.index = index
-        self.samples = []
-        self.stop_flag = False
+        self.windows = []
+        self.t0 = None
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '20'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
 
-    def run(self):
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
-                                      '--format=csv,noheader,nounits'], capture_output=True, text=True,
-                                     timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(',')])
-            except Exception:
-                pass
-            time.sleep(0.05)
+    def start(self):
+        pass
+
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.windows.append((self.t0, time.time()))
 
     def summary(self):
-        self.stop_flag = True
-        self.join(timeout=6)
-        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
-        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        import datetime
+        rows = []
+        if self.proc is not None:
+            time.sleep(0.05)
+            self.proc.terminate()
+            try:
+                out = self.proc.communicate(timeout=5)[0]
+            except Exception:
+                out = ''
+            for line in out.strip().split('\n'):
+                f = [x.strip() for x in line.split(',')]
+                if len(f) < 7:
+                    continue
+                try:
+                    ts = datetime.datetime.strptime(f[0], '%Y/%m/%d %H:%M:%S.%f').timestamp()
+                except Exception:
+                    continue
+                rows.append((ts, f[1:]))
+        inside = [f for ts, f in rows if any(a - 0.02 <= ts <= b + 0.02 for a, b in self.windows)]
+        use = inside or [f for _, f in rows]
+        sm = sorted(int(f[0]) for f in use if f[0].isdigit())
+        mx = [int(f[1]) for f in use if f[1].isdigit()]
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v == 'Active'})
+        reasons = sorted({n for f in use for n, v in zip(names, f[2:6]) if v == 'Active'})
         return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None,
-                'reasons': reasons, 'samples': len(self.samples)}
+                'reasons': reasons, 'samples': len(use), 'samples_inside_timed_regions': len(inside)}
 
 
 def make_workload(rank):
@@ -225,6 +245,7 @@ def main():
     sampler = ClockSampler(local)
     sampler.start()
     barrier()
+    sampler.mark_begin()
     t0 = time.perf_counter()
     kernel_ms, launches, d2h, call_ms = 0.0, 0, 0, 0.0
     for _ in range(args.steps):
@@ -232,7 +253,7 @@ def main():
         kernel_ms += r.timing['kernel_ms']; launches += r.timing['launches']; d2h += r.timing['d2h_bytes']; call_ms += r.timing['wall_ms']
     barrier()
     dt = allmax(time.perf_counter() - t0)
-    clocks = sampler.summary()
+    sampler.mark_end()
     nhits_timed, nrec_timed = r.nhits, r['stats']['records_parsed']
     r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert=False)   # full result for the reduce below
     assert r.nhits == nhits_timed and r['stats']['records_parsed'] == nrec_timed
@@ -257,6 +278,7 @@ def main():
     fq_pin = eng.pinned_copy(fq)                                                    # inputs in pinned host memory
     eng.findseqs_mem([fq_pin], seqs, nplus=ts.nplus, want_hits=False)               # warm-up
     barrier()
+    sampler.mark_begin()
     t0 = time.perf_counter()
     h2d = d2h_e = 0
     for _ in range(e2e_steps):
@@ -264,6 +286,8 @@ def main():
         h2d += q.timing['h2d_bytes']; d2h_e += q.timing['d2h_bytes']
     barrier()
     dt_e = allmax(time.perf_counter() - t0)
+    sampler.mark_end()
+    clocks = sampler.summary()
     e2e = allsum(q.timing['bases'] * e2e_steps) / dt_e / 1e9
     assert q.nhits == r.nhits and q['stats']['records_parsed'] == r['stats']['records_parsed']
     log('[rank %d] e2e: %.1f ms/step' % (rank, 1e3 * dt_e / e2e_steps))

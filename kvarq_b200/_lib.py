@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'libkvarq_b200.so')
+LIB_PATH = os.environ.get('KVQ_B200_LIB') or os.path.join(HERE, 'libkvarq_b200.so')   # env: kernel-variant sweeps only
 
 KVQ_MAX_READLENGTH = 1024
 

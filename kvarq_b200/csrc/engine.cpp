@@ -382,7 +382,21 @@ struct SeedTable {
         for (int k = 0; k < KVQ_NKEYS; k++) off[k + 1] += off[k];
         std::vector<uint32_t> at(off.begin(), off.end() - 1);
         for (auto &it : items) ent[at[it.first]++] = it.second;
+        // direct-mapped first entries + overflow array (see KvqTemplates)
+        first.assign(KVQ_NKEYS, make_uint4(0, 0, 0, 0)); ovf.clear();
+        for (int k = 0; k < KVQ_NKEYS; k++) {
+            const uint32_t b0 = off[k], b1 = off[k + 1];
+            if (b0 == b1) continue;
+            const uint32_t more = b1 - b0 - 1;
+            if (more >= 255) ovf.push_back(make_uint4(more, 0, 0, 0));
+            uint4 f = ent[b0];
+            f.x |= (more >= 255 ? 255u : more) << 24; f.w = (uint32_t) ovf.size();
+            first[k] = f;
+            for (uint32_t e = b0 + 1; e < b1; e++) ovf.push_back(ent[e]);
+        }
+        if (ovf.empty()) ovf.push_back(make_uint4(0, 0, 0, 0));
     }
+    std::vector<uint4> first, ovf;
 };
 
 struct TemplateSet {
@@ -390,7 +404,7 @@ struct TemplateSet {
     std::vector<int32_t> len;
     KvqTemplates dev{}; KvqParams par{};
     DevBuf d_bytes, d_boff, d_packed, d_poff, d_len, d_seedable, d_exh;
-    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2;
+    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2, d_dg1, d_bm2l, d_first1, d_first2;
 
     static unsigned char comp(unsigned char c) {
         switch (c) { case 'A': return 'T'; case 'T': return 'A'; case 'C': return 'G'; case 'G': return 'C'; default: return c; }
@@ -433,6 +447,26 @@ struct TemplateSet {
         std::vector<uint8_t> bytes; std::vector<uint32_t> boff(n + 1, 0), packed, poff(n + 1, 0);
         std::vector<uint8_t> seedable(n, 0); std::vector<int32_t> exh;
         std::vector<std::pair<uint32_t, uint4>> it1, it2;
+        // T1 digest: codes of the 3 bases that follow a piece's 8-mer inside the piece; 0xFF when a
+        // piece is shorter than 11 bases or two pieces with the same key disagree (no filtering)
+        std::vector<uint8_t> dg1(KVQ_NKEYS, 0xFE);                  // 0xFE = key not seen yet
+        // short / long template classes for the whole-read T2 probes: the long class holds at most
+        // a quarter of the T2 entries (it is everything when no such split exists)
+        int short_max = 0;
+        if (seed_ok) {
+            std::vector<std::pair<int, int64_t>> bylen;             // (length, T2 entries)
+            for (int i = 0; i < n; i++)
+                if (lens[i] / pieces >= KVQ_SEED_K && lens[i] <= KVQ_MAX_SEEDED_SEQLEN) bylen.push_back({lens[i], lens[i] - KVQ_SEED_K + 1});
+            std::sort(bylen.begin(), bylen.end());
+            int64_t total = 0, acc = 0;
+            for (auto &x : bylen) total += x.second;
+            for (size_t k = bylen.size(); k-- > 0;) {
+                acc += bylen[k].second;
+                if (acc * 4 > total) { short_max = bylen[k].first; break; }     // this length and below are "short"
+            }
+            // (the longest length ends up short when it alone holds more than a quarter: no long class)
+        }
+        std::vector<uint32_t> bm2l(KVQ_BITMAP_WORDS, 0);
         int max_len = 0;
         for (int i = 0; i < n; i++) {
             const unsigned char *s = (const unsigned char *) seqs[i]; const int sl = lens[i];
@@ -442,17 +476,26 @@ struct TemplateSet {
             packed.resize(packed.size() + words, 0);
             for (int j = 0; j < sl; j++) packed[poff[i] + j / 16] |= code_of(s[j]) << (2 * (j % 16));
             max_len = std::max(max_len, sl);
-            const bool ok = seed_ok && sl / pieces >= KVQ_SEED_K && sl <= KVQ_MAX_SEEDED_SEQLEN;
+            const bool ok = seed_ok && sl / pieces >= KVQ_SEED_K && sl <= KVQ_MAX_SEEDED_SEQLEN && i < (1 << 24);
             seedable[i] = ok;
             if (!ok) { exh.push_back(i); continue; }
             // entry = {seq, toff | len << 16, offset of the packed codes, offset of the raw bytes}
             auto entry = [&](int toff) { return make_uint4((unsigned) i, (unsigned) toff | ((unsigned) sl << 16), poff[i], boff[i]); };
             for (int j = 0; j < pieces; j++) {
                 const int toff = (int) ((int64_t) j * sl / pieces);
-                it1.push_back({kmer_key(s + toff), entry(toff)});
+                const int tnext = (int) ((int64_t) (j + 1) * sl / pieces);         // piece j = [toff, tnext)
+                const uint32_t key = kmer_key(s + toff);
+                it1.push_back({key, entry(toff)});
+                uint8_t dg = 0xFF;
+                if (tnext - toff >= KVQ_SEED_K + 3)
+                    dg = (uint8_t) (code_of(s[toff + 8]) | (code_of(s[toff + 9]) << 2) | (code_of(s[toff + 10]) << 4));
+                dg1[key] = dg1[key] == 0xFE ? dg : (dg1[key] == dg ? dg : (uint8_t) 0xFF);
             }
-            for (int toff = 0; toff + KVQ_SEED_K <= sl; toff++)
-                it2.push_back({kmer_key(s + toff), entry(toff)});
+            for (int toff = 0; toff + KVQ_SEED_K <= sl; toff++) {
+                const uint32_t key = kmer_key(s + toff);
+                it2.push_back({key, entry(toff)});
+                if (sl > short_max) bm2l[key >> 5] |= 1u << (key & 31);
+            }
         }
         boff[n] = (uint32_t) bytes.size(); poff[n] = (uint32_t) packed.size();
         bytes.resize(bytes.size() + 64, 0);
@@ -463,8 +506,9 @@ struct TemplateSet {
 
         upload(d_bytes, bytes); upload(d_boff, boff); upload(d_packed, packed, 4); upload(d_poff, poff);
         upload(d_len, len); upload(d_seedable, seedable); upload(d_exh, exh);
-        upload(d_bm1, t1.present); upload(d_off1, t1.off); upload(d_ent1, t1.ent);
-        upload(d_bm2, t2.bitmap); upload(d_off2, t2.off); upload(d_ent2, t2.ent);
+        upload(d_bm1, t1.present); upload(d_off1, t1.off); upload(d_ent1, t1.ovf); upload(d_first1, t1.first);
+        upload(d_bm2, t2.bitmap); upload(d_off2, t2.off); upload(d_ent2, t2.ovf); upload(d_first2, t2.first);
+        upload(d_dg1, dg1); upload(d_bm2l, bm2l);
         upload(d_covoff, covoff);
 
         dev.bytes = d_bytes.as<uint8_t>(); dev.byte_off = d_boff.as<uint32_t>();
@@ -473,6 +517,8 @@ struct TemplateSet {
         dev.exh_list = d_exh.as<int32_t>(); dev.nseqs = n; dev.n_exh = (int) exh.size();
         dev.t1_present = d_bm1.as<uint8_t>(); dev.t1_off = d_off1.as<uint32_t>(); dev.t1_ent = d_ent1.as<uint4>();
         dev.t2_bitmap = d_bm2.as<uint32_t>(); dev.t2_off = d_off2.as<uint32_t>(); dev.t2_ent = d_ent2.as<uint4>();
+        dev.t1_first = d_first1.as<uint4>(); dev.t2_first = d_first2.as<uint4>();
+        dev.t1_digest = d_dg1.as<uint8_t>(); dev.t2l_bitmap = d_bm2l.as<uint32_t>();
         dev.cov_off = d_covoff.as<uint32_t>(); dev.nplus = np;
 
         par.maxerrors = E; par.minoverlap = O; par.minreadlength = cfg.minreadlength;
@@ -497,11 +543,17 @@ struct TemplateSet {
         if (seed_ok)
             for (int rl = par.min_seed_rl; rl <= KVQ_MAXRL_FAST; rl++) {
                 int16_t *row = p2.data() + (size_t) rl * KVQ_P2W; int nn = 0;
-                auto add = [&](int v) { for (int i = 0; i < nn; i++) if (row[i] == v) return; row[nn++] = (int16_t) v; };
-                if (max_len >= rl) for (int j = 0; j < pieces; j++) add((int) ((int64_t) j * rl / pieces));
+                // a whole-read piece can only lie in a template at least as long as the read: reads longer
+                // than the short class probe the long-template bitmap there (KVQ_P2_LONG)
+                auto add = [&](int v, bool lng) {
+                    for (int i = 0; i < nn; i++)
+                        if ((row[i] & KVQ_P2_POS) == v) { if (!lng) row[i] = (int16_t) v; return; }
+                    row[nn++] = (int16_t) (v | (lng ? KVQ_P2_LONG : 0));
+                };
+                if (max_len >= rl) for (int j = 0; j < pieces; j++) add((int) ((int64_t) j * rl / pieces), rl > short_max);
                 if (rl > O) {
-                    for (int j = 0; j < pieces; j++) add(par.o_piece[j]);
-                    for (int j = 0; j < pieces; j++) add(rl - O + par.o_piece[j]);
+                    for (int j = 0; j < pieces; j++) add(par.o_piece[j], false);
+                    for (int j = 0; j < pieces; j++) add(rl - O + par.o_piece[j], false);
                 }
             }
         upload(d_p2, p2);
@@ -513,29 +565,29 @@ struct TemplateSet {
 
 namespace {
 
-// tiles of KVQ_TILE bytes inside every segment, in stream order
-void build_tiles(const std::vector<int64_t> &cuts, std::vector<int64_t> &toff, std::vector<int32_t> &tseg)
+// tiles of KVQ_TILE bytes inside every segment, in stream order: {start, segment end | first << 62}
+void build_tiles(const std::vector<int64_t> &cuts, std::vector<longlong2> &tiles)
 {
-    toff.clear(); tseg.clear();
+    tiles.clear();
     for (size_t sgi = 0; sgi + 1 < cuts.size(); sgi++)
-        for (int64_t t0 = cuts[sgi]; t0 < cuts[sgi + 1]; t0 += KVQ_TILE) { toff.push_back(t0); tseg.push_back((int32_t) sgi); }
+        for (int64_t t0 = cuts[sgi]; t0 < cuts[sgi + 1]; t0 += KVQ_TILE) {
+            longlong2 ti; ti.x = t0; ti.y = cuts[sgi + 1] | ((int64_t) (t0 == cuts[sgi]) << 62);
+            tiles.push_back(ti);
+        }
 }
 
 struct TileBufs {
-    DevBuf d_off, d_seg, d_status; int ntiles = 0;
-    void upload_async(const std::vector<int64_t> &toff, const std::vector<int32_t> &tseg, PinBuf &stage, cudaStream_t st) {
-        ntiles = (int) toff.size();
-        const size_t n = std::max<size_t>(1, toff.size());
-        d_off.ensure(n * 8); d_seg.ensure(n * 4); d_status.ensure(n * 4);
-        stage.ensure(n * 12);
-        memcpy(stage.p, toff.data(), toff.size() * 8);
-        memcpy(stage.as<char>() + n * 8, tseg.data(), tseg.size() * 4);
-        CK(cudaMemcpyAsync(d_off.p, stage.p, toff.size() * 8, cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpyAsync(d_seg.p, stage.as<char>() + n * 8, tseg.size() * 4, cudaMemcpyHostToDevice, st));
+    DevBuf d_info, d_status; int ntiles = 0;
+    void upload_async(const std::vector<longlong2> &tiles, PinBuf &stage, cudaStream_t st) {
+        ntiles = (int) tiles.size();
+        const size_t n = std::max<size_t>(1, tiles.size());
+        d_info.ensure(n * 16); d_status.ensure(n * 4);
+        stage.ensure(n * 16);
+        memcpy(stage.p, tiles.data(), tiles.size() * 16);
+        CK(cudaMemcpyAsync(d_info.p, stage.p, tiles.size() * 16, cudaMemcpyHostToDevice, st));
     }
     void fill(KvqBatch &b) const {
-        b.tile_off = d_off.as<int64_t>(); b.tile_seg = d_seg.as<int32_t>();
-        b.tile_status = d_status.as<uint32_t>(); b.ntiles = ntiles;
+        b.tile_info = d_info.as<longlong2>(); b.tile_status = d_status.as<uint32_t>(); b.ntiles = ntiles;
     }
 };
 
@@ -679,9 +731,9 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
         CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes + BATCH_PAD, cudaMemcpyHostToDevice, s.stream));
     }
     CK(cudaMemcpyAsync(s.d_seg.p, s.h_seg.p, hb.cuts.size() * 8, cudaMemcpyHostToDevice, s.stream));
-    std::vector<int64_t> toff; std::vector<int32_t> tseg;
-    build_tiles(hb.cuts, toff, tseg);
-    s.tiles.upload_async(toff, tseg, s.h_tiles, s.stream);
+    std::vector<longlong2> tiles;
+    build_tiles(hb.cuts, tiles);
+    s.tiles.upload_async(tiles, s.h_tiles, s.stream);
     KvqBatch b{s.d_data.as<uint8_t>(), hb.nbytes, s.d_seg.as<int64_t>(), nseg, hb.base_fpos};
     s.tiles.fill(b);
     KvqOut o = make_out(e, s.d_ctr, s.d_hits, s.hit_cap, s.d_blob, s.blob_cap, s.d_longs, s.long_cap);
@@ -1104,9 +1156,9 @@ int kvq_stage_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens
         st->d_seg.ensure(cuts.size() * 8);
         CK(cudaMemcpy(st->d_seg.p, cuts.data(), cuts.size() * 8, cudaMemcpyHostToDevice));
         {
-            std::vector<int64_t> toff; std::vector<int32_t> tseg; PinBuf stage;
-            build_tiles(cuts, toff, tseg);
-            st->tiles.upload_async(toff, tseg, stage, nullptr);
+            std::vector<longlong2> tiles; PinBuf stage;
+            build_tiles(cuts, tiles);
+            st->tiles.upload_async(tiles, stage, nullptr);
             CK(cudaDeviceSynchronize());
         }
         st->d_ctr.ensure(sizeof(KvqCounters));

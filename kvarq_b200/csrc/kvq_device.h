@@ -2,6 +2,7 @@
 // All pointers are device pointers unless a field name ends in _h.
 #pragma once
 #include <stdint.h>
+#include <cuda_runtime.h>
 
 #define KVQ_SEED_K 8                    // seed length in bases (16-bit keys)
 #define KVQ_NKEYS (1 << (2 * KVQ_SEED_K))
@@ -11,9 +12,15 @@
 #define KVQ_HIST 1024                   // MAX_READLENGTH, workhorse.c:105
 #define KVQ_MAXRL_FAST 512              // longer trimmed reads take the long-record kernel
 #define KVQ_P2W (3 * KVQ_MAX_PIECES)     // fixed read offsets probed against T2, per read length
+#define KVQ_P2_POS 0x3FFF               // p2_tab entry: read offset ...
+#define KVQ_P2_LONG 0x4000              // ... | flag: only templates longer than the short class can match here
 #define KVQ_ROW 1024                    // bytes one warp loads per step (32 lanes x 32 bytes)
-#define KVQ_OWN_ROWS 8
+#ifndef KVQ_OWN_ROWS
+#define KVQ_OWN_ROWS 10
+#endif
+#ifndef KVQ_TPK_SMEM_WORDS
 #define KVQ_TPK_SMEM_WORDS 2048          // packed template codes up to this size are staged in shared memory
+#endif
 #define KVQ_TILE (KVQ_OWN_ROWS * KVQ_ROW) // bytes of a segment owned by one tile (host builds the tile table)
 
 // 2-bit code of a raw byte: A->0 C->1 T->2 G->3; any other byte maps to *some* code.  Equal
@@ -48,7 +55,13 @@ struct KvqTemplates {
     int32_t nseqs, n_exh;
     // seed tables: presence per 16-bit key (T1: one byte per key, T2: one bit per key), CSR
     // offsets per key and entries {seq, toff | len << 16, packed_off, byte_off}
+    // *_first[key] = first bucket entry {seq | more << 24, toff | len << 16, packed_off, overflow index}:
+    // `more` further entries of the bucket start at *_ent[overflow index] (more == 255: the count is
+    // in *_ent[overflow index - 1].x)
+    const uint4 *t1_first, *t2_first;
     const uint8_t *t1_present; const uint32_t *t1_off; const uint4 *t1_ent;   // template-piece seeds
+    const uint8_t *t1_digest;           // per key: codes of the 3 bases after the piece 8-mer, 0xFF = do not filter
+    const uint32_t *t2l_bitmap;         // T2 presence restricted to templates longer than short_max
     const uint32_t *t2_bitmap, *t2_off; const uint4 *t2_ent;                  // every template offset
     const int16_t *p2_tab;              // [KVQ_MAXRL_FAST+1][KVQ_P2W] T2 probe offsets per read length, -1 = unused
     const uint32_t *cov_off;            // [nplus+1] offset of each plus template in coverage[]
@@ -61,8 +74,8 @@ struct KvqBatch {
     const int64_t *seg_off;             // [nseg+1] record-aligned cuts (reference chunk emulation)
     int32_t nseg;
     int64_t base_fpos;                  // stream offset of data[0]
-    const int64_t *tile_off;            // [ntiles] start of every tile (KVQ_TILE bytes of one segment)
-    const int32_t *tile_seg;            // [ntiles] owning segment
+    const longlong2 *tile_info;         // [ntiles] {start of the tile (KVQ_TILE bytes of one segment),
+                                        //           end of its segment | first tile of the segment << 62}
     uint32_t *tile_status;              // [ntiles] look-back words, zeroed before the launch
     int32_t ntiles;
 };

@@ -1,7 +1,7 @@
 // sm_100a kernels of the KvarQ read-scanning path (reference: csrc/workhorse.c:976-1197).
 //
 // Persistent kernel, one CTA per SM, every WARP an independent worker (no block-wide barrier in
-// the steady state).  A warp claims 8 KiB tiles of the FastQ stream in stream order from a global
+// the steady state).  A warp claims 10 KiB tiles of the FastQ stream in stream order from a global
 // queue and runs the whole path on its tile:
 //   P1  coalesced 128-bit loads, 32 bytes per lane; straight from registers every 32-byte word
 //       is reduced to three bit planes kept in shared memory: newline mask, quality-pass mask
@@ -25,15 +25,40 @@
 
 namespace {
 
-constexpr int NWARPS = 20;                  // warps per CTA (shared memory bound)
+#ifndef KVQ_NWARPS
+#define KVQ_NWARPS 16
+#endif
+#ifndef KVQ_DIGEST
+#define KVQ_DIGEST 0
+#endif
+#ifndef KVQ_PREFETCH
+#define KVQ_PREFETCH 1
+#endif
+#ifndef KVQ_NS
+#define KVQ_NS 1
+#endif
+#ifndef KVQ_INPASS
+#define KVQ_INPASS 1
+#endif
+#ifndef KVQ_NOINLINE_DRAIN
+#define KVQ_NOINLINE_DRAIN 0
+#endif
+#if KVQ_NOINLINE_DRAIN
+#define KVQ_DRAIN_ATTR __noinline__
+#else
+#define KVQ_DRAIN_ATTR
+#endif
+constexpr int NWARPS = KVQ_NWARPS;          // warps per CTA (shared memory bound)
 constexpr int THREADS = NWARPS * 32;
 constexpr int OWN_ROWS = KVQ_OWN_ROWS;
-constexpr int EXTRA_ROWS = 3;               // spill: records starting in the tile may end here
+constexpr int EXTRA_ROWS = 2;               // spill: records starting in the tile may end here
 constexpr int MAX_ROWS = OWN_ROWS + EXTRA_ROWS;
 constexpr int NWORDS = MAX_ROWS * 32;       // 32-byte words of the staged region
 constexpr int NLCAP = 144;                  // newline positions kept per round (32 records + slack)
 constexpr int MAXRL_FAST = KVQ_MAXRL_FAST;  // longer trimmed reads go to the long-record kernel
-constexpr int SEEDQ = 64;
+constexpr int NS = KVQ_NS;                  // seeds per lane and drain
+constexpr int DRAIN = 32 * NS;
+constexpr int SEEDQ = 128;
 
 struct WarpSmem {
     uint32_t nl[NWORDS + 1];                // newline plane, bit j of word w <=> byte 32 w + j is '\n'
@@ -43,11 +68,14 @@ struct WarpSmem {
     uint16_t nlpos[NLCAP];                  // positions of the newlines ranked [base, base + NLCAP)
     uint32_t rd[32];                        // reads of the round: start | length << 16 (0 = none)
     uint32_t seedq[SEEDQ];
+    uint32_t qn;                            // seeds reserved on the stack (may exceed SEEDQ until drained)
+    uint32_t pad;
 };
 
 struct Smem {
     uint8_t t1[KVQ_NKEYS];                  // T1 presence, one byte per key
     uint32_t bm2[KVQ_BITMAP_WORDS];         // T2 presence, one bit per key
+    uint32_t bm2l[KVQ_BITMAP_WORDS];        // T2 restricted to the long templates (whole-read probes)
     uint32_t hist[KVQ_HIST];
     uint32_t tpk[KVQ_TPK_SMEM_WORDS];       // packed template codes when they fit (else read through L1/L2)
     int longest;
@@ -219,23 +247,15 @@ __device__ __forceinline__ void reduce_row(WarpSmem &s, const TileCtx &t, const 
         uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
         if (lane >= o) inc += n;
     }
-    s.pre[w] = (uint16_t) (nl_total + inc - cnt);
+    uint32_t rank = nl_total + inc - cnt;
+    s.pre[w] = (uint16_t) rank;
     nl_total += __shfl_sync(0xffffffffu, inc, 31);
-}
-
-// P1 over rows [row0, row1): two rows of loads in flight
-template <bool NEG>
-__device__ __forceinline__ void stage_rows(WarpSmem &s, const KvqBatch &b, const TileCtx &t, int row0, int row1, int lane,
-                                           uint32_t cl, uint32_t &nl_total, uint32_t &nl_owned)
-{
-    Row r0 = load_row(b, t, row0, lane), r1 = load_row(b, t, row0 + 1, lane);
-#pragma unroll 1
-    for (int row = row0; row < row1; row++) {
-        Row r2 = r1;
-        if (row + 2 < row1) r2 = load_row(b, t, row + 2, lane);
-        reduce_row<NEG>(s, t, r0, row, lane, cl, nl_total, nl_owned);
-        r0 = r1; r1 = r2;
+#if KVQ_INPASS
+    while (nl && rank < NLCAP) {                    // positions of the first NLCAP newlines (round 0)
+        s.nlpos[rank++] = (uint16_t) ((w << 5) + __ffs(nl) - 1);
+        nl &= nl - 1;
     }
+#endif
 }
 
 // positions of the newlines ranked [base, base + NLCAP), from the plane
@@ -260,6 +280,10 @@ __device__ __forceinline__ int count_owned_newlines(const KvqBatch &b, int64_t a
 {
     uint32_t cnt = 0;
     const uint4 *src = reinterpret_cast<const uint4 *>(b.data + a0);
+#if KVQ_PREFETCH
+    for (int x = lane * 128; x < tile_end; x += 32 * 128)           // whole tile on its way to L2
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(b.data + a0 + x));
+#endif
 #pragma unroll 3
     for (int row = 0; row <= OWN_ROWS; row++) {
         const int w = row * 32 + lane;
@@ -436,7 +460,7 @@ __device__ __forceinline__ int byte_mismatches(const uint8_t *a, const uint8_t *
 }
 
 // Exhaustive matcher: one warp per (read, seq) pair, lanes over all diagonals, raw bytes.
-__device__ void exhaustive_pair(const KvqParams &p, const KvqTemplates &t, const KvqOut &o,
+__device__ __noinline__ void exhaustive_pair(const KvqParams &p, const KvqTemplates &t, const KvqOut &o,
                                 const uint8_t *rd, int rl, int64_t file_pos, int sq, int lane)
 {
     const int sl = __ldg(t.len + sq);
@@ -450,6 +474,19 @@ __device__ void exhaustive_pair(const KvqParams &p, const KvqTemplates &t, const
     }
 }
 
+// A T1 seed (piece 8-mer found at read offset pos) is only followed when the 3 bases after it
+// agree with the template piece as well -- the pigeonhole piece matches over its whole length --
+// unless the table says the key's pieces are too short or disagree (digest 0xFF).
+// r16 = the 16 read bases from pos on.
+__device__ __forceinline__ bool t1_fires(const KvqTemplates &t, uint32_t r16, int pos, int rl)
+{
+#if !KVQ_DIGEST
+    return true;
+#endif
+    const uint32_t dg = __ldg(t.t1_digest + (r16 & 0xFFFFu));
+    return dg == 0xFFu || (pos + KVQ_SEED_K + 3 <= rl && ((r16 >> 16) & 0x3Fu) == dg);
+}
+
 // Is (kind, pos) the first seed, in the fixed order T1 pieces then T2 offsets, that fires on
 // diagonal d of (read, seq)?  Every firing seed reaches the same diagonal; only this one emits.
 // rpk = code plane, rb = base offset of the read in it.
@@ -460,17 +497,21 @@ __device__ __noinline__ bool canonical_seed(const KvqParams &p, const KvqTemplat
         const int toff = j * sl / p.npieces;
         const int pj = toff - d;
         if (pj < 0 || pj > rl - KVQ_SEED_K) continue;
-        if (((extract16(rpk, rb + pj) ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
+        const uint32_t r16 = extract16(rpk, rb + pj);
+        if (((r16 ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0 && t1_fires(t, r16, pj, rl))
             return kind == 0 && pos == pj;
     }
     const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
     for (int i = 0; i < p.n2max; i++) {
-        const int pp = __ldg(p2 + i);
-        if (pp < 0) continue;
+        const int pv = __ldg(p2 + i);
+        if (pv < 0) continue;
+        const int pp = pv & KVQ_P2_POS;
         const int toff = pp + d;
         if (toff < 0 || toff > sl - KVQ_SEED_K) continue;
-        if (((extract16(rpk, rb + pp) ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
-            return kind == 1 && pos == pp;
+        const uint32_t key = extract16(rpk, rb + pp) & 0xFFFFu;
+        if (key != (extract16_g(tpk, toff) & 0xFFFFu)) continue;
+        if ((pv & KVQ_P2_LONG) && !((__ldg(t.t2l_bitmap + (key >> 5)) >> (key & 31)) & 1u)) continue;
+        return kind == 1 && pos == pp;
     }
     return false;
 }
@@ -492,97 +533,143 @@ __device__ __forceinline__ uint32_t extract16_t(const uint32_t *pk, int b)      
 
 // ---- P4: seeds -> bucket entries -> code-space verify -> confirm + emit ------------------------
 // Seeds s.seedq[base, base + n), one per lane.  Seed = read | pos << 5 | kind << 15.
-__device__ void drain_seeds(WarpSmem &s, const Ctx &c, int base, int n, int lane, ThreadStats &ts)
+__device__ KVQ_DRAIN_ATTR int drain_seeds(WarpSmem &s, const Ctx &c, int base, int n, int lane)
 {
+    // Up to 64 seeds, two per lane, so that the table loads of both are in flight together.  A
+    // key's first bucket entry sits in a table addressed by the key itself (one load finds the
+    // candidate); further entries of the bucket follow in the overflow array.
     const KvqTemplates &t = c.t; const KvqParams &p = c.p;
-    uint32_t e0 = 0, e1 = 0;
-    int pos = 0, kind = 0, rd0 = 0, rl = 0;
-    if (lane < n) {
-        const uint32_t sd = s.seedq[base + lane];
-        const uint32_t rdv = s.rd[sd & 31];
-        pos = (int) ((sd >> 5) & 1023); kind = (int) (sd >> 15);
-        rd0 = (int) (rdv & 0xFFFFu); rl = (int) (rdv >> 16);
-        if (kind) pos = __ldg(t.p2_tab + rl * KVQ_P2W + pos);      // T2 seeds carry their probe slot
-        const uint32_t key = extract16(s.pk, rd0 + pos) & 0xFFFFu;
-        const uint32_t *off = kind ? t.t2_off : t.t1_off;
-        e0 = __ldg(off + key); e1 = __ldg(off + key + 1);
+    int ncand = 0;
+    uint4 nxt[NS];
+    int cnt[NS], pos[NS], kind[NS], rd0[NS], rl[NS];
+    uint32_t ovf[NS];
+#pragma unroll
+    for (int u = 0; u < NS; u++) {
+        cnt[u] = 0; pos[u] = 0; kind[u] = 0; rd0[u] = 0; rl[u] = 0; ovf[u] = 0;
+        nxt[u] = make_uint4(0, 0, 0, 0);
+        if (lane + 32 * u < n) {
+            const uint32_t sd = s.seedq[base + lane + 32 * u];
+            const uint32_t rdv = s.rd[sd & 31];
+            pos[u] = (int) ((sd >> 5) & 1023); kind[u] = (int) (sd >> 15);
+            rd0[u] = (int) (rdv & 0xFFFFu); rl[u] = (int) (rdv >> 16);
+            if (kind[u]) pos[u] = __ldg(t.p2_tab + rl[u] * KVQ_P2W + pos[u]) & KVQ_P2_POS;   // T2 seeds carry their probe slot
+            const uint32_t r16 = extract16(s.pk, rd0[u] + pos[u]);
+            if (kind[u] || KVQ_DIGEST != 1 || t1_fires(t, r16, pos[u], rl[u])) {
+                nxt[u] = __ldg((kind[u] ? t.t2_first : t.t1_first) + (r16 & 0xFFFFu));
+                cnt[u] = 1;
+            }
+        }
     }
     __syncwarp();
-    const uint4 *ent = kind ? t.t2_ent : t.t1_ent;
-    for (;;) {
-        const bool has = e0 < e1;
-        if (!__any_sync(0xffffffffu, has)) break;
-        bool surv = false;
-        uint4 en = make_uint4(0, 0, 0, 0);
-        int d = 0;
-        if (has) {
-            en = __ldg(ent + e0); e0++;
-            const int sl = (int) (en.y >> 16);
-            d = (int) (en.y & 0xFFFFu) - pos;
-            // overlap of the diagonal; Hamming distance in code space first (a lower bound of the
-            // byte distance, most candidates die on the first word), the acceptance rule after
-            const int ro = d < 0 ? -d : 0, to = d > 0 ? d : 0;
-            const int L = min(rl - ro, sl - to);
-            const uint32_t *tpk = c.tpk + en.z;
-            int e = 0;
-            for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
-                uint32_t x = extract16(s.pk, rd0 + ro + j) ^ extract16_t(tpk, to + j);
-                uint32_t m = (x | (x >> 1)) & 0x55555555u;
-                if (L - j < 16) m &= (1u << (2 * (L - j))) - 1u;
-                e += __popc(m);
-            }
-            if (e <= p.maxerrors) {
-                int ro2, to2, L2, rule;
-                surv = diag_rule(d, rl, sl, p.minoverlap, ro2, to2, L2, rule) != 0;
-            }
-            ts.cands++;
+#pragma unroll
+    for (int u = 0; u < NS; u++)
+        if (cnt[u]) {                               // bucket size: 1 + entries in the overflow array
+            uint32_t more = nxt[u].x >> 24;
+            ovf[u] = nxt[u].w;
+            if (more == 255u) more = __ldg(&(kind[u] ? t.t2_ent : t.t1_ent)[ovf[u] - 1].x);
+            cnt[u] = 1 + (int) more;
         }
-        uint32_t m = __ballot_sync(0xffffffffu, surv);
-        while (m) {                                 // warp-wide: byte-exact confirm, dedupe, emit
-            const int src = __ffs(m) - 1;
-            m &= m - 1;
-            const int sq = (int) __shfl_sync(0xffffffffu, en.x, src);
-            const uint32_t y = __shfl_sync(0xffffffffu, en.y, src);
-            const uint32_t poff = __shfl_sync(0xffffffffu, en.z, src);
-            const uint32_t boff = __shfl_sync(0xffffffffu, en.w, src);
-            const int dd = __shfl_sync(0xffffffffu, d, src);
-            const int bpos = __shfl_sync(0xffffffffu, pos, src), bkind = __shfl_sync(0xffffffffu, kind, src);
-            const int brd0 = __shfl_sync(0xffffffffu, rd0, src), brl = __shfl_sync(0xffffffffu, rl, src);
-            const int sl = (int) (y >> 16);
-            int ro, to, L, rule;
-            const int copies = diag_rule(dd, brl, sl, p.minoverlap, ro, to, L, rule);
-            const uint8_t *rdp = c.b.data + c.tc.a0 + brd0;
-            const uint8_t *tp = t.bytes + boff;
-            int e = 0;
-            for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
-            e = __reduce_add_sync(0xffffffffu, e);
-            if (e > p.maxerrors) continue;
-            if (!canonical_seed(p, t, s.pk, brd0, t.packed + poff, brl, sl, dd, bkind, bpos)) continue;
-            emit_hit_warp(t, p, c.o, sq, dd, ro, to, L, brl, sl, c.b.base_fpos + c.tc.a0 + brd0, rdp, tp,
-                          copies, rule, lane);
+    for (;;) {
+        int alive = 0;
+#pragma unroll
+        for (int u = 0; u < NS; u++) alive |= cnt[u];
+        if (!__any_sync(0xffffffffu, alive != 0)) break;
+        uint4 en[NS]; int d[NS]; bool surv[NS];
+#pragma unroll
+        for (int u = 0; u < NS; u++) {
+            en[u] = nxt[u]; d[u] = 0; surv[u] = false;
+            if (cnt[u]) {
+                if (--cnt[u]) nxt[u] = __ldg((kind[u] ? t.t2_ent : t.t1_ent) + ovf[u]++);      // next entry in flight
+                const int sl = (int) (en[u].y >> 16);
+                d[u] = (int) (en[u].y & 0xFFFFu) - pos[u];
+                // overlap of the diagonal; Hamming distance in code space first (a lower bound of the
+                // byte distance, most candidates die on the first word), the acceptance rule after
+                const int ro = d[u] < 0 ? -d[u] : 0, to = d[u] > 0 ? d[u] : 0;
+                const int L = min(rl[u] - ro, sl - to);
+                const uint32_t *tpk = c.tpk + en[u].z;
+                int e = 0;
+                for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
+                    uint32_t x = extract16(s.pk, rd0[u] + ro + j) ^ extract16_t(tpk, to + j);
+                    uint32_t m = (x | (x >> 1)) & 0x55555555u;
+                    if (L - j < 16) m &= (1u << (2 * (L - j))) - 1u;
+                    e += __popc(m);
+                }
+                if (e <= p.maxerrors) {
+                    int ro2, to2, L2, rule;
+                    surv[u] = diag_rule(d[u], rl[u], sl, p.minoverlap, ro2, to2, L2, rule) != 0;
+                }
+                ncand++;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < NS; u++) {
+            uint32_t m = __ballot_sync(0xffffffffu, surv[u]);
+            while (m) {                             // warp-wide: byte-exact confirm, dedupe, emit
+                const int src = __ffs(m) - 1;
+                m &= m - 1;
+                const int sq = (int) (__shfl_sync(0xffffffffu, en[u].x, src) & 0xFFFFFFu);
+                const uint32_t y = __shfl_sync(0xffffffffu, en[u].y, src);
+                const uint32_t poff = __shfl_sync(0xffffffffu, en[u].z, src);
+                const int dd = __shfl_sync(0xffffffffu, d[u], src);
+                const int bpos = __shfl_sync(0xffffffffu, pos[u], src), bkind = __shfl_sync(0xffffffffu, kind[u], src);
+                const int brd0 = __shfl_sync(0xffffffffu, rd0[u], src), brl = __shfl_sync(0xffffffffu, rl[u], src);
+                const int sl = (int) (y >> 16);
+                int ro, to, L, rule;
+                const int copies = diag_rule(dd, brl, sl, p.minoverlap, ro, to, L, rule);
+                const uint8_t *rdp = c.b.data + c.tc.a0 + brd0;
+                const uint8_t *tp = t.bytes + __ldg(t.byte_off + sq);
+                int e = 0;
+                for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
+                e = __reduce_add_sync(0xffffffffu, e);
+                if (e > p.maxerrors) continue;
+                if (!canonical_seed(p, t, s.pk, brd0, t.packed + poff, brl, sl, dd, bkind, bpos)) continue;
+                emit_hit_warp(t, p, c.o, sq, dd, ro, to, L, brl, sl, c.b.base_fpos + c.tc.a0 + brd0, rdp, tp,
+                              copies, rule, lane);
+            }
         }
     }
+    return ncand;
 }
 
-// Push the set bits of every lane's `hits` (bit j = read offset posbase + j) on the seed stack;
-// whenever 32 seeds are waiting they are drained with all lanes busy.
-__device__ __forceinline__ void push_seeds(WarpSmem &s, const Ctx &c, int &qn, uint32_t hits, uint32_t tag,
-                                           int posbase, int lane, ThreadStats &ts)
+// Drain the first n seeds of the stack 64 at a time.
+__device__ __forceinline__ void drain_chunks(WarpSmem &s, const Ctx &c, int n, int lane, ThreadStats &ts)
+{
+    for (int done = 0; done < n; done += DRAIN)
+        ts.cands += (unsigned long long) drain_seeds(s, c, done, min(DRAIN, n - done), lane);
+}
+
+// Push the set bits of every lane's `hits` (bit j = read offset posbase + j) on the seed stack:
+// a lane reserves room with one shared-memory atomic.  Whenever 32 seeds are waiting they are
+// drained with all lanes busy; what does not fit the stack waits for the drain.
+__device__ __forceinline__ void push_seeds(WarpSmem &s, const Ctx &c, uint32_t hits, uint32_t tag,
+                                           int posbase, bool flush, int lane, ThreadStats &ts)
 {
     for (;;) {
-        const uint32_t any = __ballot_sync(0xffffffffu, hits != 0);
-        if (!any) break;
         if (hits) {
-            const int j = __ffs(hits) - 1;
-            hits &= hits - 1;
-            s.seedq[qn + __popc(any & ((1u << lane) - 1u))] = tag | ((uint32_t) (posbase + j) << 5);
+            uint32_t at = atomicAdd(&s.qn, (uint32_t) __popc(hits));
+            while (hits && at < SEEDQ) {
+                const int j = __ffs(hits) - 1;
+                hits &= hits - 1;
+                s.seedq[at++] = tag | ((uint32_t) (posbase + j) << 5);
+            }
         }
-        qn += __popc(any);
         __syncwarp();
-        if (qn >= 32) {
-            drain_seeds(s, c, qn - 32, 32, lane, ts);
-            qn -= 32;
-        }
+        const uint32_t q = s.qn;
+        const uint32_t left = __ballot_sync(0xffffffffu, hits != 0);       // only when the stack is full
+        if (q < DRAIN && !left && !(flush && q)) break;
+        const int stored = q < SEEDQ ? (int) q : SEEDQ;
+        const int take = (left || flush) ? stored : (stored & ~(DRAIN - 1));
+        drain_chunks(s, c, take, lane, ts);
+        const int rem = stored - take;                                      // < DRAIN, moves to the front
+        uint32_t keep[NS];
+#pragma unroll
+        for (int u = 0; u < NS; u++) keep[u] = lane + 32 * u < rem ? s.seedq[take + lane + 32 * u] : 0u;
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < NS; u++) if (lane + 32 * u < rem) s.seedq[lane + 32 * u] = keep[u];
+        if (lane == 0) s.qn = (uint32_t) rem;
+        __syncwarp();
+        if (!left) break;
     }
 }
 
@@ -668,42 +755,52 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
     const int k = k0 + lane;
     const uint32_t rdv = parse_record(s, sh, c, k, 4 * k + off - 1 - base, k < nown, n_all, off, at_seg_end, lane, ts);
     s.rd[lane] = rdv;
+#ifdef KVQ_ONLY_P2
+    return;
+#endif
     __syncwarp();
     if (!__any_sync(0xffffffffu, rdv != 0)) return;
     const int rd0 = (int) (rdv & 0xFFFFu), rl = (int) (rdv >> 16);
     const bool seeded = p.seed_ok && t.n_exh < t.nseqs;
     const bool seedable = seeded && rdv != 0 && rl >= p.min_seed_rl;
     if (seeded) {
-        int qn = 0;
-        // T1: every read offset rd0 .. rd0 + rl - 8, one 32-byte word of the code plane per step
+        // T2: a few fixed offsets per read (whole-read / head / tail pieces), table per read length
+        uint32_t hit2 = 0;
+        if (seedable) {
+            const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
+            for (int i = 0; i < p.n2max; i++) {
+                const int pv = __ldg(p2 + i);
+                if (pv < 0) continue;
+                const uint32_t key = extract16(s.pk, rd0 + (pv & KVQ_P2_POS)) & 0xFFFFu;
+                const uint32_t *bm = (pv & KVQ_P2_LONG) ? sh.bm2l : sh.bm2;
+                hit2 |= ((bm[key >> 5] >> (key & 31)) & 1u) << i;
+            }
+        }
+        // T1: every read offset rd0 .. rd0 + rl - 8, one 32-byte word of the code plane per step;
+        // the last step pushes the T2 seeds and flushes the stack (one push / drain site)
         const int w0 = rd0 >> 5, plast = rd0 + rl - KVQ_SEED_K;
         const int nw = seedable ? (plast >> 5) - w0 + 1 : 0;
         const int maxnw = __reduce_max_sync(0xffffffffu, nw);
-        for (int q = 0; q < maxnw; q++) {
-            uint32_t hits = 0;
+        for (int q = 0; q <= maxnw; q++) {
+            uint32_t hits = 0, tag = (uint32_t) lane;
             const int w = w0 + q;
+            int posbase = (w << 5) - rd0;
             if (q < nw) {
                 const uint2 x = reinterpret_cast<const uint2 *>(s.pk)[w];
                 hits = probe_word(sh.t1, x.x, x.y, s.pk[2 * w + 2]);
                 const int lo = rd0 - (w << 5), hi = plast - (w << 5);
                 if (lo > 0) hits &= 0xFFFFFFFFu << lo;
                 if (hi < 31) hits &= (2u << hi) - 1u;
+#if KVQ_DIGEST == 2
+                for (uint32_t m = hits; m; m &= m - 1) {    // drop seeds whose piece does not go on in the read
+                    const int j = __ffs(m) - 1;
+                    if (!t1_fires(t, extract16(s.pk, (w << 5) + j), (w << 5) + j - rd0, rl)) hits &= ~(1u << j);
+                }
+#endif
             }
-            push_seeds(s, c, qn, hits, (uint32_t) lane, (w << 5) - rd0, lane, ts);
+            if (q == maxnw) { hits = hit2; tag |= 1u << 15; posbase = 0; }
+            push_seeds(s, c, hits, tag, posbase, q == maxnw, lane, ts);
         }
-        // T2: a few fixed offsets per read (whole-read / head / tail pieces), table per read length
-        uint32_t hit2 = 0;
-        if (seedable) {
-            const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
-            for (int i = 0; i < p.n2max; i++) {
-                const int pos = __ldg(p2 + i);
-                if (pos < 0) continue;
-                const uint32_t key = extract16(s.pk, rd0 + pos) & 0xFFFFu;
-                hit2 |= ((sh.bm2[key >> 5] >> (key & 31)) & 1u) << i;
-            }
-        }
-        push_seeds(s, c, qn, hit2, (uint32_t) lane | (1u << 15), 0, lane, ts);
-        if (qn) drain_seeds(s, c, 0, qn, lane, ts);
     }
     // exhaustive matcher: reads the seed scheme does not cover against every template, the
     // others against the templates it does not cover
@@ -747,7 +844,10 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         const uint4 *src = reinterpret_cast<const uint4 *>(t.t1_present);
         uint4 *dst = reinterpret_cast<uint4 *>(sh.t1);
         for (int i = threadIdx.x; i < KVQ_NKEYS / 16; i += THREADS) dst[i] = __ldg(src + i);
-        for (int i = threadIdx.x; i < KVQ_BITMAP_WORDS; i += THREADS) sh.bm2[i] = __ldg(t.t2_bitmap + i);
+        for (int i = threadIdx.x; i < KVQ_BITMAP_WORDS; i += THREADS) {
+            sh.bm2[i] = __ldg(t.t2_bitmap + i); sh.bm2l[i] = __ldg(t.t2l_bitmap + i);
+        }
+        if (lane == 0) s.qn = 0;
         for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS) sh.hist[i] = 0;
         if (t.packed_words <= KVQ_TPK_SMEM_WORDS)
             for (int i = threadIdx.x; i < t.packed_words; i += THREADS) sh.tpk[i] = __ldg(t.packed + i);
@@ -760,30 +860,29 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
 
     // Tile geometry + look-ahead: claim the next tile, count the newlines of the bytes it owns
     // and publish them (status word, see resolve_phase) before the current tile is processed.
-    struct Claim { int tile; int n_tile; };
+    struct Claim { int tile; int n_tile; int first; int64_t t0, seg_end; };
     auto claim = [&]() -> Claim {
         int tile = 0;
         if (lane == 0) tile = (int) atomicAdd(&o.ctr->tile_next, 1u);
         tile = __shfl_sync(0xffffffffu, tile, 0);
-        if (tile >= b.ntiles) return Claim{-1, 0};
-        const int seg = __ldg(b.tile_seg + tile);
-        const int64_t t0 = __ldg(b.tile_off + tile);
-        const int64_t seg_beg = __ldg(b.seg_off + seg), seg_end = __ldg(b.seg_off + seg + 1);
+        if (tile >= b.ntiles) return Claim{-1, 0, 0, 0, 0};
+        const longlong2 ti = __ldg(b.tile_info + tile);            // {start, segment end | first << 62}
+        const int64_t t0 = ti.x, seg_end = ti.y & ~(1ll << 62);
+        const int first = (int) ((ti.y >> 62) & 1);
         const int64_t a0 = t0 & ~(int64_t) 31;
         const int64_t t1 = t0 + KVQ_TILE < seg_end ? t0 + KVQ_TILE : seg_end;
         const int n = count_owned_newlines(b, a0, (int) (t0 - a0), (int) (t1 - a0), lane);
         if (lane == 0)
-            ((volatile uint32_t *) b.tile_status)[tile] = (t0 == seg_beg ? 8u : 4u) | (uint32_t) (n & 3);
-        return Claim{tile, n};
+            ((volatile uint32_t *) b.tile_status)[tile] = (first ? 8u : 4u) | (uint32_t) (n & 3);
+        return Claim{tile, n, first, t0, seg_end};
     };
 
-    Claim cur = claim();
-    while (cur.tile >= 0) {
-        const Claim nxt = claim();
+    Claim cur{-2, 0, 0, 0, 0};                      // -2: nothing claimed yet, -1: queue exhausted
+    for (;;) {
+        const Claim nxt = claim();                  // the one look-ahead site (code size matters here)
+        if (cur.tile >= 0) {
         const int tile = cur.tile;
-        const int seg = __ldg(b.tile_seg + tile);
-        const int64_t t0 = __ldg(b.tile_off + tile);
-        const int64_t seg_beg = __ldg(b.seg_off + seg), seg_end = __ldg(b.seg_off + seg + 1);
+        const int64_t t0 = cur.t0, seg_end = cur.seg_end;
         TileCtx tc;
         tc.a0 = t0 & ~(int64_t) 31;
         tc.shift = (int) (t0 - tc.a0);
@@ -791,14 +890,11 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         tc.tile_end = (int) (t1 - tc.a0);
         const int64_t lim = seg_end - tc.a0;
         tc.lim = lim < (int64_t) MAX_ROWS * KVQ_ROW ? (int) lim : MAX_ROWS * KVQ_ROW;
-        tc.first = (t0 == seg_beg);
+        tc.first = cur.first;
         tc.seg_end = seg_end;
         const Ctx c{b, t, p, o, tc, tpk};
 
-        // P1: rows 0 .. OWN_ROWS (the tile plus one row of spill)
-        uint32_t n_all = 0, n_own = 0;
-        int nrows = OWN_ROWS + 1;
-        stage_rows<NEG>(s, b, tc, 0, nrows, lane, cl, n_all, n_own);
+        // line phase of the tile (its count was published one tile ago), then the owned records
         const int n_tile = cur.n_tile;
         const int phase = resolve_phase(b, tile, tc.first, n_tile, lane);
         // newline rank -> record-relative numbering (see parse_record)
@@ -806,21 +902,42 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         const int vmax_tile = n_tile - 1 - off;
         int nown = 0;
         if (tc.first || vmax_tile >= -1) nown = (vmax_tile + 1) / 4 + 1;
-        // spill rows while the last owned record is incomplete and the segment goes on
-        while (nrows < MAX_ROWS && nown > 0 && 4 * (nown - 1) + 3 + off >= (int) n_all && nrows * KVQ_ROW < tc.lim) {
-            stage_rows<NEG>(s, b, tc, nrows, nrows + 1, lane, cl, n_all, n_own);
-            nrows++;
+        const int need = nown > 0 ? 4 * (nown - 1) + 3 + off : -1;  // rank of the last newline the tile needs
+
+        // P1: rows 0 .. OWN_ROWS (the tile plus one row of spill) with two rows of loads in
+        // flight, then further spill rows while the last owned record is incomplete
+        uint32_t n_all = 0, n_own = 0;
+        int nrows = 0;
+        {
+            Row r0 = load_row(b, tc, 0, lane), r1 = load_row(b, tc, 1, lane);
+#pragma unroll 1
+            for (int row = 0; row < MAX_ROWS; row++) {
+                if (row > OWN_ROWS) {
+                    if (need < (int) n_all || row * KVQ_ROW >= tc.lim) break;
+                    r0 = load_row(b, tc, row, lane);
+                }
+                Row r2 = r1;
+                if (row + 2 <= OWN_ROWS) r2 = load_row(b, tc, row + 2, lane);
+                reduce_row<NEG>(s, tc, r0, row, lane, cl, n_all, n_own);
+                r0 = r1; r1 = r2;
+                nrows = row + 1;
+            }
         }
         const bool at_seg_end = tc.a0 + (int64_t) nrows * KVQ_ROW >= seg_end;
+#ifdef KVQ_ONLY_P1
+        if (n_all == 0x7fffffff)
+#endif
         for (int k0 = 0; k0 < nown; k0 += 32) {
             const int base = k0 > 0 ? 4 * k0 + off - 1 : 0;
             __syncwarp();
-            scatter_newlines(s, nrows, base, lane);
+            if (k0 > 0 || !KVQ_INPASS) scatter_newlines(s, nrows, base, lane);
             __syncwarp();
             run_round(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
         }
         __syncwarp();                               // planes are reused by the next tile
+        }
         cur = nxt;
+        if (cur.tile < 0) break;
     }
 
     // flush the statistics: warp-reduce the per-thread counters, one atomic per warp
