@@ -404,7 +404,7 @@ struct TemplateSet {
     std::vector<int32_t> len;
     KvqTemplates dev{}; KvqParams par{};
     DevBuf d_bytes, d_boff, d_packed, d_poff, d_len, d_seedable, d_exh;
-    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2, d_dg1, d_bm2l, d_first1, d_first2;
+    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2, d_bm2l, d_first1, d_first2;
 
     static unsigned char comp(unsigned char c) {
         switch (c) { case 'A': return 'T'; case 'T': return 'A'; case 'C': return 'G'; case 'G': return 'C'; default: return c; }
@@ -447,9 +447,6 @@ struct TemplateSet {
         std::vector<uint8_t> bytes; std::vector<uint32_t> boff(n + 1, 0), packed, poff(n + 1, 0);
         std::vector<uint8_t> seedable(n, 0); std::vector<int32_t> exh;
         std::vector<std::pair<uint32_t, uint4>> it1, it2;
-        // T1 digest: codes of the 3 bases that follow a piece's 8-mer inside the piece; 0xFF when a
-        // piece is shorter than 11 bases or two pieces with the same key disagree (no filtering)
-        std::vector<uint8_t> dg1(KVQ_NKEYS, 0xFE);                  // 0xFE = key not seen yet
         // short / long template classes for the whole-read T2 probes: the long class holds at most
         // a quarter of the T2 entries (it is everything when no such split exists)
         int short_max = 0;
@@ -483,13 +480,7 @@ struct TemplateSet {
             auto entry = [&](int toff) { return make_uint4((unsigned) i, (unsigned) toff | ((unsigned) sl << 16), poff[i], boff[i]); };
             for (int j = 0; j < pieces; j++) {
                 const int toff = (int) ((int64_t) j * sl / pieces);
-                const int tnext = (int) ((int64_t) (j + 1) * sl / pieces);         // piece j = [toff, tnext)
-                const uint32_t key = kmer_key(s + toff);
-                it1.push_back({key, entry(toff)});
-                uint8_t dg = 0xFF;
-                if (tnext - toff >= KVQ_SEED_K + 3)
-                    dg = (uint8_t) (code_of(s[toff + 8]) | (code_of(s[toff + 9]) << 2) | (code_of(s[toff + 10]) << 4));
-                dg1[key] = dg1[key] == 0xFE ? dg : (dg1[key] == dg ? dg : (uint8_t) 0xFF);
+                it1.push_back({kmer_key(s + toff), entry(toff)});
             }
             for (int toff = 0; toff + KVQ_SEED_K <= sl; toff++) {
                 const uint32_t key = kmer_key(s + toff);
@@ -508,7 +499,7 @@ struct TemplateSet {
         upload(d_len, len); upload(d_seedable, seedable); upload(d_exh, exh);
         upload(d_bm1, t1.present); upload(d_off1, t1.off); upload(d_ent1, t1.ovf); upload(d_first1, t1.first);
         upload(d_bm2, t2.bitmap); upload(d_off2, t2.off); upload(d_ent2, t2.ovf); upload(d_first2, t2.first);
-        upload(d_dg1, dg1); upload(d_bm2l, bm2l);
+        upload(d_bm2l, bm2l);
         upload(d_covoff, covoff);
 
         dev.bytes = d_bytes.as<uint8_t>(); dev.byte_off = d_boff.as<uint32_t>();
@@ -518,7 +509,7 @@ struct TemplateSet {
         dev.t1_present = d_bm1.as<uint8_t>(); dev.t1_off = d_off1.as<uint32_t>(); dev.t1_ent = d_ent1.as<uint4>();
         dev.t2_bitmap = d_bm2.as<uint32_t>(); dev.t2_off = d_off2.as<uint32_t>(); dev.t2_ent = d_ent2.as<uint4>();
         dev.t1_first = d_first1.as<uint4>(); dev.t2_first = d_first2.as<uint4>();
-        dev.t1_digest = d_dg1.as<uint8_t>(); dev.t2l_bitmap = d_bm2l.as<uint32_t>();
+        dev.t2l_bitmap = d_bm2l.as<uint32_t>();
         dev.cov_off = d_covoff.as<uint32_t>(); dev.nplus = np;
 
         par.maxerrors = E; par.minoverlap = O; par.minreadlength = cfg.minreadlength;
@@ -550,7 +541,7 @@ struct TemplateSet {
                         if ((row[i] & KVQ_P2_POS) == v) { if (!lng) row[i] = (int16_t) v; return; }
                     row[nn++] = (int16_t) (v | (lng ? KVQ_P2_LONG : 0));
                 };
-                if (max_len >= rl) for (int j = 0; j < pieces; j++) add((int) ((int64_t) j * rl / pieces), rl > short_max);
+                if (max_len >= rl) for (int j = 0; j < pieces; j++) add((int) ((int64_t) j * rl / pieces), KVQ_T2L && rl > short_max);
                 if (rl > O) {
                     for (int j = 0; j < pieces; j++) add(par.o_piece[j], false);
                     for (int j = 0; j < pieces; j++) add(rl - O + par.o_piece[j], false);

@@ -16,7 +16,10 @@
 #define KVQ_P2_LONG 0x4000              // ... | flag: only templates longer than the short class can match here
 #define KVQ_ROW 1024                    // bytes one warp loads per step (32 lanes x 32 bytes)
 #ifndef KVQ_OWN_ROWS
-#define KVQ_OWN_ROWS 10
+#define KVQ_OWN_ROWS 8
+#endif
+#ifndef KVQ_T2L
+#define KVQ_T2L 1                       // separate T2 bitmap of the long templates for whole-read probes
 #endif
 #ifndef KVQ_TPK_SMEM_WORDS
 #define KVQ_TPK_SMEM_WORDS 2048          // packed template codes up to this size are staged in shared memory
@@ -60,7 +63,6 @@ struct KvqTemplates {
     // in *_ent[overflow index - 1].x)
     const uint4 *t1_first, *t2_first;
     const uint8_t *t1_present; const uint32_t *t1_off; const uint4 *t1_ent;   // template-piece seeds
-    const uint8_t *t1_digest;           // per key: codes of the 3 bases after the piece 8-mer, 0xFF = do not filter
     const uint32_t *t2l_bitmap;         // T2 presence restricted to templates longer than short_max
     const uint32_t *t2_bitmap, *t2_off; const uint4 *t2_ent;                  // every template offset
     const int16_t *p2_tab;              // [KVQ_MAXRL_FAST+1][KVQ_P2W] T2 probe offsets per read length, -1 = unused

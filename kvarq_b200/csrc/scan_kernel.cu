@@ -1,7 +1,7 @@
 // sm_100a kernels of the KvarQ read-scanning path (reference: csrc/workhorse.c:976-1197).
 //
 // Persistent kernel, one CTA per SM, every WARP an independent worker (no block-wide barrier in
-// the steady state).  A warp claims 10 KiB tiles of the FastQ stream in stream order from a global
+// the steady state).  A warp claims 8 KiB tiles of the FastQ stream in stream order from a global
 // queue and runs the whole path on its tile:
 //   P1  coalesced 128-bit loads, 32 bytes per lane; straight from registers every 32-byte word
 //       is reduced to three bit planes kept in shared memory: newline mask, quality-pass mask
@@ -26,27 +26,13 @@
 namespace {
 
 #ifndef KVQ_NWARPS
-#define KVQ_NWARPS 16
-#endif
-#ifndef KVQ_DIGEST
-#define KVQ_DIGEST 0
+#define KVQ_NWARPS 20
 #endif
 #ifndef KVQ_PREFETCH
 #define KVQ_PREFETCH 1
 #endif
 #ifndef KVQ_NS
 #define KVQ_NS 1
-#endif
-#ifndef KVQ_INPASS
-#define KVQ_INPASS 1
-#endif
-#ifndef KVQ_NOINLINE_DRAIN
-#define KVQ_NOINLINE_DRAIN 0
-#endif
-#if KVQ_NOINLINE_DRAIN
-#define KVQ_DRAIN_ATTR __noinline__
-#else
-#define KVQ_DRAIN_ATTR
 #endif
 constexpr int NWARPS = KVQ_NWARPS;          // warps per CTA (shared memory bound)
 constexpr int THREADS = NWARPS * 32;
@@ -58,7 +44,7 @@ constexpr int NLCAP = 144;                  // newline positions kept per round 
 constexpr int MAXRL_FAST = KVQ_MAXRL_FAST;  // longer trimmed reads go to the long-record kernel
 constexpr int NS = KVQ_NS;                  // seeds per lane and drain
 constexpr int DRAIN = 32 * NS;
-constexpr int SEEDQ = 128;
+constexpr int SEEDQ = 2 * DRAIN;
 
 struct WarpSmem {
     uint32_t nl[NWORDS + 1];                // newline plane, bit j of word w <=> byte 32 w + j is '\n'
@@ -75,7 +61,9 @@ struct WarpSmem {
 struct Smem {
     uint8_t t1[KVQ_NKEYS];                  // T1 presence, one byte per key
     uint32_t bm2[KVQ_BITMAP_WORDS];         // T2 presence, one bit per key
+#if KVQ_T2L
     uint32_t bm2l[KVQ_BITMAP_WORDS];        // T2 restricted to the long templates (whole-read probes)
+#endif
     uint32_t hist[KVQ_HIST];
     uint32_t tpk[KVQ_TPK_SMEM_WORDS];       // packed template codes when they fit (else read through L1/L2)
     int longest;
@@ -250,12 +238,10 @@ __device__ __forceinline__ void reduce_row(WarpSmem &s, const TileCtx &t, const 
     uint32_t rank = nl_total + inc - cnt;
     s.pre[w] = (uint16_t) rank;
     nl_total += __shfl_sync(0xffffffffu, inc, 31);
-#if KVQ_INPASS
     while (nl && rank < NLCAP) {                    // positions of the first NLCAP newlines (round 0)
         s.nlpos[rank++] = (uint16_t) ((w << 5) + __ffs(nl) - 1);
         nl &= nl - 1;
     }
-#endif
 }
 
 // positions of the newlines ranked [base, base + NLCAP), from the plane
@@ -474,19 +460,6 @@ __device__ __noinline__ void exhaustive_pair(const KvqParams &p, const KvqTempla
     }
 }
 
-// A T1 seed (piece 8-mer found at read offset pos) is only followed when the 3 bases after it
-// agree with the template piece as well -- the pigeonhole piece matches over its whole length --
-// unless the table says the key's pieces are too short or disagree (digest 0xFF).
-// r16 = the 16 read bases from pos on.
-__device__ __forceinline__ bool t1_fires(const KvqTemplates &t, uint32_t r16, int pos, int rl)
-{
-#if !KVQ_DIGEST
-    return true;
-#endif
-    const uint32_t dg = __ldg(t.t1_digest + (r16 & 0xFFFFu));
-    return dg == 0xFFu || (pos + KVQ_SEED_K + 3 <= rl && ((r16 >> 16) & 0x3Fu) == dg);
-}
-
 // Is (kind, pos) the first seed, in the fixed order T1 pieces then T2 offsets, that fires on
 // diagonal d of (read, seq)?  Every firing seed reaches the same diagonal; only this one emits.
 // rpk = code plane, rb = base offset of the read in it.
@@ -498,7 +471,7 @@ __device__ __noinline__ bool canonical_seed(const KvqParams &p, const KvqTemplat
         const int pj = toff - d;
         if (pj < 0 || pj > rl - KVQ_SEED_K) continue;
         const uint32_t r16 = extract16(rpk, rb + pj);
-        if (((r16 ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0 && t1_fires(t, r16, pj, rl))
+        if (((r16 ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
             return kind == 0 && pos == pj;
     }
     const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
@@ -533,7 +506,7 @@ __device__ __forceinline__ uint32_t extract16_t(const uint32_t *pk, int b)      
 
 // ---- P4: seeds -> bucket entries -> code-space verify -> confirm + emit ------------------------
 // Seeds s.seedq[base, base + n), one per lane.  Seed = read | pos << 5 | kind << 15.
-__device__ KVQ_DRAIN_ATTR int drain_seeds(WarpSmem &s, const Ctx &c, int base, int n, int lane)
+__device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, int n, int lane)
 {
     // Up to 64 seeds, two per lane, so that the table loads of both are in flight together.  A
     // key's first bucket entry sits in a table addressed by the key itself (one load finds the
@@ -554,10 +527,8 @@ __device__ KVQ_DRAIN_ATTR int drain_seeds(WarpSmem &s, const Ctx &c, int base, i
             rd0[u] = (int) (rdv & 0xFFFFu); rl[u] = (int) (rdv >> 16);
             if (kind[u]) pos[u] = __ldg(t.p2_tab + rl[u] * KVQ_P2W + pos[u]) & KVQ_P2_POS;   // T2 seeds carry their probe slot
             const uint32_t r16 = extract16(s.pk, rd0[u] + pos[u]);
-            if (kind[u] || KVQ_DIGEST != 1 || t1_fires(t, r16, pos[u], rl[u])) {
-                nxt[u] = __ldg((kind[u] ? t.t2_first : t.t1_first) + (r16 & 0xFFFFu));
-                cnt[u] = 1;
-            }
+            nxt[u] = __ldg((kind[u] ? t.t2_first : t.t1_first) + (r16 & 0xFFFFu));
+            cnt[u] = 1;
         }
     }
     __syncwarp();
@@ -772,7 +743,11 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
                 const int pv = __ldg(p2 + i);
                 if (pv < 0) continue;
                 const uint32_t key = extract16(s.pk, rd0 + (pv & KVQ_P2_POS)) & 0xFFFFu;
+#if KVQ_T2L
                 const uint32_t *bm = (pv & KVQ_P2_LONG) ? sh.bm2l : sh.bm2;
+#else
+                const uint32_t *bm = sh.bm2;
+#endif
                 hit2 |= ((bm[key >> 5] >> (key & 31)) & 1u) << i;
             }
         }
@@ -791,12 +766,6 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
                 const int lo = rd0 - (w << 5), hi = plast - (w << 5);
                 if (lo > 0) hits &= 0xFFFFFFFFu << lo;
                 if (hi < 31) hits &= (2u << hi) - 1u;
-#if KVQ_DIGEST == 2
-                for (uint32_t m = hits; m; m &= m - 1) {    // drop seeds whose piece does not go on in the read
-                    const int j = __ffs(m) - 1;
-                    if (!t1_fires(t, extract16(s.pk, (w << 5) + j), (w << 5) + j - rd0, rl)) hits &= ~(1u << j);
-                }
-#endif
             }
             if (q == maxnw) { hits = hit2; tag |= 1u << 15; posbase = 0; }
             push_seeds(s, c, hits, tag, posbase, q == maxnw, lane, ts);
@@ -845,7 +814,10 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         uint4 *dst = reinterpret_cast<uint4 *>(sh.t1);
         for (int i = threadIdx.x; i < KVQ_NKEYS / 16; i += THREADS) dst[i] = __ldg(src + i);
         for (int i = threadIdx.x; i < KVQ_BITMAP_WORDS; i += THREADS) {
-            sh.bm2[i] = __ldg(t.t2_bitmap + i); sh.bm2l[i] = __ldg(t.t2l_bitmap + i);
+            sh.bm2[i] = __ldg(t.t2_bitmap + i);
+#if KVQ_T2L
+            sh.bm2l[i] = __ldg(t.t2l_bitmap + i);
+#endif
         }
         if (lane == 0) s.qn = 0;
         for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS) sh.hist[i] = 0;
@@ -930,7 +902,7 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         for (int k0 = 0; k0 < nown; k0 += 32) {
             const int base = k0 > 0 ? 4 * k0 + off - 1 : 0;
             __syncwarp();
-            if (k0 > 0 || !KVQ_INPASS) scatter_newlines(s, nrows, base, lane);
+            if (k0 > 0) scatter_newlines(s, nrows, base, lane);
             __syncwarp();
             run_round(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
         }
