@@ -265,13 +265,17 @@ def main():
     log('[rank %d] resident: %.3f ms/step wall, %.3f ms/step inside the C call, %.3f ms/step kernels, %d hits, %d records' %
         (rank, 1e3 * dt / args.steps, call_ms / args.steps, kernel_ms / args.steps, r.nhits, r['stats']['records_parsed']))
 
-    # ---- one NCCL reduce of the per-template counters (north_star; not in the timed region) --
+    # ---- one NCCL all-reduce of the per-template counters (north_star; not in the timed region) --
     if dist is not None:
-        import torch
-        cov = torch.tensor(r.coverage.tolist() + list(r['stats']['nseqhits']) + list(r['stats']['nseqbasehits']),
-                           dtype=torch.int64, device='cuda')
-        dist.all_reduce(cov, op=dist.ReduceOp.SUM)
-        log('[rank %d] NCCL all-reduce of %d counters: total coverage %d' % (rank, cov.numel(), int(cov[:len(r.coverage)].sum())))
+        import numpy as np
+        from kvarq_b200 import multi
+        flat, layout = multi.pack_counters(r.coverage, r.mutcount, r['stats']['nseqhits'], r['stats']['nseqbasehits'],
+                                           r['stats']['readlengths'], r['stats']['records_parsed'])
+        red = multi.unpack_counters(multi.all_reduce_counters(flat, dist, device='cuda'), layout)
+        assert red['records_parsed'] == world * r['stats']['records_parsed']
+        assert int(red['coverage'].sum()) == int(np.asarray(red['nseqbasehits']).sum())
+        log('[rank %d] NCCL all-reduce of %d int64 counters: %d records, total coverage %d' %
+            (rank, flat.size, red['records_parsed'], int(red['coverage'].sum())))
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region -----------------
     e2e_steps = args.e2e_steps or min(args.steps, 3)
