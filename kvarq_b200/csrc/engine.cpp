@@ -630,6 +630,7 @@ struct kvq_engine {
     Slot slots[NSLOT]; bool slots_ready = false;
     Accum acc;
     TemplateSet tpl;
+    PinBuf pin_out, pin_acc;                        // page-locked staging of the result copies
 
     void set_error(int cls, const std::string &m) { std::lock_guard<std::mutex> g(mu); err_cls = cls; err_msg = m; }
 };
@@ -752,9 +753,14 @@ void collect_hits(kvq_engine *e, const KvqBatch &b, DevBuf &d_ctr, DevBuf &d_hit
     if (nh == 0) return;
     const size_t h0 = tot.hits.size(), b0 = tot.blob.size();
     tot.hits.resize(h0 + nh); tot.blob.resize(b0 + nb);
-    CK(cudaMemcpyAsync(tot.hits.data() + h0, d_hits.p, nh * sizeof(KvqHitRec), cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(tot.blob.data() + b0, d_blob.p, nb, cudaMemcpyDeviceToHost, st));
+    // D2H through page-locked staging (DMA at full rate), then a plain copy into the result vectors
+    const size_t hbytes = nh * sizeof(KvqHitRec);
+    e->pin_out.ensure(((hbytes + 255) & ~(size_t) 255) + nb + 256);
+    char *ph = e->pin_out.as<char>(), *pb = ph + ((hbytes + 255) & ~(size_t) 255);
+    CK(cudaMemcpyAsync(ph, d_hits.p, hbytes, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(pb, d_blob.p, nb, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    memcpy(tot.hits.data() + h0, ph, hbytes); memcpy(tot.blob.data() + b0, pb, nb);
     for (size_t i = h0; i < h0 + nh; i++) tot.hits[i].blob_off += (int64_t) b0;
     tot.d2h += (int64_t) (nh * sizeof(KvqHitRec) + nb);
 }
@@ -801,16 +807,6 @@ private:
 
 // reference emission order for nthreads=1 (workhorse.c:1107-1175): file order, then template,
 // then (a) shifts descending, (b) shifts descending, (c)/(d) shifts ascending
-bool hit_before(const KvqHitRec &x, const KvqHitRec &y)
-{
-    if (x.file_pos != y.file_pos) return x.file_pos < y.file_pos;
-    if (x.seq_nr != y.seq_nr) return x.seq_nr < y.seq_nr;
-    if (x.rule != y.rule) return x.rule < y.rule;
-    const int ox = x.rule == 0 ? x.seq_pos : x.rule == 1 ? -x.seq_pos : std::abs(x.seq_pos);
-    const int oy = y.rule == 0 ? y.seq_pos : y.rule == 1 ? -y.seq_pos : std::abs(y.seq_pos);
-    return ox < oy;
-}
-
 std::string format_error_message(unsigned long long key)
 {
     // see report_format_error() in scan_kernel.cu; texts are workhorse.c:1039-1046
@@ -838,13 +834,42 @@ void fill_stats(kvq_engine *e, kvq_stats_t &st, const int64_t *rls, int64_t long
 
 kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
 {
+    const double t_fin = now_ms();
     std::unique_ptr<kvq_result> r(new kvq_result());
-    std::stable_sort(tot.hits.begin(), tot.hits.end(), hit_before);
+    // reference emission order: sort 24-byte keys, not the records
     const size_t nh = tot.hits.size();
+    struct Key { int64_t fpos; uint64_t k2; uint32_t idx; };
+    std::vector<Key> keys(nh);
+    for (size_t i = 0; i < nh; i++) {
+        const KvqHitRec &h = tot.hits[i];
+        const int o = h.rule == 0 ? h.seq_pos : h.rule == 1 ? -h.seq_pos : std::abs(h.seq_pos);
+        keys[i] = Key{h.file_pos, ((uint64_t) (uint32_t) h.seq_nr << 34) | ((uint64_t) (uint32_t) h.rule << 32)
+                                      | (uint64_t) (uint32_t) (o + (1 << 30)), (uint32_t) i};
+    }
+    auto before = [](const Key &a, const Key &b) {
+        return a.fpos != b.fpos ? a.fpos < b.fpos : a.k2 != b.k2 ? a.k2 < b.k2 : a.idx < b.idx; };
+    if (nh > 64) {
+        // hits spread evenly over the stream: one counting pass into nh buckets by file position,
+        // then a sort inside the (tiny) buckets
+        int64_t lo = keys[0].fpos, hi = keys[0].fpos;
+        for (const Key &k : keys) { lo = std::min(lo, k.fpos); hi = std::max(hi, k.fpos); }
+        const long double scale = (long double) nh / (long double) (hi - lo + 1);
+        std::vector<uint32_t> start(nh + 1, 0), bucket(nh);
+        for (size_t i = 0; i < nh; i++) { bucket[i] = (uint32_t) ((long double) (keys[i].fpos - lo) * scale); start[bucket[i] + 1]++; }
+        for (size_t i = 0; i < nh; i++) start[i + 1] += start[i];
+        std::vector<Key> sorted(nh);
+        std::vector<uint32_t> at(start.begin(), start.end() - 1);
+        for (size_t i = 0; i < nh; i++) sorted[at[bucket[i]]++] = keys[i];
+        for (size_t bk = 0; bk < nh; bk++)
+            if (start[bk + 1] - start[bk] > 1) std::sort(sorted.begin() + start[bk], sorted.begin() + start[bk + 1], before);
+        keys.swap(sorted);
+    } else {
+        std::sort(keys.begin(), keys.end(), before);
+    }
     r->hits.resize(nh); r->offsets.resize(nh + 1); r->blob.resize(tot.blob.size());
     int64_t at = 0;
     for (size_t i = 0; i < nh; i++) {
-        const KvqHitRec &h = tot.hits[i];
+        const KvqHitRec &h = tot.hits[keys[i].idx];
         r->hits[i] = kvq_hit_t{h.seq_nr, h.seq_pos, h.file_pos, h.length, h.readlength};
         r->offsets[i] = at;
         memcpy(r->blob.data() + at, tot.blob.data() + h.blob_off, h.length);
@@ -857,20 +882,21 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
     {
         const bool want_cov = e->tpl.nplus > 0 && nc > 0;
         const size_t words = want_cov ? e->acc.words() : 2 * e->acc.ns;
-        std::vector<int64_t> all(words);
-        CK(cudaMemcpy(all.data(), e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost));
+        e->pin_acc.ensure(words * 8);
+        CK(cudaMemcpy(e->pin_acc.p, e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost));
+        const int64_t *all = e->pin_acc.as<int64_t>();
         for (int i = 0; i < ns; i++) {
             r->nseqhits[i] = all[i]; r->nseqbasehits[i] = all[e->acc.ns + i];
             e->live.seqhits[i] = all[i]; e->live.seqbasehits[i] = all[e->acc.ns + i];
         }
         if (want_cov) {
-            r->coverage.assign(all.begin() + 2 * e->acc.ns, all.begin() + 2 * e->acc.ns + nc);
-            r->mutcount.assign(all.begin() + 2 * e->acc.ns + e->acc.nc, all.begin() + 2 * e->acc.ns + e->acc.nc + 6 * nc);
+            r->coverage.assign(all + 2 * e->acc.ns, all + 2 * e->acc.ns + nc);
+            r->mutcount.assign(all + 2 * e->acc.ns + e->acc.nc, all + 2 * e->acc.ns + e->acc.nc + 6 * nc);
             tot.d2h += nc * 56;
         }
     }
     tot.d2h += (int64_t) ns * 16;
-    r->timing.kernel_ms = tot.kernel_ms; r->timing.wall_ms = wall_ms; r->timing.launches = tot.launches;
+    r->timing.kernel_ms = tot.kernel_ms; r->timing.wall_ms = wall_ms + (now_ms() - t_fin); r->timing.launches = tot.launches;
     r->timing.h2d_bytes = tot.h2d; r->timing.d2h_bytes = tot.d2h; r->timing.bases = tot.bases;
     r->timing.stream_bytes = tot.stream_bytes; r->timing.exhaustive_reads = tot.exh; r->timing.candidates = tot.cands;
     return r.release();
@@ -1169,13 +1195,18 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         RunGuard run(e);
         if (!run.owns) throw KvqError(KVQ_ERR_RUNTIME, "findseqs() already running!");
         const double t_begin = now_ms();
+        static const bool trace = getenv("KVQ_TRACE") != nullptr;
+        double tp[8]; int ntp = 0;
+        auto mark = [&] { if (trace && ntp < 8) tp[ntp++] = now_ms(); };
         e->stop = 0;
         CK(cudaSetDevice(e->device));
         kvq_config_t cfg;
         { std::lock_guard<std::mutex> g(e->mu); cfg = e->cfg; e->live.reset(nseqs); }
         e->tpl.build(seqs, seqlens, nseqs, nplus, cfg);
         e->tpl.par.want_hits = want_hits ? 1 : 0;
+        mark();
         reset_accum(e);
+        mark();
         e->live.parsed = st->parsed; e->live.total = st->total;
         init_slots(e);                                  // borrow slot 0's stream and events
         Slot &s0 = e->slots[0];
@@ -1185,7 +1216,9 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         KvqOut o = make_out(e, st->d_ctr, st->d_hits, st->hit_cap, st->d_blob, st->blob_cap, st->d_longs, st->long_cap);
         enqueue_kernels(e, b, e->tpl.par, o, s0.stream, s0.ev0, s0.ev1);
         CK(cudaMemcpyAsync(s0.h_ctr.p, st->d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s0.stream));
+        mark();
         CK(cudaStreamSynchronize(s0.stream));
+        mark();
         float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1));
         tot.kernel_ms = ms; tot.launches = 2; tot.stream_bytes = st->nbytes; tot.d2h = sizeof(KvqCounters);
         const KvqCounters &c = *s0.h_ctr.as<KvqCounters>();
@@ -1193,8 +1226,14 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         if (want_hits)
             collect_hits(e, b, st->d_ctr, st->d_hits, st->hit_cap, st->d_blob, st->blob_cap, st->d_longs,
                          st->long_cap, c, s0.stream, tot);
+        mark();
         if (tot.err_key != ~0ULL) throw KvqError(KVQ_ERR_FASTQ_FORMAT, format_error_message(tot.err_key));
         *out = finish_result(e, tot, now_ms() - t_begin);
+        mark();
+        if (trace) {
+            fprintf(stderr, "[kvq trace] build %.3f reset %.3f enqueue %.3f sync %.3f hits %.3f finish %.3f (kernel %.3f)\n",
+                    tp[0] - t_begin, tp[1] - tp[0], tp[2] - tp[1], tp[3] - tp[2], tp[4] - tp[3], tp[5] - tp[4], ms);
+        }
     });
 }
 

@@ -3,7 +3,7 @@ sys.path.insert(0, '/root/repo')
 from kvarq_b200.engine import Engine
 from kvarq_b200 import synth
 g = synth.genome(); ts = synth.mtbc_templates(g, seed=1)
-fq = synth.fastq_reads(synth.isolate(g, ts, seed=7), 300000, readlen=150, seed=2)
+fq = synth.fastq_reads(synth.isolate(g, ts, seed=7), 3000000, readlen=150, seed=2)
 seqs = ts.seqs()
 e = Engine(0); e.config(maxerrors=2, minoverlap=25, minreadlength=25, Amin='.')
 st = e.stage([fq])
