@@ -403,3 +403,73 @@ def test_stats_and_stop_from_another_thread(gpu_engine, tmp_path):
     engine.stop()
     t.join()
     assert out['s']['stats']['records_parsed'] <= 300000
+
+
+def test_thousands_of_templates(gpu_engine, checker, tmp_path):
+    """BASELINE config 4 at test scale: a few thousand 51-bp templates (packed template codes no
+    longer fit shared memory, seed buckets overflow into the entry array), reads as in config 2."""
+    g = synth.genome(120000, seed=41)
+    rng = np.random.RandomState(42)
+    comp = bytes.maketrans(b'ACGT', b'TGCA')
+    plus = []
+    for p in sorted(rng.choice(len(g) - 60, 1500, replace=False)):
+        plus.append(bytes(g[p:p + 51]))
+    seqs = [s.decode() for s in plus] + [s.translate(comp)[::-1].decode() for s in plus]
+    fn = str(tmp_path / 'c4.fastq')
+    open(fn, 'wb').write(synth.fastq_reads(g, 1500, readlen=150, seed=43).tobytes())
+    from kvarq_b200.engine import Engine
+    e = Engine(0)
+    e.config(**DEFAULT)
+    got = e.findseqs(fn, seqs, nplus=len(plus))
+    want = oracle(checker, fn, seqs, DEFAULT, impl='oracle')
+    assert_same_result(got, want, what='3000 templates')
+    assert len(want['hits']) > 500
+    assert got.timing['exhaustive_reads'] == 0
+    cov, mut = coverage_from_hits(want['hits'], want['hitseqs'], seqs, len(plus))
+    assert got.coverage.tolist() == cov and got.mutcount.tolist() == mut
+    e.close()
+
+
+def test_huge_seed_buckets(gpu_engine, checker, tmp_path):
+    """Hundreds of templates sharing their k-mers: buckets beyond the 8-bit count of the first-entry
+    table (the count then sits in the overflow array), every read matching many templates."""
+    rng = random.Random(7)
+    core = ''.join(rng.choice('ACGT') for _ in range(60))
+    seqs = []
+    for i in range(300):
+        s = list(core[:51])
+        s[rng.randrange(51)] = rng.choice('ACGT')          # near-identical templates
+        seqs.append(''.join(s))
+    recs = []
+    for i in range(40):
+        L = rng.randint(60, 120)
+        left = ''.join(rng.choice('ACGT') for _ in range(rng.randint(0, L - 55)))
+        s = (left + core + ''.join(rng.choice('ACGT') for _ in range(L)))[:L]
+        recs.append('@r%d\n%s\n+\n%s\n' % (i, s, 'I' * L))
+    fn = str(tmp_path / 'hb.fastq')
+    open(fn, 'w').write(''.join(recs))
+    gpu_engine.config(**DEFAULT)
+    got = gpu_engine.findseqs(fn, seqs)
+    want = oracle(checker, fn, seqs, DEFAULT, impl='oracle')
+    assert_same_result(got, want, what='huge buckets')
+    assert len(want['hits']) > 3000
+
+
+def test_paired_end_250_gz(gpu_engine, checker, tmp_path):
+    """BASELINE config 3 at test scale: 2 x 250 bp, MiSeq-like quality decay (real trimming), two
+    gz files scanned as one stream with a continuing file_pos."""
+    g = synth.genome(150000, seed=51)
+    ts = synth.mtbc_templates(g, seed=52)
+    iso = synth.isolate(g, ts, seed=53)
+    files = []
+    for k in (1, 2):
+        fq = synth.fastq_reads(iso, 4000, readlen=250, seed=60 + k, qmean0=37.0 - 3 * (k - 1), qdrop=26.0, mate=k).tobytes()
+        fn = str(tmp_path / ('pe_%d.fastq.gz' % k))
+        with gzip.open(fn, 'wb', compresslevel=6) as f:
+            f.write(fq)
+        files.append(fn)
+    gpu_engine.config(**DEFAULT)
+    got = gpu_engine.findseqs(files, ts.seqs())
+    want = oracle(checker, files, ts.seqs(), DEFAULT)
+    assert_same_result(got, want, what='paired-end gz')
+    assert len(set(want['stats']['readlengths'])) > 3, 'quality trimming was not exercised'
