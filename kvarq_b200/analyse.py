@@ -259,3 +259,148 @@ def calls(template_set, coverages):
     if snpcov:
         out['remarks'] = depth_remarks(snpcov)
     return out
+
+
+# ------------------------------------------------------------------ result file
+VERSION = '0.12.2-b200'             # info.version: the reference writes kvarq.VERSION here
+
+
+def json_dump(data, fd, indent=2, max_indent_level=2):
+    """kvarq/util.py:272-294: indent=2 JSON whose levels deeper than `max_indent_level` are folded
+    onto one line (a coverage string, a hit, the readlengths tuple stay on their line).  Python 2's
+    encoder separates items by ', ' also when indenting; the separators are set to match."""
+    import json
+    import re
+    deep = indent * max_indent_level
+    fold = re.compile('^([\\[{,]? ?)\n {%d,}' % (deep + 1), re.MULTILINE)      # break into a deeper level
+    closing = re.compile('^\n {%d}$' % deep, re.MULTILINE)                      # break back to the last kept level
+    held = ''
+    for chunk in json.JSONEncoder(indent=2, separators=(', ', ': ')).iterencode(data):
+        if closing.match(chunk):
+            held = chunk
+            continue
+        if held and chunk not in ('}', ']', ','):
+            fd.write(held)
+        held = ''
+        fd.write(fold.sub('\\1', chunk))
+
+
+class Analyser(object):
+    """The scan -> coverages -> result-file part of kvarq/analyse.py:208-435 over named templates
+    (`OrderedDict name -> Sequence`; the reference derives them from testsuites,
+    load_coverages :261-282).  `scan` asks the engine for the fused arrays, so no Python loop
+    over hits is needed; `update_coverages` is the reference's loop, for results read back
+    from a file with hits."""
+
+    def __init__(self, spacing=25):
+        self.config = None
+        self.fastq_filenames = None
+        self.fastq_sizes = None
+        self.fastq_readlength = None
+        self.fastq_records_approx = None
+        self.spacing = spacing
+        self.hits = None
+        self.hitseqs = None
+        self.stats = None
+        self.scantime = 0
+        self.coverages = None
+        self.results = None
+        self.testsuite_versions = {}
+
+    def coverage_at(self, i):                                           # :284-294
+        n = len(self.coverages)
+        return list(self.coverages.values())[i - n if i >= n else i]
+
+    def get_indexes(self, name):                                        # :296-308
+        idx = list(self.coverages.keys()).index(str(name))
+        return [idx, idx + len(self.coverages)]
+
+    def __len__(self):
+        return len(self.coverages)
+
+    def __getitem__(self, thing):
+        return self.coverage_at(thing) if type(thing) == int else self.coverages[str(thing)]
+
+    def scan(self, fastq, templates, do_reverse=True, engine=None, fused=True):        # :325-364
+        import time
+        if engine is None:
+            from . import engine as _e
+            engine = _e._engine()
+        self.fastq = fastq
+        self.fastq_filenames = fastq.filenames()
+        self.fastq_sizes = fastq.filesizes()
+        self.fastq_readlength = fastq.readlength
+        self.fastq_records_approx = fastq.records_approx
+        self.coverages = OrderedDict((name, Coverage(seq)) for name, seq in templates.items())
+        self.config = engine.get_config()
+        seqs = [c.plus_seq.bases for c in self.coverages.values()]
+        if do_reverse:
+            seqs += [c.minus_seq.bases for c in self.coverages.values()]
+        t0 = time.time()
+        fused = fused and do_reverse
+        ret = engine.findseqs(self.fastq.filenames(), seqs, nplus=len(self.coverages) if fused else 0)
+        self.stats = ret['stats']
+        self.hits = ret['hits']
+        self.hitseqs = ret['hitseqs']
+        self.scantime = time.time() - t0
+        if fused:
+            plus = [c.plus_seq for c in self.coverages.values()]
+            for name, c in zip(self.coverages, coverages_from_fused(plus, ret.coverage, ret.mutcount)):
+                self.coverages[name] = c
+        else:
+            self.update_coverages()
+
+    def update_coverages(self):                                         # :367-381
+        assert self.hits is not None, 'cannot update coverages without .hits'
+        assert self.hitseqs is not None, 'cannot update coverages without .hitseqs'
+        for hit, hitseq in zip(self.hits, self.hitseqs):
+            hit = Hit(*hit)
+            self.coverage_at(hit.seq_nr).apply_hit(hit, hitseq, hit.seq_nr < len(self.coverages))
+
+    def encode(self, hits=False):                                       # :398-435
+        import time
+        more = {}
+        if hits:
+            more['hits'] = [list(h) for h in self.hits]
+            more['hitseqs'] = list(self.hitseqs)
+        return dict(
+            analyses=self.results,
+            info={
+                'format': 'kvarq',
+                'fastq': self.fastq_filenames,
+                'size': self.fastq_sizes,
+                'readlength': self.fastq_readlength,
+                'records_approx': self.fastq_records_approx,
+                'scantime': self.scantime,
+                'when': time.asctime(time.localtime()),
+                'version': VERSION,
+                'config': self.config,
+                'spacing': self.spacing,
+                'testsuites': dict(self.testsuite_versions),
+            },
+            stats=self.stats,
+            coverages=[(name, c.serialize()) for name, c in self.coverages.items()],
+            **more)
+
+    def decode(self, templates, data):                                  # :438-524, current format only
+        self.config = data['info']['config']
+        self.fastq_filenames = data['info']['fastq']
+        self.fastq_sizes = data['info']['size']
+        self.fastq_readlength = data['info'].get('readlength', -1)
+        self.fastq_records_approx = data['info'].get('records_approx', -1)
+        self.stats = data['stats']
+        self.scantime = data['info'].get('scantime', -1)
+        self.spacing = data['info'].get('spacing', self.spacing)
+        self.hits = [Hit(*h) for h in data['hits']] if 'hits' in data else None
+        self.hitseqs = data.get('hitseqs')
+        self.results = data.get('analyses')
+        stored = dict(data['coverages'])
+        self.coverages = OrderedDict()
+        for name, seq in templates.items():
+            c = Coverage(seq)
+            if name in stored:
+                c.deserialize(stored[name])
+                if len(c.coverage) != len(seq):
+                    raise ValueError('coverage "%s" has %d positions, template has %d'
+                                     % (name, len(c.coverage), len(seq)))
+            self.coverages[name] = c

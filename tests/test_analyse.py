@@ -101,3 +101,94 @@ def test_calls_from_gpu_equal_calls_from_reference_hits(tmp_path, checker):
     assert [c.serialize() for c in gpu_cov_hits] == [c.serialize() for c in ref_cov]
     assert analyse.calls(ts, gpu_cov) == analyse.calls(ts, ref_cov)
     e.close()
+
+
+# ------------------------------------------------------------------ result file
+def _named(ts):
+    from collections import OrderedDict
+    return OrderedDict(('%s%03d' % (k, i), s) for i, (k, s) in enumerate(zip(ts.kinds, _plus_sequences(ts))))
+
+
+def test_json_dump_layout():
+    """kvarq/util.py:272-294: two levels indented, everything deeper on one line; still valid JSON"""
+    import io
+    import json
+    data = {'info': {'fastq': ['a.fastq', 'b.fastq'], 'config': {'Amin': '.', 'maxerrors': 2}},
+            'coverages': [['t0', '1-2-3 1[AC]'], ['t1', '0-0 ']], 'hits': [[0, 10, -3, 25, 150]]}
+    out = io.StringIO()
+    analyse.json_dump(data, out)
+    text = out.getvalue()
+    assert json.loads(text) == data
+    lines = [l.rstrip(' ') for l in text.split('\n')]
+    assert '    "fastq": ["a.fastq", "b.fastq"],' in lines
+    assert '    ["t0", "1-2-3 1[AC]"],' in lines
+    assert '    [0, 10, -3, 25, 150]' in lines
+    assert max(len(l) - len(l.lstrip(' ')) for l in lines) == 4
+
+
+def test_result_file_round_trip(tmp_path):
+    """encode (kvarq/analyse.py:398-435) -> json_dump -> json.load -> decode gives the coverages
+    back; with hits stored, update_coverages rebuilds them from the hit list (CPU only)"""
+    import io
+    import json
+    from oracle import checker
+    from kvarq_b200.fastq import Fastq
+    if not checker.available('oracle'):
+        checker.build()
+    ts, fn = _case(tmp_path, 2000)
+    want = checker.findseqs(fn, ts.seqs(), nthreads=1, impl='oracle', **DEFAULT)
+    named = _named(ts)
+    a = analyse.Analyser()
+    fq = Fastq(fn, quiet=True)
+    a.fastq_filenames, a.fastq_sizes = fq.filenames(), fq.filesizes()
+    a.fastq_readlength, a.fastq_records_approx = fq.readlength, fq.records_approx
+    a.config = dict(DEFAULT, nthreads=1, Azero='!')
+    a.stats = {'records_parsed': 2000}
+    a.hits = [analyse.Hit(*h) for h in want['hits']]
+    a.hitseqs = [h.decode('latin-1') if isinstance(h, bytes) else h for h in want['hitseqs']]
+    from collections import OrderedDict
+    a.coverages = OrderedDict((n, Coverage(s)) for n, s in named.items())
+    a.update_coverages()
+    a.results = {'calls': analyse.calls(ts, list(a.coverages.values()))['spoligo']}
+    out = io.StringIO()
+    analyse.json_dump(a.encode(hits=True), out)
+    data = json.loads(out.getvalue())
+    assert data['info']['format'] == 'kvarq' and data['info']['size'] == [os.path.getsize(fn)]
+    b = analyse.Analyser()
+    b.decode(named, data)
+    assert [c.serialize() for c in b.coverages.values()] == [c.serialize() for c in a.coverages.values()]
+    assert b.hits == a.hits and b.results == a.results
+    for c in b.coverages.values():                       # rebuild from the stored hits
+        c.coverage = [0] * len(c.coverage)
+        c.mutations = {}
+    b.update_coverages()
+    assert [c.serialize() for c in b.coverages.values()] == [c.serialize() for c in a.coverages.values()]
+
+
+@pytest.mark.gpu
+def test_scan_to_result_file(tmp_path, checker):
+    """Fastq pre-flight -> engine.config -> Analyser.scan (fused arrays) -> result file: the
+    coverage strings equal the ones the reference's hits give"""
+    import io
+    import json
+    from kvarq_b200.engine import Engine
+    from kvarq_b200.fastq import Fastq
+    ts, fn = _case(tmp_path)
+    fq = Fastq(fn, paired=True, quiet=True)
+    e = Engine(0)
+    e.config(maxerrors=2, minoverlap=25, minreadlength=25, Amin=fq.Q2A(13), Azero=fq.Azero)
+    named = _named(ts)
+    a = analyse.Analyser()
+    a.scan(fq, named, engine=e)
+    out = io.StringIO()
+    analyse.json_dump(a.encode(), out)
+    data = json.loads(out.getvalue())
+    impl = 'ref' if checker.available('ref') else 'oracle'
+    want = checker.findseqs(fn, ts.seqs(), nthreads=1, impl=impl, **DEFAULT)
+    ref_cov = analyse.coverages_from_hits(_plus_sequences(ts), want['hits'], want['hitseqs'])
+    assert [s for _, s in data['coverages']] == [c.serialize() for c in ref_cov]
+    assert data['info']['config']['Amin'] == '.' and data['stats']['records_parsed'] == 6000
+    hits_way = analyse.Analyser()
+    hits_way.scan(fq, named, engine=e, fused=False)
+    assert [c.serialize() for c in hits_way.coverages.values()] == [c.serialize() for c in ref_cov]
+    e.close()
