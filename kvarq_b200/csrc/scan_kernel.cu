@@ -505,98 +505,111 @@ __device__ __forceinline__ uint32_t extract16_t(const uint32_t *pk, int b)      
 }
 
 // ---- P4: seeds -> bucket entries -> code-space verify -> confirm + emit ------------------------
-// Seeds s.seedq[base, base + n), one per lane.  Seed = read | pos << 5 | kind << 15.
+// Seeds s.seedq[base, base + n), n <= 32.  Seed = read | pos << 5 | kind << 15.
+// Stage A, one lane per seed: the key's bucket head (a table addressed by the key itself holds the
+// first entry and the size; further entries follow in the overflow array).  Stage B, one lane per
+// CANDIDATE: the (seed, entry) pairs of all 32 buckets are numbered through a warp prefix sum and
+// dealt to the lanes 32 at a time, so a long bucket is verified by many lanes instead of keeping
+// 31 lanes waiting for one.
 __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, int n, int lane)
 {
-    // Up to 64 seeds, two per lane, so that the table loads of both are in flight together.  A
-    // key's first bucket entry sits in a table addressed by the key itself (one load finds the
-    // candidate); further entries of the bucket follow in the overflow array.
+    static_assert(NS == 1, "one seed per lane");
     const KvqTemplates &t = c.t; const KvqParams &p = c.p;
-    int ncand = 0;
-    uint4 nxt[NS];
-    int cnt[NS], pos[NS], kind[NS], rd0[NS], rl[NS];
-    uint32_t ovf[NS];
+    uint4 head = make_uint4(0, 0, 0, 0);
+    uint32_t sa = 0, sb = 0;                // rd0 | rl << 16;  pos | kind << 10 | key << 16
+    int cnt = 0;
+    if (lane < n) {
+        const uint32_t sd = s.seedq[base + lane];
+        const uint32_t rdv = s.rd[sd & 31];
+        int pos = (int) ((sd >> 5) & 1023);
+        const int kind = (int) (sd >> 15);
+        const int rd0 = (int) (rdv & 0xFFFFu), rl = (int) (rdv >> 16);
+        if (kind) pos = __ldg(t.p2_tab + rl * KVQ_P2W + pos) & KVQ_P2_POS;      // T2 seeds carry their probe slot
+        const uint32_t key = extract16(s.pk, rd0 + pos) & 0xFFFFu;
+        head = __ldg((kind ? t.t2_first : t.t1_first) + key);
+        uint32_t more = head.x >> 24;
+        if (more == 255u) more = __ldg(&(kind ? t.t2_ent : t.t1_ent)[head.w - 1].x);
+        cnt = 1 + (int) more;
+        sa = rdv; sb = (uint32_t) pos | ((uint32_t) kind << 10) | (key << 16);
+    }
+    int inc = cnt > 0 ? cnt - 1 : 0;        // inclusive prefix sum of the overflow entries
+    const int extra = inc;
+    if (__any_sync(0xffffffffu, extra != 0)) {
 #pragma unroll
-    for (int u = 0; u < NS; u++) {
-        cnt[u] = 0; pos[u] = 0; kind[u] = 0; rd0[u] = 0; rl[u] = 0; ovf[u] = 0;
-        nxt[u] = make_uint4(0, 0, 0, 0);
-        if (lane + 32 * u < n) {
-            const uint32_t sd = s.seedq[base + lane + 32 * u];
-            const uint32_t rdv = s.rd[sd & 31];
-            pos[u] = (int) ((sd >> 5) & 1023); kind[u] = (int) (sd >> 15);
-            rd0[u] = (int) (rdv & 0xFFFFu); rl[u] = (int) (rdv >> 16);
-            if (kind[u]) pos[u] = __ldg(t.p2_tab + rl[u] * KVQ_P2W + pos[u]) & KVQ_P2_POS;   // T2 seeds carry their probe slot
-            const uint32_t r16 = extract16(s.pk, rd0[u] + pos[u]);
-            nxt[u] = __ldg((kind[u] ? t.t2_first : t.t1_first) + (r16 & 0xFFFFu));
-            cnt[u] = 1;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
         }
     }
-    __syncwarp();
+    const int total = __shfl_sync(0xffffffffu, inc, 31);
+    const int exc = inc - extra;
+    int ncand = 0;
+    // round -1: every lane verifies the head of its own bucket; rounds >= 0: overflow entries
+    for (int x0 = -32; x0 < total; x0 += 32) {
+        const int x = x0 + lane;
+        uint32_t a = sa, b = sb;
+        uint4 en = head;
+        bool active = lane < n;
+        if (x0 >= 0) {
+            int src = 0;                    // the seed entry x belongs to: first lane with inc > x
 #pragma unroll
-    for (int u = 0; u < NS; u++)
-        if (cnt[u]) {                               // bucket size: 1 + entries in the overflow array
-            uint32_t more = nxt[u].x >> 24;
-            ovf[u] = nxt[u].w;
-            if (more == 255u) more = __ldg(&(kind[u] ? t.t2_ent : t.t1_ent)[ovf[u] - 1].x);
-            cnt[u] = 1 + (int) more;
+            for (int step = 16; step; step >>= 1) {
+                const int v = __shfl_sync(0xffffffffu, inc, src + step - 1);
+                if (v <= x) src += step;
+            }
+            src &= 31;
+            const int k = x - __shfl_sync(0xffffffffu, exc, src);
+            a = __shfl_sync(0xffffffffu, sa, src); b = __shfl_sync(0xffffffffu, sb, src);
+            const uint32_t ovf = __shfl_sync(0xffffffffu, head.w, src);
+            active = x < total;
+            if (active) en = __ldg(((b >> 10) & 1u ? t.t2_ent : t.t1_ent) + ovf + k);
         }
-    for (;;) {
-        int alive = 0;
-#pragma unroll
-        for (int u = 0; u < NS; u++) alive |= cnt[u];
-        if (!__any_sync(0xffffffffu, alive != 0)) break;
-        uint4 en[NS]; int d[NS]; bool surv[NS];
-#pragma unroll
-        for (int u = 0; u < NS; u++) {
-            en[u] = nxt[u]; d[u] = 0; surv[u] = false;
-            if (cnt[u]) {
-                if (--cnt[u]) nxt[u] = __ldg((kind[u] ? t.t2_ent : t.t1_ent) + ovf[u]++);      // next entry in flight
-                const int sl = (int) (en[u].y >> 16);
-                d[u] = (int) (en[u].y & 0xFFFFu) - pos[u];
-                // overlap of the diagonal; Hamming distance in code space first (a lower bound of the
-                // byte distance, most candidates die on the first word), the acceptance rule after
-                const int ro = d[u] < 0 ? -d[u] : 0, to = d[u] > 0 ? d[u] : 0;
-                const int L = min(rl[u] - ro, sl - to);
-                const uint32_t *tpk = c.tpk + en[u].z;
-                int e = 0;
-                for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
-                    uint32_t x = extract16(s.pk, rd0[u] + ro + j) ^ extract16_t(tpk, to + j);
-                    uint32_t m = (x | (x >> 1)) & 0x55555555u;
-                    if (L - j < 16) m &= (1u << (2 * (L - j))) - 1u;
-                    e += __popc(m);
-                }
-                if (e <= p.maxerrors) {
-                    int ro2, to2, L2, rule;
-                    surv[u] = diag_rule(d[u], rl[u], sl, p.minoverlap, ro2, to2, L2, rule) != 0;
-                }
-                ncand++;
+        const int pos = (int) (b & 1023u), kind = (int) ((b >> 10) & 1u);
+        const int rd0 = (int) (a & 0xFFFFu), rl = (int) (a >> 16);
+        int d = 0; bool surv = false;
+        if (active) {
+            ncand++;
+            const int sl = (int) (en.y >> 16);
+            d = (int) (en.y & 0xFFFFu) - pos;
+            // overlap of the diagonal; Hamming distance in code space first (a lower bound of the
+            // byte distance, most candidates die on the first word), the acceptance rule after
+            const int ro = d < 0 ? -d : 0, to = d > 0 ? d : 0;
+            const int L = min(rl - ro, sl - to);
+            const uint32_t *tpk = c.tpk + en.z;
+            int e = 0;
+            for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
+                uint32_t xw = extract16(s.pk, rd0 + ro + j) ^ extract16_t(tpk, to + j);
+                uint32_t m = (xw | (xw >> 1)) & 0x55555555u;
+                if (L - j < 16) m &= (1u << (2 * (L - j))) - 1u;
+                e += __popc(m);
+            }
+            if (e <= p.maxerrors) {
+                int ro2, to2, L2, rule;
+                surv = diag_rule(d, rl, sl, p.minoverlap, ro2, to2, L2, rule) != 0;
             }
         }
-#pragma unroll
-        for (int u = 0; u < NS; u++) {
-            uint32_t m = __ballot_sync(0xffffffffu, surv[u]);
-            while (m) {                             // warp-wide: byte-exact confirm, dedupe, emit
-                const int src = __ffs(m) - 1;
-                m &= m - 1;
-                const int sq = (int) (__shfl_sync(0xffffffffu, en[u].x, src) & 0xFFFFFFu);
-                const uint32_t y = __shfl_sync(0xffffffffu, en[u].y, src);
-                const uint32_t poff = __shfl_sync(0xffffffffu, en[u].z, src);
-                const int dd = __shfl_sync(0xffffffffu, d[u], src);
-                const int bpos = __shfl_sync(0xffffffffu, pos[u], src), bkind = __shfl_sync(0xffffffffu, kind[u], src);
-                const int brd0 = __shfl_sync(0xffffffffu, rd0[u], src), brl = __shfl_sync(0xffffffffu, rl[u], src);
-                const int sl = (int) (y >> 16);
-                int ro, to, L, rule;
-                const int copies = diag_rule(dd, brl, sl, p.minoverlap, ro, to, L, rule);
-                const uint8_t *rdp = c.b.data + c.tc.a0 + brd0;
-                const uint8_t *tp = t.bytes + __ldg(t.byte_off + sq);
-                int e = 0;
-                for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
-                e = __reduce_add_sync(0xffffffffu, e);
-                if (e > p.maxerrors) continue;
-                if (!canonical_seed(p, t, s.pk, brd0, t.packed + poff, brl, sl, dd, bkind, bpos)) continue;
-                emit_hit_warp(t, p, c.o, sq, dd, ro, to, L, brl, sl, c.b.base_fpos + c.tc.a0 + brd0, rdp, tp,
-                              copies, rule, lane);
-            }
+        uint32_t m = __ballot_sync(0xffffffffu, surv);
+        while (m) {                                 // warp-wide: byte-exact confirm, dedupe, emit
+            const int w = __ffs(m) - 1;
+            m &= m - 1;
+            const int sq = (int) (__shfl_sync(0xffffffffu, en.x, w) & 0xFFFFFFu);
+            const uint32_t y = __shfl_sync(0xffffffffu, en.y, w);
+            const uint32_t poff = __shfl_sync(0xffffffffu, en.z, w);
+            const int dd = __shfl_sync(0xffffffffu, d, w);
+            const int bpos = __shfl_sync(0xffffffffu, pos, w), bkind = __shfl_sync(0xffffffffu, kind, w);
+            const int brd0 = __shfl_sync(0xffffffffu, rd0, w), brl = __shfl_sync(0xffffffffu, rl, w);
+            const int sl = (int) (y >> 16);
+            int ro, to, L, rule;
+            const int copies = diag_rule(dd, brl, sl, p.minoverlap, ro, to, L, rule);
+            const uint8_t *rdp = c.b.data + c.tc.a0 + brd0;
+            const uint8_t *tp = t.bytes + __ldg(t.byte_off + sq);
+            int e = 0;
+            for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
+            e = __reduce_add_sync(0xffffffffu, e);
+            if (e > p.maxerrors) continue;
+            if (!canonical_seed(p, t, s.pk, brd0, t.packed + poff, brl, sl, dd, bkind, bpos)) continue;
+            emit_hit_warp(t, p, c.o, sq, dd, ro, to, L, brl, sl, c.b.base_fpos + c.tc.a0 + brd0, rdp, tp,
+                          copies, rule, lane);
         }
     }
     return ncand;
