@@ -375,7 +375,7 @@ uint32_t kmer_key(const unsigned char *s)            // KVQ_SEED_K bases, base 0
 
 struct SeedTable {
     std::vector<uint32_t> bitmap, off; std::vector<uint4> ent; std::vector<uint8_t> present;
-    void build(std::vector<std::pair<uint32_t, uint4>> &items) {
+    void build(std::vector<std::pair<uint32_t, uint4>> &items, int pieces, bool flag_short) {
         bitmap.assign(KVQ_BITMAP_WORDS, 0); off.assign(KVQ_NKEYS + 1, 0); ent.resize(items.size());
         present.assign(KVQ_NKEYS, 0);
         for (auto &it : items) { off[it.first + 1]++; bitmap[it.first >> 5] |= 1u << (it.first & 31); present[it.first] = 1; }
@@ -388,9 +388,11 @@ struct SeedTable {
             const uint32_t b0 = off[k], b1 = off[k + 1];
             if (b0 == b1) continue;
             const uint32_t more = b1 - b0 - 1;
-            if (more >= 255) ovf.push_back(make_uint4(more, 0, 0, 0));
+            if (more >= KVQ_HEAD_MORE) ovf.push_back(make_uint4(more, 0, 0, 0));
             uint4 f = ent[b0];
-            f.x |= (more >= 255 ? 255u : more) << 24; f.w = (uint32_t) ovf.size();
+            f.x |= (more >= KVQ_HEAD_MORE ? KVQ_HEAD_MORE : more) << 24; f.w = (uint32_t) ovf.size();
+            for (uint32_t e = b0; e < b1; e++)
+                if (flag_short && (int) (ent[e].y >> 16) / pieces < KVQ_T1X_K) f.x |= KVQ_HEAD_SHORT;
             first[k] = f;
             for (uint32_t e = b0 + 1; e < b1; e++) ovf.push_back(ent[e]);
         }
@@ -404,7 +406,7 @@ struct TemplateSet {
     std::vector<int32_t> len;
     KvqTemplates dev{}; KvqParams par{};
     DevBuf d_bytes, d_boff, d_packed, d_poff, d_len, d_seedable, d_exh;
-    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2, d_bm2l, d_first1, d_first2;
+    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2, d_bm2l, d_first1, d_first2, d_t1x;
 
     static unsigned char comp(unsigned char c) {
         switch (c) { case 'A': return 'T'; case 'T': return 'A'; case 'C': return 'G'; case 'G': return 'C'; default: return c; }
@@ -463,7 +465,7 @@ struct TemplateSet {
             }
             // (the longest length ends up short when it alone holds more than a quarter: no long class)
         }
-        std::vector<uint32_t> bm2l(KVQ_BITMAP_WORDS, 0);
+        std::vector<uint32_t> bm2l(KVQ_BITMAP_WORDS, 0), t1x;
         int max_len = 0;
         for (int i = 0; i < n; i++) {
             const unsigned char *s = (const unsigned char *) seqs[i]; const int sl = lens[i];
@@ -481,6 +483,12 @@ struct TemplateSet {
             for (int j = 0; j < pieces; j++) {
                 const int toff = (int) ((int64_t) j * sl / pieces);
                 it1.push_back({kmer_key(s + toff), entry(toff)});
+                if (sl / pieces >= KVQ_T1X_K) {         // second level: the piece's first 12 bases
+                    if (t1x.empty()) t1x.assign(KVQ_T1X_WORDS, 0);
+                    uint32_t k = 0;
+                    for (int q = 0; q < KVQ_T1X_K; q++) k |= code_of(s[toff + q]) << (2 * q);
+                    t1x[k >> 5] |= 1u << (k & 31);
+                }
             }
             for (int toff = 0; toff + KVQ_SEED_K <= sl; toff++) {
                 const uint32_t key = kmer_key(s + toff);
@@ -490,7 +498,9 @@ struct TemplateSet {
         }
         boff[n] = (uint32_t) bytes.size(); poff[n] = (uint32_t) packed.size();
         bytes.resize(bytes.size() + 64, 0);
-        SeedTable t1, t2; t1.build(it1); t2.build(it2);
+        const bool t1x_on = it1.size() > KVQ_T1X_MIN_PIECES;
+        if (t1x_on && t1x.empty()) t1x.assign(KVQ_T1X_WORDS, 0);
+        SeedTable t1, t2; t1.build(it1, pieces, t1x_on); t2.build(it2, pieces, false);
         std::vector<uint32_t> covoff(np + 1, 0);
         for (int i = 0; i < np; i++) covoff[i + 1] = covoff[i] + (uint32_t) lens[i];
         cov_total = np > 0 ? covoff[np] : 0;
@@ -499,7 +509,7 @@ struct TemplateSet {
         upload(d_len, len); upload(d_seedable, seedable); upload(d_exh, exh);
         upload(d_bm1, t1.present); upload(d_off1, t1.off); upload(d_ent1, t1.ovf); upload(d_first1, t1.first);
         upload(d_bm2, t2.bitmap); upload(d_off2, t2.off); upload(d_ent2, t2.ovf); upload(d_first2, t2.first);
-        upload(d_bm2l, bm2l);
+        upload(d_bm2l, bm2l); if (t1x_on) upload(d_t1x, t1x);
         upload(d_covoff, covoff);
 
         dev.bytes = d_bytes.as<uint8_t>(); dev.byte_off = d_boff.as<uint32_t>();
@@ -509,13 +519,14 @@ struct TemplateSet {
         dev.t1_present = d_bm1.as<uint8_t>(); dev.t1_off = d_off1.as<uint32_t>(); dev.t1_ent = d_ent1.as<uint4>();
         dev.t2_bitmap = d_bm2.as<uint32_t>(); dev.t2_off = d_off2.as<uint32_t>(); dev.t2_ent = d_ent2.as<uint4>();
         dev.t1_first = d_first1.as<uint4>(); dev.t2_first = d_first2.as<uint4>();
-        dev.t2l_bitmap = d_bm2l.as<uint32_t>();
+        dev.t2l_bitmap = d_bm2l.as<uint32_t>(); dev.t1x_bitmap = d_t1x.as<uint32_t>();
         dev.cov_off = d_covoff.as<uint32_t>(); dev.nplus = np;
 
         par.maxerrors = E; par.minoverlap = O; par.minreadlength = cfg.minreadlength;
         par.amin = (int) (signed char) cfg.Amin;
         par.seed_ok = seed_ok; par.npieces = pieces < 1 ? 1 : pieces; par.max_seqlen = max_len;
         par.want_hits = 1; par.accumulate = 1;
+        par.t1x = t1x_on ? KVQ_T1X_K * pieces : 0;
         par.min_seed_rl = KVQ_SEED_K * par.npieces;
         par.div_magic = (uint32_t) ((65536 + par.npieces - 1) / par.npieces);
         for (int x = 0; x < 8192; x++)                  // the kernels divide by multiplication

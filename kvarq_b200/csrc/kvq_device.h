@@ -7,6 +7,11 @@
 #define KVQ_SEED_K 8                    // seed length in bases (16-bit keys)
 #define KVQ_NKEYS (1 << (2 * KVQ_SEED_K))
 #define KVQ_BITMAP_WORDS (KVQ_NKEYS / 32)
+#define KVQ_T1X_K 12                   // T1 second level: a piece's first 12 bases (24-bit key), bitmap in L2
+#define KVQ_T1X_MIN_PIECES 2048         // template sets with more T1 pieces run the kernel variant with the second level
+#define KVQ_T1X_WORDS ((1 << (2 * KVQ_T1X_K)) / 32)
+#define KVQ_HEAD_MORE 127u              // bucket-head size field [30:24]; 127 = read it from the overflow array
+#define KVQ_HEAD_SHORT 0x80000000u      // bucket holds a piece shorter than KVQ_T1X_K: no second level for this key
 #define KVQ_MAX_PIECES 8                // seeded path needs maxerrors+1 <= 8
 #define KVQ_MAX_SEEDED_SEQLEN 32000     // diagonal must fit the candidate encoding
 #define KVQ_HIST 1024                   // MAX_READLENGTH, workhorse.c:105
@@ -34,6 +39,7 @@
 struct KvqParams {
     int32_t maxerrors, minoverlap, minreadlength;
     int32_t amin;                       // signed char value of Amin
+    int32_t t1x;                        // 0, or (many templates) KVQ_T1X_K * npieces: T1 seeds of templates at least this long pass the 12-mer second level
     int32_t seed_ok;                    // floor(minoverlap/(E+1)) >= K and E+1 <= KVQ_MAX_PIECES
     int32_t npieces;                    // E+1
     int32_t max_seqlen;                 // longest template (decides the whole-read T2 probes)
@@ -64,6 +70,7 @@ struct KvqTemplates {
     const uint4 *t1_first, *t2_first;
     const uint8_t *t1_present; const uint32_t *t1_off; const uint4 *t1_ent;   // template-piece seeds
     const uint32_t *t2l_bitmap;         // T2 presence restricted to templates longer than short_max
+    const uint32_t *t1x_bitmap;         // 2^24 bits: 12-mers that start a piece of a template with pieces >= 12 bases
     const uint32_t *t2_bitmap, *t2_off; const uint4 *t2_ent;                  // every template offset
     const int16_t *p2_tab;              // [KVQ_MAXRL_FAST+1][KVQ_P2W] T2 probe offsets per read length, -1 = unused
     const uint32_t *cov_off;            // [nplus+1] offset of each plus template in coverage[]

@@ -463,6 +463,7 @@ __device__ __noinline__ void exhaustive_pair(const KvqParams &p, const KvqTempla
 // Is (kind, pos) the first seed, in the fixed order T1 pieces then T2 offsets, that fires on
 // diagonal d of (read, seq)?  Every firing seed reaches the same diagonal; only this one emits.
 // rpk = code plane, rb = base offset of the read in it.
+template <bool BIG>
 __device__ __noinline__ bool canonical_seed(const KvqParams &p, const KvqTemplates &t, const uint32_t *rpk, int rb,
                                const uint32_t *tpk, int rl, int sl, int d, int kind, int pos)
 {
@@ -470,9 +471,11 @@ __device__ __noinline__ bool canonical_seed(const KvqParams &p, const KvqTemplat
         const int toff = j * sl / p.npieces;
         const int pj = toff - d;
         if (pj < 0 || pj > rl - KVQ_SEED_K) continue;
-        const uint32_t r16 = extract16(rpk, rb + pj);
-        if (((r16 ^ extract16_g(tpk, toff)) & 0xFFFFu) == 0)
-            return kind == 0 && pos == pj;
+        const uint32_t x16 = extract16(rpk, rb + pj) ^ extract16_g(tpk, toff);
+        if (x16 & 0xFFFFu) continue;
+        // second level (drain_seeds): where 12 bases fit both the piece and the read they must match too
+        if (BIG && sl >= p.t1x && pj + KVQ_T1X_K <= rl && (x16 & 0xFFFFFFu)) continue;
+        return kind == 0 && pos == pj;
     }
     const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
     for (int i = 0; i < p.n2max; i++) {
@@ -507,16 +510,19 @@ __device__ __forceinline__ uint32_t extract16_t(const uint32_t *pk, int b)      
 // ---- P4: seeds -> bucket entries -> code-space verify -> confirm + emit ------------------------
 // Seeds s.seedq[base, base + n), n <= 32.  Seed = read | pos << 5 | kind << 15.
 // Stage A, one lane per seed: the key's bucket head (a table addressed by the key itself holds the
-// first entry and the size; further entries follow in the overflow array).  Stage B, one lane per
-// CANDIDATE: the (seed, entry) pairs of all 32 buckets are numbered through a warp prefix sum and
-// dealt to the lanes 32 at a time, so a long bucket is verified by many lanes instead of keeping
-// 31 lanes waiting for one.
+// first entry and the size; further entries follow in the overflow array).  A T1 seed whose 12
+// bases fit the read must also be in the 12-mer bitmap of piece starts (L2), unless its bucket
+// holds a piece shorter than 12 bases: at thousands of templates nearly every 8-mer is some
+// piece's start, the 12-mer is not.  Stage B, one lane per CANDIDATE: the (seed, entry) pairs of
+// the surviving buckets are numbered through a warp prefix sum and dealt to the lanes 32 at a
+// time, so a long bucket is verified by many lanes instead of keeping 31 lanes waiting for one.
+template <bool BIG>
 __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, int n, int lane)
 {
     static_assert(NS == 1, "one seed per lane");
     const KvqTemplates &t = c.t; const KvqParams &p = c.p;
     uint4 head = make_uint4(0, 0, 0, 0);
-    uint32_t sa = 0, sb = 0;                // rd0 | rl << 16;  pos | kind << 10 | key << 16
+    uint32_t sa = 0, sb = 0;                // rd0 | rl << 16;  pos | kind << 10
     int cnt = 0;
     if (lane < n) {
         const uint32_t sd = s.seedq[base + lane];
@@ -525,16 +531,25 @@ __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, 
         const int kind = (int) (sd >> 15);
         const int rd0 = (int) (rdv & 0xFFFFu), rl = (int) (rdv >> 16);
         if (kind) pos = __ldg(t.p2_tab + rl * KVQ_P2W + pos) & KVQ_P2_POS;      // T2 seeds carry their probe slot
-        const uint32_t key = extract16(s.pk, rd0 + pos) & 0xFFFFu;
-        head = __ldg((kind ? t.t2_first : t.t1_first) + key);
-        uint32_t more = head.x >> 24;
-        if (more == 255u) more = __ldg(&(kind ? t.t2_ent : t.t1_ent)[head.w - 1].x);
+        const uint32_t r16 = extract16(s.pk, rd0 + pos);
+        head = __ldg((kind ? t.t2_first : t.t1_first) + (r16 & 0xFFFFu));
+        bool pass = true;
+        if (BIG && !kind && pos + KVQ_T1X_K <= rl) {
+            const uint32_t k24 = r16 & 0xFFFFFFu;
+            pass = (__ldg(t.t1x_bitmap + (k24 >> 5)) >> (k24 & 31)) & 1u;
+        }
+        uint32_t more = BIG ? (head.x >> 24) & KVQ_HEAD_MORE : head.x >> 24;   // (the flag is only set for BIG)
+        if (more == KVQ_HEAD_MORE) more = __ldg(&(kind ? t.t2_ent : t.t1_ent)[head.w - 1].x);
         cnt = 1 + (int) more;
-        sa = rdv; sb = (uint32_t) pos | ((uint32_t) kind << 10) | (key << 16);
+        if (BIG && !pass && !(head.x & KVQ_HEAD_SHORT)) cnt = 0;
+        sa = rdv; sb = (uint32_t) pos | ((uint32_t) kind << 10);
     }
-    int inc = cnt > 0 ? cnt - 1 : 0;        // inclusive prefix sum of the overflow entries
-    const int extra = inc;
-    if (__any_sync(0xffffffffu, extra != 0)) {
+    // BIG: all entries are dealt out.  Otherwise (a few hundred templates: most buckets hold one
+    // entry) round -1 verifies every bucket's head on its own lane and only the overflow entries
+    // are dealt out.
+    const int mine = BIG ? cnt : (cnt > 0 ? cnt - 1 : 0);
+    int inc = mine;                         // inclusive prefix sum
+    if (BIG || __any_sync(0xffffffffu, mine != 0)) {
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int v = __shfl_up_sync(0xffffffffu, inc, o);
@@ -542,27 +557,31 @@ __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, 
         }
     }
     const int total = __shfl_sync(0xffffffffu, inc, 31);
-    const int exc = inc - extra;
+    const int exc = inc - mine;
     int ncand = 0;
-    // round -1: every lane verifies the head of its own bucket; rounds >= 0: overflow entries
-    for (int x0 = -32; x0 < total; x0 += 32) {
+    for (int x0 = BIG ? 0 : -32; x0 < total; x0 += 32) {
         const int x = x0 + lane;
         uint32_t a = sa, b = sb;
         uint4 en = head;
         bool active = lane < n;
-        if (x0 >= 0) {
-            int src = 0;                    // the seed entry x belongs to: first lane with inc > x
+        if (BIG || x0 >= 0) {
+            int src = 0;                    // the bucket entry x belongs to: first lane with inc > x
 #pragma unroll
             for (int step = 16; step; step >>= 1) {
                 const int v = __shfl_sync(0xffffffffu, inc, src + step - 1);
                 if (v <= x) src += step;
             }
             src &= 31;
-            const int k = x - __shfl_sync(0xffffffffu, exc, src);
+            int k = x - __shfl_sync(0xffffffffu, exc, src);
             a = __shfl_sync(0xffffffffu, sa, src); b = __shfl_sync(0xffffffffu, sb, src);
+            if (BIG) {
+                en.x = __shfl_sync(0xffffffffu, head.x, src); en.y = __shfl_sync(0xffffffffu, head.y, src);
+                en.z = __shfl_sync(0xffffffffu, head.z, src);
+                k--;                        // entry 0 is the head itself
+            }
             const uint32_t ovf = __shfl_sync(0xffffffffu, head.w, src);
             active = x < total;
-            if (active) en = __ldg(((b >> 10) & 1u ? t.t2_ent : t.t1_ent) + ovf + k);
+            if (active && (!BIG || k >= 0)) en = __ldg(((b >> 10) & 1u ? t.t2_ent : t.t1_ent) + ovf + k);
         }
         const int pos = (int) (b & 1023u), kind = (int) ((b >> 10) & 1u);
         const int rd0 = (int) (a & 0xFFFFu), rl = (int) (a >> 16);
@@ -607,7 +626,7 @@ __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, 
             for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
             e = __reduce_add_sync(0xffffffffu, e);
             if (e > p.maxerrors) continue;
-            if (!canonical_seed(p, t, s.pk, brd0, t.packed + poff, brl, sl, dd, bkind, bpos)) continue;
+            if (!canonical_seed<BIG>(p, t, s.pk, brd0, t.packed + poff, brl, sl, dd, bkind, bpos)) continue;
             emit_hit_warp(t, p, c.o, sq, dd, ro, to, L, brl, sl, c.b.base_fpos + c.tc.a0 + brd0, rdp, tp,
                           copies, rule, lane);
         }
@@ -616,15 +635,17 @@ __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, 
 }
 
 // Drain the first n seeds of the stack 64 at a time.
+template <bool BIG>
 __device__ __forceinline__ void drain_chunks(WarpSmem &s, const Ctx &c, int n, int lane, ThreadStats &ts)
 {
     for (int done = 0; done < n; done += DRAIN)
-        ts.cands += (unsigned long long) drain_seeds(s, c, done, min(DRAIN, n - done), lane);
+        ts.cands += (unsigned long long) drain_seeds<BIG>(s, c, done, min(DRAIN, n - done), lane);
 }
 
 // Push the set bits of every lane's `hits` (bit j = read offset posbase + j) on the seed stack:
 // a lane reserves room with one shared-memory atomic.  Whenever 32 seeds are waiting they are
 // drained with all lanes busy; what does not fit the stack waits for the drain.
+template <bool BIG>
 __device__ __forceinline__ void push_seeds(WarpSmem &s, const Ctx &c, uint32_t hits, uint32_t tag,
                                            int posbase, bool flush, int lane, ThreadStats &ts)
 {
@@ -643,7 +664,7 @@ __device__ __forceinline__ void push_seeds(WarpSmem &s, const Ctx &c, uint32_t h
         if (q < DRAIN && !left && !(flush && q)) break;
         const int stored = q < SEEDQ ? (int) q : SEEDQ;
         const int take = (left || flush) ? stored : (stored & ~(DRAIN - 1));
-        drain_chunks(s, c, take, lane, ts);
+        drain_chunks<BIG>(s, c, take, lane, ts);
         const int rem = stored - take;                                      // < DRAIN, moves to the front
         uint32_t keep[NS];
 #pragma unroll
@@ -732,6 +753,7 @@ __device__ __forceinline__ uint32_t parse_record(WarpSmem &s, Smem &sh, const Ct
 }
 
 // One round = up to 32 owned records of the tile, one per lane.
+template <bool BIG>
 __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown, int base, int n_all, int off,
                           bool at_seg_end, int lane, ThreadStats &ts)
 {
@@ -781,7 +803,7 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
                 if (hi < 31) hits &= (2u << hi) - 1u;
             }
             if (q == maxnw) { hits = hit2; tag |= 1u << 15; posbase = 0; }
-            push_seeds(s, c, hits, tag, posbase, q == maxnw, lane, ts);
+            push_seeds<BIG>(s, c, hits, tag, posbase, q == maxnw, lane, ts);
         }
     }
     // exhaustive matcher: reads the seed scheme does not cover against every template, the
@@ -812,7 +834,7 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
 
 namespace {
 
-template <bool NEG>
+template <bool NEG, bool BIG>
 __global__ void __launch_bounds__(THREADS, 1)
 kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqTemplates t,
                 const __grid_constant__ KvqParams p, const __grid_constant__ KvqOut o)
@@ -917,7 +939,7 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
             __syncwarp();
             if (k0 > 0) scatter_newlines(s, nrows, base, lane);
             __syncwarp();
-            run_round(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
+            run_round<BIG>(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
         }
         __syncwarp();                               // planes are reused by the next tile
         }
@@ -1008,17 +1030,15 @@ int kvq_scan_groups(void) { return NWARPS; }
 int kvq_launch_scan(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
                     int sm_count, void *stream)
 {
-    cudaError_t e = p.amin < 0
-        ? cudaFuncSetAttribute(kvq_scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(Smem))
-        : cudaFuncSetAttribute(kvq_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(Smem));
+    void (*k)(const KvqBatch, const KvqTemplates, const KvqParams, const KvqOut) =
+        p.amin < 0 ? (p.t1x ? kvq_scan_kernel<true, true> : kvq_scan_kernel<true, false>)
+                   : (p.t1x ? kvq_scan_kernel<false, true> : kvq_scan_kernel<false, false>);
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) sizeof(Smem));
     if (e != cudaSuccess) return (int) e;
     int grid = (b.ntiles + NWARPS - 1) / NWARPS;
     if (grid > sm_count) grid = sm_count;
     if (grid < 1) grid = 1;
-    if (p.amin < 0)
-        kvq_scan_kernel<true><<<grid, THREADS, sizeof(Smem), (cudaStream_t) stream>>>(b, t, p, o);
-    else
-        kvq_scan_kernel<false><<<grid, THREADS, sizeof(Smem), (cudaStream_t) stream>>>(b, t, p, o);
+    k<<<grid, THREADS, sizeof(Smem), (cudaStream_t) stream>>>(b, t, p, o);
     return (int) cudaGetLastError();
 }
 
