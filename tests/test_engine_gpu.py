@@ -455,6 +455,66 @@ def test_huge_seed_buckets(gpu_engine, checker, tmp_path):
     assert len(want['hits']) > 3000
 
 
+def test_large_set_mixed_template_classes(gpu_engine, checker, tmp_path):
+    """The large-set kernel variant (more than 2048 T1 pieces: 12-mer second level, all bucket
+    entries dealt to lanes) with every template class at once: 25-bp spacers (pieces shorter
+    than 12 bases: no second level for their keys), 51-bp SNP templates, a few long regions;
+    noisy reads (errors inside the 12-mers, heavy trimming: seeds closer than 12 bases to the
+    read end) and two values of maxerrors."""
+    g = synth.genome(40000, seed=51)
+    rng = np.random.RandomState(52)
+    comp = bytes.maketrans(b'ACGT', b'TGCA')
+    plus = [bytes(g[p:p + 25]) for p in sorted(rng.choice(len(g) - 700, 500, replace=False))]
+    plus += [bytes(g[p:p + 51]) for p in sorted(rng.choice(len(g) - 700, 500, replace=False))]
+    plus += [bytes(g[p:p + n]) for p, n in ((1000, 131), (9000, 611), (20000, 53), (30000, 36))]
+    seqs = [s.decode() for s in plus] + [s.translate(comp)[::-1].decode() for s in plus]
+    fn = str(tmp_path / 'mixed.fastq')
+    fq = [synth.fastq_reads(g, 1200, readlen=150, seed=53, qmean0=30.0, qdrop=26.0, qsd=5.0).tobytes(),
+          synth.fastq_reads(g, 600, readlen=60, seed=54, qmean0=26.0, qdrop=14.0, qsd=6.0, first_index=5000).tobytes()]
+    open(fn, 'wb').write(b''.join(fq))
+    from kvarq_b200.engine import Engine
+    e = Engine(0)
+    for cfg in (DEFAULT, dict(DEFAULT, maxerrors=1, minoverlap=20)):
+        e.config(**cfg)
+        got = e.findseqs(fn, seqs, nplus=len(plus))
+        want = oracle(checker, fn, seqs, cfg, impl='oracle')
+        assert_same_result(got, want, what='mixed classes %r' % (cfg,))
+        assert len(want['hits']) > 1000
+        assert got.timing['exhaustive_reads'] == 0
+        cov, mut = coverage_from_hits(want['hits'], want['hitseqs'], seqs, len(plus))
+        assert got.coverage.tolist() == cov and got.mutcount.tolist() == mut
+    e.close()
+
+
+def test_large_set_huge_buckets(gpu_engine, checker, tmp_path):
+    """Large-set variant with buckets of hundreds of entries (the count escape of the bucket head,
+    one bucket spread over many rounds of 32 lanes)."""
+    rng = random.Random(17)
+    core = ''.join(rng.choice('ACGT') for _ in range(70))
+    seqs = []
+    for i in range(800):
+        s = list(core[:51])
+        s[rng.randrange(51)] = rng.choice('ACGT')
+        if i % 3 == 0:
+            s[rng.randrange(51)] = rng.choice('ACGT')
+        seqs.append(''.join(s))
+    recs = []
+    for i in range(30):
+        L = rng.randint(56, 130)
+        left = ''.join(rng.choice('ACGT') for _ in range(rng.randint(0, L - 55)))
+        s = list((left + core + ''.join(rng.choice('ACGT') for _ in range(L)))[:L])
+        if i % 2:
+            s[rng.randrange(L)] = rng.choice('ACGT')
+        recs.append('@r%d\n%s\n+\n%s\n' % (i, ''.join(s), 'I' * L))
+    fn = str(tmp_path / 'hb2.fastq')
+    open(fn, 'w').write(''.join(recs))
+    gpu_engine.config(**DEFAULT)
+    got = gpu_engine.findseqs(fn, seqs)
+    want = oracle(checker, fn, seqs, DEFAULT, impl='oracle')
+    assert_same_result(got, want, what='large set, huge buckets')
+    assert len(want['hits']) > 5000
+
+
 def test_paired_end_250_gz(gpu_engine, checker, tmp_path):
     """BASELINE config 3 at test scale: 2 x 250 bp, MiSeq-like quality decay (real trimming), two
     gz files scanned as one stream with a continuing file_pos."""
