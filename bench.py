@@ -56,6 +56,9 @@ class ClockSampler(object):
     def __init__(self, index):
         self.windows = []
         self.t0 = None
+        self.proc = None
+        if index is None:                   # ranks > 0: one sampler per box (rank 0's GPU) is enough, and
+            return                          # concurrent nvidia-smi pollers slow every rank's CUDA calls
         try:
             self.proc = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
                                           '--format=csv,noheader,nounits', '-lms', '20'],
@@ -242,7 +245,7 @@ def main():
     staged = eng.stage([fq])
     for _ in range(args.warmup):
         r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert=False)
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local if rank == 0 else None)
     sampler.start()
     barrier()
     sampler.mark_begin()
