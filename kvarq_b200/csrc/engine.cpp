@@ -401,12 +401,35 @@ struct SeedTable {
     std::vector<uint4> first, ovf;
 };
 
+// Large sets: one more table (nkeys heads) appended to the shared head / overflow arrays; head
+// {seq | more << 24, toff | len << 16, packed_off, index into the shared overflow array}, empty
+// heads are all zero (len == 0).
+void append_table(std::vector<std::pair<uint32_t, uint4>> &items, uint32_t nkeys,
+                  std::vector<uint4> &first_all, std::vector<uint4> &ent_all)
+{
+    const size_t base = first_all.size();
+    first_all.resize(base + nkeys, make_uint4(0, 0, 0, 0));
+    std::stable_sort(items.begin(), items.end(),
+                     [](const std::pair<uint32_t, uint4> &a, const std::pair<uint32_t, uint4> &b) { return a.first < b.first; });
+    for (size_t b0 = 0; b0 < items.size();) {
+        size_t b1 = b0;
+        while (b1 < items.size() && items[b1].first == items[b0].first) b1++;
+        const uint32_t more = (uint32_t) (b1 - b0 - 1);
+        if (more >= KVQ_HEAD_MORE) ent_all.push_back(make_uint4(more, 0, 0, 0));
+        uint4 f = items[b0].second;
+        f.x |= (more >= KVQ_HEAD_MORE ? KVQ_HEAD_MORE : more) << 24; f.w = (uint32_t) ent_all.size();
+        first_all[base + items[b0].first] = f;
+        for (size_t e = b0 + 1; e < b1; e++) ent_all.push_back(items[e].second);
+        b0 = b1;
+    }
+}
+
 struct TemplateSet {
     int nseqs = 0, nplus = 0; int64_t cov_total = 0;
     std::vector<int32_t> len;
     KvqTemplates dev{}; KvqParams par{};
     DevBuf d_bytes, d_boff, d_packed, d_poff, d_len, d_seedable, d_exh;
-    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2, d_bm2l, d_first1, d_first2, d_t1x;
+    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2, d_bm2l, d_first1, d_first2, d_t1x, d_t2e, d_t2x;
 
     static unsigned char comp(unsigned char c) {
         switch (c) { case 'A': return 'T'; case 'T': return 'A'; case 'C': return 'G'; case 'G': return 'C'; default: return c; }
@@ -466,6 +489,17 @@ struct TemplateSet {
             // (the longest length ends up short when it alone holds more than a quarter: no long class)
         }
         std::vector<uint32_t> bm2l(KVQ_BITMAP_WORDS, 0), t1x;
+        // large sets (kernel variant BIG): 12-mer second level for T1, slot-specific T2 tables
+        size_t n_ok = 0;
+        for (int i = 0; i < n; i++)
+            n_ok += seed_ok && lens[i] / pieces >= KVQ_SEED_K && lens[i] <= KVQ_MAX_SEEDED_SEQLEN && i < (1 << 24);
+        const bool t1x_on = n_ok * (size_t) pieces > KVQ_T1X_MIN_PIECES && 5 * pieces <= 32;
+        const int OX = KVQ_T1X_K * pieces;                          // overlaps >= OX hold E+1 disjoint 12-mers
+        std::vector<std::vector<std::pair<uint32_t, uint4>>> itH(pieces), itT(pieces);
+        std::vector<std::pair<uint32_t, uint4>> itX;
+        std::vector<uint32_t> t2e, t2x; std::vector<uint8_t> t1mask;
+        if (t1x_on) t1mask.assign(KVQ_NKEYS, 0);
+        if (t1x_on) { t2e.assign(KVQ_BITMAP_WORDS, 0); t2x.assign(KVQ_T1X_WORDS, 0); }
         int max_len = 0;
         for (int i = 0; i < n; i++) {
             const unsigned char *s = (const unsigned char *) seqs[i]; const int sl = lens[i];
@@ -483,6 +517,9 @@ struct TemplateSet {
             for (int j = 0; j < pieces; j++) {
                 const int toff = (int) ((int64_t) j * sl / pieces);
                 it1.push_back({kmer_key(s + toff), entry(toff)});
+                if (t1x_on)                             // probe filter: the 3 code bits after the 8-mer (bases 8, 9)
+                    t1mask[kmer_key(s + toff)] |= sl / pieces >= KVQ_T1X_K
+                        ? (uint8_t) (1u << (code_of(s[toff + 8]) | ((code_of(s[toff + 9]) & 1u) << 2))) : (uint8_t) 0xFF;
                 if (sl / pieces >= KVQ_T1X_K) {         // second level: the piece's first 12 bases
                     if (t1x.empty()) t1x.assign(KVQ_T1X_WORDS, 0);
                     uint32_t k = 0;
@@ -494,22 +531,51 @@ struct TemplateSet {
                 const uint32_t key = kmer_key(s + toff);
                 it2.push_back({key, entry(toff)});
                 if (sl > short_max) bm2l[key >> 5] |= 1u << (key & 31);
+                if (!t1x_on) continue;
+                // Slot-specific tables.  Head slot j (read offset o_j) answers for read-head-on-template-tail
+                // overlaps ov in [O, OX): template offset sl - ov + o_j; tail slot j (read offset rl - O + o_j)
+                // for read-tail-on-template-head overlaps ov in [O, OX): template offset ov - O + o_j.
+                // Overlaps >= OX are found through the 12-mer slots (any template offset).
+                if (sl > O)
+                    for (int j = 0; j < pieces; j++) {
+                        const int oj = (int) ((int64_t) j * O / pieces);
+                        if (toff >= sl - OX + 1 + oj && toff <= sl - O + oj) {
+                            itH[j].push_back({key, entry(toff)}); t2e[key >> 5] |= 1u << (key & 31);
+                        }
+                        if (toff >= oj && toff <= OX - 1 - O + oj && toff <= sl - 1 - O + oj) {
+                            itT[j].push_back({key, entry(toff)}); t2e[key >> 5] |= 1u << (key & 31);
+                        }
+                    }
+                if (toff + KVQ_T1X_K <= sl) {
+                    uint32_t k = 0;
+                    for (int q = 0; q < KVQ_T1X_K; q++) k |= code_of(s[toff + q]) << (2 * q);
+                    t2x[k >> 5] |= 1u << (k & 31);
+                    itX.push_back({KVQ_X_HASH(k), entry(toff)});
+                }
             }
         }
         boff[n] = (uint32_t) bytes.size(); poff[n] = (uint32_t) packed.size();
         bytes.resize(bytes.size() + 64, 0);
-        const bool t1x_on = it1.size() > KVQ_T1X_MIN_PIECES;
         if (t1x_on && t1x.empty()) t1x.assign(KVQ_T1X_WORDS, 0);
         SeedTable t1, t2; t1.build(it1, pieces, t1x_on); t2.build(it2, pieces, false);
+        if (t1x_on) {                           // every T2 class back to back (see KvqTemplates)
+            std::vector<uint4> first_all, ent_all;
+            append_table(it2, KVQ_NKEYS, first_all, ent_all);
+            for (int j = 0; j < pieces; j++) append_table(itH[j], KVQ_NKEYS, first_all, ent_all);
+            for (int j = 0; j < pieces; j++) append_table(itT[j], KVQ_NKEYS, first_all, ent_all);
+            append_table(itX, 1u << KVQ_X_HASH_BITS, first_all, ent_all);
+            if (ent_all.empty()) ent_all.push_back(make_uint4(0, 0, 0, 0));
+            t2.first.swap(first_all); t2.ovf.swap(ent_all);
+        }
         std::vector<uint32_t> covoff(np + 1, 0);
         for (int i = 0; i < np; i++) covoff[i + 1] = covoff[i] + (uint32_t) lens[i];
         cov_total = np > 0 ? covoff[np] : 0;
 
         upload(d_bytes, bytes); upload(d_boff, boff); upload(d_packed, packed, 4); upload(d_poff, poff);
         upload(d_len, len); upload(d_seedable, seedable); upload(d_exh, exh);
-        upload(d_bm1, t1.present); upload(d_off1, t1.off); upload(d_ent1, t1.ovf); upload(d_first1, t1.first);
+        upload(d_bm1, t1x_on ? t1mask : t1.present); upload(d_off1, t1.off); upload(d_ent1, t1.ovf); upload(d_first1, t1.first);
         upload(d_bm2, t2.bitmap); upload(d_off2, t2.off); upload(d_ent2, t2.ovf); upload(d_first2, t2.first);
-        upload(d_bm2l, bm2l); if (t1x_on) upload(d_t1x, t1x);
+        upload(d_bm2l, bm2l); if (t1x_on) { upload(d_t1x, t1x); upload(d_t2e, t2e); upload(d_t2x, t2x); }
         upload(d_covoff, covoff);
 
         dev.bytes = d_bytes.as<uint8_t>(); dev.byte_off = d_boff.as<uint32_t>();
@@ -519,7 +585,7 @@ struct TemplateSet {
         dev.t1_present = d_bm1.as<uint8_t>(); dev.t1_off = d_off1.as<uint32_t>(); dev.t1_ent = d_ent1.as<uint4>();
         dev.t2_bitmap = d_bm2.as<uint32_t>(); dev.t2_off = d_off2.as<uint32_t>(); dev.t2_ent = d_ent2.as<uint4>();
         dev.t1_first = d_first1.as<uint4>(); dev.t2_first = d_first2.as<uint4>();
-        dev.t2l_bitmap = d_bm2l.as<uint32_t>(); dev.t1x_bitmap = d_t1x.as<uint32_t>();
+        dev.t2l_bitmap = d_bm2l.as<uint32_t>(); dev.t1x_bitmap = d_t1x.as<uint32_t>(); dev.t2e_bitmap = d_t2e.as<uint32_t>(); dev.t2x_bitmap = d_t2x.as<uint32_t>();
         dev.cov_off = d_covoff.as<uint32_t>(); dev.nplus = np;
 
         par.maxerrors = E; par.minoverlap = O; par.minreadlength = cfg.minreadlength;
@@ -533,11 +599,7 @@ struct TemplateSet {
             if ((int) (((uint32_t) x * par.div_magic) >> 16) != x / par.npieces)
                 throw KvqError(KVQ_ERR_RUNTIME, "internal: reciprocal division is inexact");
         for (int j = 0; j < KVQ_MAX_PIECES; j++) par.o_piece[j] = (int) ((int64_t) j * O / par.npieces);
-        par.n2max = 3 * par.npieces;
-        par.div_magic_n2 = (uint32_t) ((65536 + par.n2max - 1) / par.n2max);
-        for (int x = 0; x < 8192; x++)
-            if ((int) (((uint32_t) x * par.div_magic_n2) >> 16) != x / par.n2max)
-                throw KvqError(KVQ_ERR_RUNTIME, "internal: reciprocal division is inexact");
+        par.n2max = (t1x_on ? 5 : 3) * par.npieces;
         // Fixed read offsets probed against T2, per trimmed read length: E+1 pieces of the whole read
         // (rule d, only if some template is at least as long), of its first minoverlap bases
         // (rule b) and of its last minoverlap bases (rule a); duplicates removed.
@@ -552,6 +614,20 @@ struct TemplateSet {
                         if ((row[i] & KVQ_P2_POS) == v) { if (!lng) row[i] = (int16_t) v; return; }
                     row[nn++] = (int16_t) (v | (lng ? KVQ_P2_LONG : 0));
                 };
+                if (t1x_on) {                   // fixed layout, slot = class * pieces + j: W, H, T, HX, TX
+                    if (max_len >= rl)
+                        for (int j = 0; j < pieces; j++)
+                            row[j] = (int16_t) ((int) ((int64_t) j * rl / pieces) | (KVQ_T2L && rl > short_max ? KVQ_P2_LONG : 0));
+                    if (rl > O) {
+                        for (int j = 0; j < pieces; j++) row[pieces + j] = (int16_t) par.o_piece[j];
+                        for (int j = 0; j < pieces; j++) row[2 * pieces + j] = (int16_t) (rl - O + par.o_piece[j]);
+                        if (rl >= OX) {
+                            for (int j = 0; j < pieces; j++) row[3 * pieces + j] = (int16_t) (KVQ_T1X_K * j);
+                            for (int j = 0; j < pieces; j++) row[4 * pieces + j] = (int16_t) (rl - OX + KVQ_T1X_K * j);
+                        }
+                    }
+                    continue;
+                }
                 if (max_len >= rl) for (int j = 0; j < pieces; j++) add((int) ((int64_t) j * rl / pieces), KVQ_T2L && rl > short_max);
                 if (rl > O) {
                     for (int j = 0; j < pieces; j++) add(par.o_piece[j], false);

@@ -16,7 +16,9 @@
 #define KVQ_MAX_SEEDED_SEQLEN 32000     // diagonal must fit the candidate encoding
 #define KVQ_HIST 1024                   // MAX_READLENGTH, workhorse.c:105
 #define KVQ_MAXRL_FAST 512              // longer trimmed reads take the long-record kernel
-#define KVQ_P2W (3 * KVQ_MAX_PIECES)     // fixed read offsets probed against T2, per read length
+#define KVQ_P2W (5 * KVQ_MAX_PIECES)     // fixed read offsets probed against T2, per read length (3 classes; 5 for large sets)
+#define KVQ_X_HASH_BITS 20              // large sets: heads of the 12-mer table, addressed by a hash of the 24-bit key
+#define KVQ_X_HASH(k24) ((uint32_t) ((k24) * 0x9E3779B1u) >> (32 - KVQ_X_HASH_BITS))
 #define KVQ_P2_POS 0x3FFF               // p2_tab entry: read offset ...
 #define KVQ_P2_LONG 0x4000              // ... | flag: only templates longer than the short class can match here
 #define KVQ_ROW 1024                    // bytes one warp loads per step (32 lanes x 32 bytes)
@@ -47,8 +49,7 @@ struct KvqParams {
     int32_t min_seed_rl;                // KVQ_SEED_K * npieces: shortest read the seed scheme covers
     uint32_t div_magic;                 // floor(x / npieces) == (x * div_magic) >> 16 for x < 8192
     int32_t o_piece[KVQ_MAX_PIECES];    // floor(j * minoverlap / npieces)
-    int32_t n2max;                      // 3 * npieces: T2 probe slots per read
-    uint32_t div_magic_n2;              // floor(x / n2max) == (x * div_magic_n2) >> 16 for x < 8192
+    int32_t n2max;                      // T2 probe slots per read: 3 * npieces (5 * npieces for large sets)
     int32_t accumulate;                 // 0: re-run after a buffer overflow, counters already taken
 };
 
@@ -71,6 +72,11 @@ struct KvqTemplates {
     const uint8_t *t1_present; const uint32_t *t1_off; const uint4 *t1_ent;   // template-piece seeds
     const uint32_t *t2l_bitmap;         // T2 presence restricted to templates longer than short_max
     const uint32_t *t1x_bitmap;         // 2^24 bits: 12-mers that start a piece of a template with pieces >= 12 bases
+    // large sets (KvqParams.t1x != 0): t2_first / t2_ent hold every T2 class back to back --
+    // [W: all offsets, 65536 heads][H_j: head slots, 65536 each][T_j: tail slots, 65536 each]
+    // [X: 12-mers at all offsets, 2^KVQ_X_HASH_BITS heads]; overflow indices are global in t2_ent.
+    const uint32_t *t2e_bitmap;         // union of the H_j / T_j keys (staged in shared memory)
+    const uint32_t *t2x_bitmap;         // 2^24 bits: 12-mers at any template offset
     const uint32_t *t2_bitmap, *t2_off; const uint4 *t2_ent;                  // every template offset
     const int16_t *p2_tab;              // [KVQ_MAXRL_FAST+1][KVQ_P2W] T2 probe offsets per read length, -1 = unused
     const uint32_t *cov_off;            // [nplus+1] offset of each plus template in coverage[]

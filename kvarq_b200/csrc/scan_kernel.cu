@@ -474,10 +474,38 @@ __device__ __noinline__ bool canonical_seed(const KvqParams &p, const KvqTemplat
         const uint32_t x16 = extract16(rpk, rb + pj) ^ extract16_g(tpk, toff);
         if (x16 & 0xFFFFu) continue;
         // second level (drain_seeds): where 12 bases fit both the piece and the read they must match too
-        if (BIG && sl >= p.t1x && pj + KVQ_T1X_K <= rl && (x16 & 0xFFFFFFu)) continue;
+        if (BIG && sl >= p.t1x && (pj + KVQ_T1X_K > rl || (x16 & 0xFFFFFFu))) continue;
         return kind == 0 && pos == pj;
     }
     const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
+    if (BIG) {
+        // slot = class * npieces + j, classes W, H, T (8-mers), HX, TX (12-mers); `pos` is the slot.
+        // A slot fires where the keys agree and (template, offset) is in the slot's table
+        // (engine.cpp, TemplateSet::build).
+        const int P = p.npieces, O = p.minoverlap, OX = KVQ_T1X_K * P;
+        for (int i = 0; i < p.n2max; i++) {
+            const int pv = __ldg(p2 + i);
+            if (pv < 0) continue;
+            const int pp = pv & KVQ_P2_POS;
+            const int toff = pp + d;
+            const int cls = i < P ? 0 : i < 2 * P ? 1 : i < 3 * P ? 2 : 3;
+            const int kc = cls == 3 ? KVQ_T1X_K : KVQ_SEED_K;
+            if (toff < 0 || toff > sl - kc) continue;
+            const uint32_t x16 = extract16(rpk, rb + pp) ^ extract16_g(tpk, toff);
+            if (x16 & (cls == 3 ? 0xFFFFFFu : 0xFFFFu)) continue;
+            if (cls == 0 && (pv & KVQ_P2_LONG)) {
+                const uint32_t key = extract16_g(tpk, toff) & 0xFFFFu;
+                if (!((__ldg(t.t2l_bitmap + (key >> 5)) >> (key & 31)) & 1u)) continue;
+            }
+            if (cls == 1 && !(sl > O && toff >= sl - OX + 1 + pp && toff <= sl - O + pp)) continue;
+            if (cls == 2) {
+                const int oj = p.o_piece[i - 2 * P];
+                if (!(sl > O && toff >= oj && toff <= OX - 1 - O + oj && toff <= sl - 1 - O + oj)) continue;
+            }
+            return kind == 1 && pos == i;
+        }
+        return false;
+    }
     for (int i = 0; i < p.n2max; i++) {
         const int pv = __ldg(p2 + i);
         if (pv < 0) continue;
@@ -530,19 +558,24 @@ __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, 
         int pos = (int) ((sd >> 5) & 1023);
         const int kind = (int) (sd >> 15);
         const int rd0 = (int) (rdv & 0xFFFFu), rl = (int) (rdv >> 16);
+        const int slot = pos;
         if (kind) pos = __ldg(t.p2_tab + rl * KVQ_P2W + pos) & KVQ_P2_POS;      // T2 seeds carry their probe slot
         const uint32_t r16 = extract16(s.pk, rd0 + pos);
-        head = __ldg((kind ? t.t2_first : t.t1_first) + (r16 & 0xFFFFu));
+        uint32_t hidx = r16 & 0xFFFFu;
+        if (BIG && kind && slot >= p.npieces)   // table of the slot's class, all back to back in t2_first
+            hidx = slot < 3 * p.npieces ? hidx + ((uint32_t) (slot - p.npieces + 1) << 16)
+                                        : ((uint32_t) (2 * p.npieces + 1) << 16) + KVQ_X_HASH(r16 & 0xFFFFFFu);
+        head = __ldg((kind ? t.t2_first : t.t1_first) + hidx);
         bool pass = true;
-        if (BIG && !kind && pos + KVQ_T1X_K <= rl) {
+        if (BIG && !kind) {                     // pieces of >= 12 bases fire only with their 12 bases inside the read
             const uint32_t k24 = r16 & 0xFFFFFFu;
-            pass = (__ldg(t.t1x_bitmap + (k24 >> 5)) >> (k24 & 31)) & 1u;
+            pass = pos + KVQ_T1X_K <= rl && ((__ldg(t.t1x_bitmap + (k24 >> 5)) >> (k24 & 31)) & 1u);
         }
         uint32_t more = BIG ? (head.x >> 24) & KVQ_HEAD_MORE : head.x >> 24;   // (the flag is only set for BIG)
         if (more == KVQ_HEAD_MORE) more = __ldg(&(kind ? t.t2_ent : t.t1_ent)[head.w - 1].x);
         cnt = 1 + (int) more;
-        if (BIG && !pass && !(head.x & KVQ_HEAD_SHORT)) cnt = 0;
-        sa = rdv; sb = (uint32_t) pos | ((uint32_t) kind << 10);
+        if (BIG && ((!pass && !(head.x & KVQ_HEAD_SHORT)) || head.y == 0)) cnt = 0;
+        sa = rdv; sb = (uint32_t) pos | ((uint32_t) kind << 10) | ((uint32_t) slot << 11);
     }
     // BIG: all entries are dealt out.  Otherwise (a few hundred templates: most buckets hold one
     // entry) round -1 verifies every bucket's head on its own lane and only the overflow entries
@@ -615,7 +648,8 @@ __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, 
             const uint32_t y = __shfl_sync(0xffffffffu, en.y, w);
             const uint32_t poff = __shfl_sync(0xffffffffu, en.z, w);
             const int dd = __shfl_sync(0xffffffffu, d, w);
-            const int bpos = __shfl_sync(0xffffffffu, pos, w), bkind = __shfl_sync(0xffffffffu, kind, w);
+            const uint32_t bb = __shfl_sync(0xffffffffu, b, w);
+            const int bkind = (int) ((bb >> 10) & 1u), bpos = BIG && bkind ? (int) (bb >> 11) : (int) (bb & 1023u);
             const int brd0 = __shfl_sync(0xffffffffu, rd0, w), brl = __shfl_sync(0xffffffffu, rl, w);
             const int sl = (int) (y >> 16);
             int ro, to, L, rule;
@@ -679,6 +713,9 @@ __device__ __forceinline__ void push_seeds(WarpSmem &s, const Ctx &c, uint32_t h
 }
 
 // ---- P3: T1 probes of one 32-byte word: bit j <=> the 8-mer at base offset j is a template piece
+// BIG: the byte of a key is a mask over the 3 code bits that follow the 8-mer in the piece (all
+// ones for pieces shorter than 12 bases), so most chance 8-mer matches never become seeds.
+template <bool BIG>
 __device__ __forceinline__ uint32_t probe_word(const uint8_t *t1, uint32_t x0, uint32_t x1, uint32_t x2)
 {
     uint32_t hits = 0;
@@ -686,6 +723,14 @@ __device__ __forceinline__ uint32_t probe_word(const uint8_t *t1, uint32_t x0, u
     for (int j = 0; j < 8; j++) {
         const uint32_t sa = j ? funnel_r(x0, x1, 2 * j) : x0;       // bases j .. j+15
         const uint32_t sb = j ? funnel_r(x1, x2, 2 * j) : x1;       // bases 16+j .. 31+j
+        if (BIG) {
+            const uint32_t sc = x2 >> (2 * j);                      // bases 32+j .. (low bits only)
+            hits += (((uint32_t) t1[sa & 0xFFFFu] >> ((sa >> 16) & 7u)) & 1u) << j;
+            hits += (((uint32_t) t1[sa >> 16] >> (sb & 7u)) & 1u) << (j + 8);
+            hits += (((uint32_t) t1[sb & 0xFFFFu] >> ((sb >> 16) & 7u)) & 1u) << (j + 16);
+            hits += (((uint32_t) t1[sb >> 16] >> (sc & 7u)) & 1u) << (j + 24);
+            continue;
+        }
         hits += (uint32_t) t1[sa & 0xFFFFu] << j;
         hits += (uint32_t) t1[sa >> 16] << (j + 8);
         hits += (uint32_t) t1[sb & 0xFFFFu] << (j + 16);
@@ -777,12 +822,21 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
             for (int i = 0; i < p.n2max; i++) {
                 const int pv = __ldg(p2 + i);
                 if (pv < 0) continue;
-                const uint32_t key = extract16(s.pk, rd0 + (pv & KVQ_P2_POS)) & 0xFFFFu;
+                const uint32_t r16 = extract16(s.pk, rd0 + (pv & KVQ_P2_POS));
+                const uint32_t key = r16 & 0xFFFFu;
 #if KVQ_T2L
                 const uint32_t *bm = (pv & KVQ_P2_LONG) ? sh.bm2l : sh.bm2;
 #else
                 const uint32_t *bm = sh.bm2;
 #endif
+                if (BIG && i >= p.npieces) {    // slot classes: W | H, T (8-mers, own tables) | HX, TX (12-mers)
+                    if (i >= 3 * p.npieces) {
+                        const uint32_t k24 = r16 & 0xFFFFFFu;
+                        hit2 |= ((__ldg(t.t2x_bitmap + (k24 >> 5)) >> (k24 & 31)) & 1u) << i;
+                        continue;
+                    }
+                    bm = sh.tpk;
+                }
                 hit2 |= ((bm[key >> 5] >> (key & 31)) & 1u) << i;
             }
         }
@@ -797,7 +851,7 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
             int posbase = (w << 5) - rd0;
             if (q < nw) {
                 const uint2 x = reinterpret_cast<const uint2 *>(s.pk)[w];
-                hits = probe_word(sh.t1, x.x, x.y, s.pk[2 * w + 2]);
+                hits = probe_word<BIG>(sh.t1, x.x, x.y, s.pk[2 * w + 2]);
                 const int lo = rd0 - (w << 5), hi = plast - (w << 5);
                 if (lo > 0) hits &= 0xFFFFFFFFu << lo;
                 if (hi < 31) hits &= (2u << hi) - 1u;
@@ -856,14 +910,17 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         }
         if (lane == 0) s.qn = 0;
         for (int i = threadIdx.x; i < KVQ_HIST; i += THREADS) sh.hist[i] = 0;
-        if (t.packed_words <= KVQ_TPK_SMEM_WORDS)
+        static_assert(KVQ_TPK_SMEM_WORDS == KVQ_BITMAP_WORDS, "BIG keeps the head/tail-slot bitmap where the template codes would be");
+        if (BIG)
+            for (int i = threadIdx.x; i < KVQ_BITMAP_WORDS; i += THREADS) sh.tpk[i] = __ldg(t.t2e_bitmap + i);
+        else if (t.packed_words <= KVQ_TPK_SMEM_WORDS)
             for (int i = threadIdx.x; i < t.packed_words; i += THREADS) sh.tpk[i] = __ldg(t.packed + i);
         if (threadIdx.x == 0) sh.longest = -1;
     }
     __syncthreads();
     ThreadStats ts{0, 0, 0, 0};
     const uint32_t cl = (uint32_t) (p.amin & 0x7F) * 0x01010101u;
-    const uint32_t *tpk = t.packed_words <= KVQ_TPK_SMEM_WORDS ? sh.tpk : t.packed;
+    const uint32_t *tpk = (!BIG && t.packed_words <= KVQ_TPK_SMEM_WORDS) ? sh.tpk : t.packed;
 
     // Tile geometry + look-ahead: claim the next tile, count the newlines of the bytes it owns
     // and publish them (status word, see resolve_phase) before the current tile is processed.
