@@ -685,7 +685,7 @@ namespace {
 
 struct Slot {                           // one batch in flight
     HostBatch hb; PinBuf pin;
-    DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs;
+    DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs, d_surv; size_t surv_cap = 0;
     PinBuf h_ctr, h_seg, h_tiles;
     TileBufs tiles;
     cudaStream_t stream = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -724,13 +724,21 @@ struct kvq_engine {
 
 struct kvq_staged {
     kvq_engine *e = nullptr;
-    DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs;
+    DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs, d_surv; size_t surv_cap = 0;
     TileBufs tiles;
     size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
     int64_t nbytes = 0, base_fpos = 0, parsed = 0, total = 0; int nseg = 0;
 };
 
 namespace {
+
+// survivor-queue records to start with (KVQ_SURV_CAP: tests of the overflow re-run)
+size_t initial_surv_cap()
+{
+    const char *v = getenv("KVQ_SURV_CAP");
+    const long long n = v ? atoll(v) : 0;
+    return n > 0 ? (size_t) n : (size_t) 1 << 20;
+}
 
 void init_slots(kvq_engine *e)
 {
@@ -744,6 +752,7 @@ void init_slots(kvq_engine *e)
         s.d_ctr.ensure(sizeof(KvqCounters)); s.h_ctr.ensure(sizeof(KvqCounters));
         s.long_cap = (size_t) (BATCH_BYTES / 1024) + 64;
         s.d_longs.ensure(s.long_cap * sizeof(KvqLongRec));
+        s.surv_cap = initial_surv_cap(); s.d_surv.ensure(s.surv_cap * sizeof(KvqSurvRec));
         s.hit_cap = 1u << 18; s.d_hits.ensure(s.hit_cap * sizeof(KvqHitRec));
         s.blob_cap = 32u << 20; s.d_blob.ensure(s.blob_cap);
         CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
@@ -760,14 +769,26 @@ struct ScanTotals {
     ScanTotals() { memset(rls, 0, sizeof(rls)); }
 };
 
-KvqOut make_out(kvq_engine *e, DevBuf &ctr, DevBuf &hits, size_t hit_cap, DevBuf &blob, size_t blob_cap,
-                DevBuf &longs, size_t long_cap)
+// device buffers of one batch in flight (a Slot's or a staged stream's)
+struct OutBufs {
+    DevBuf &ctr, &hits; size_t &hit_cap; DevBuf &blob; size_t &blob_cap; DevBuf &longs; size_t long_cap;
+    DevBuf &surv; size_t &surv_cap;
+};
+template <class S> OutBufs bufs_of(S &s)
 {
+    return OutBufs{s.d_ctr, s.d_hits, s.hit_cap, s.d_blob, s.blob_cap, s.d_longs, s.long_cap, s.d_surv, s.surv_cap};
+}
+
+KvqOut make_out(kvq_engine *e, const OutBufs &ob)
+{
+    DevBuf &ctr = ob.ctr, &hits = ob.hits, &blob = ob.blob, &longs = ob.longs;
+    const size_t hit_cap = ob.hit_cap, blob_cap = ob.blob_cap, long_cap = ob.long_cap;
     KvqOut o{};
     o.ctr = ctr.as<KvqCounters>();
     o.hits = hits.as<KvqHitRec>(); o.hit_cap = hit_cap;
     o.blob = blob.as<uint8_t>(); o.blob_cap = blob_cap;
     o.longs = longs.as<KvqLongRec>(); o.long_cap = long_cap;
+    o.surv = ob.surv.as<KvqSurvRec>(); o.surv_cap = ob.surv_cap;
     o.nseqhits = e->acc.seqhits();
     o.nseqbasehits = e->acc.seqbase();
     o.coverage = e->acc.cov();
@@ -783,7 +804,7 @@ void reset_accum(kvq_engine *e)
     CK(cudaMemset(e->acc.d_all.p, 0, e->acc.words() * 8));
 }
 
-// enqueue memset + scan + long-record kernels for one batch already resident on the device
+// enqueue memset + scan + emit + long-record kernels for one batch already resident on the device
 void enqueue_kernels(kvq_engine *e, const KvqBatch &b, const KvqParams &p, const KvqOut &o,
                      cudaStream_t st, cudaEvent_t ev0, cudaEvent_t ev1)
 {
@@ -793,6 +814,7 @@ void enqueue_kernels(kvq_engine *e, const KvqBatch &b, const KvqParams &p, const
     CK(cudaMemsetAsync(b.tile_status, 0, (size_t) std::max(1, b.ntiles) * 4, st));
     if (ev0) CK(cudaEventRecord(ev0, st));
     cuda_check((cudaError_t) kvq_launch_scan(b, e->tpl.dev, p, o, e->sm_count, st), "scan kernel launch");
+    cuda_check((cudaError_t) kvq_launch_emit(b, e->tpl.dev, p, o, e->sm_count, st), "emit kernel launch");
     cuda_check((cudaError_t) kvq_launch_long(b, e->tpl.dev, p, o, e->sm_count, st), "long-record kernel launch");
     if (ev1) CK(cudaEventRecord(ev1, st));
 }
@@ -815,27 +837,44 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     s.tiles.upload_async(tiles, s.h_tiles, s.stream);
     KvqBatch b{s.d_data.as<uint8_t>(), hb.nbytes, s.d_seg.as<int64_t>(), nseg, hb.base_fpos};
     s.tiles.fill(b);
-    KvqOut o = make_out(e, s.d_ctr, s.d_hits, s.hit_cap, s.d_blob, s.blob_cap, s.d_longs, s.long_cap);
+    KvqOut o = make_out(e, bufs_of(s));
     enqueue_kernels(e, b, e->tpl.par, o, s.stream, s.ev0, s.ev1);
     CK(cudaMemcpyAsync(s.h_ctr.p, s.d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s.stream));
-    tot.launches += 2; tot.h2d += hb.nbytes + (int64_t) hb.cuts.size() * 8; tot.d2h += sizeof(KvqCounters);
+    tot.launches += 3; tot.h2d += hb.nbytes + (int64_t) hb.cuts.size() * 8; tot.d2h += sizeof(KvqCounters);
     tot.stream_bytes += hb.nbytes;
 }
 
+// The survivor queue of the scan kernel overflowed: the emit and long-record kernels did nothing.
+// Run the batch again with a queue that fits (its size is known now) and take the counters of
+// that run.
+void rerun_for_survivors(kvq_engine *e, const KvqBatch &b, const OutBufs &ob, KvqCounters &c, PinBuf &h_ctr,
+                         cudaStream_t st, ScanTotals &tot)
+{
+    if (c.surv_count <= ob.surv_cap) return;
+    ob.surv_cap = (size_t) (c.surv_count + c.surv_count / 8 + 1024);
+    ob.surv.ensure(ob.surv_cap * sizeof(KvqSurvRec));
+    enqueue_kernels(e, b, e->tpl.par, make_out(e, ob), st, nullptr, nullptr);
+    CK(cudaMemcpyAsync(h_ctr.p, ob.ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    c = *h_ctr.as<KvqCounters>();
+    tot.launches += 3;
+}
+
 // Fetch hits of a finished batch (re-running it with larger buffers when they overflowed).
-void collect_hits(kvq_engine *e, const KvqBatch &b, DevBuf &d_ctr, DevBuf &d_hits, size_t &hit_cap,
-                  DevBuf &d_blob, size_t &blob_cap, DevBuf &d_longs, size_t long_cap,
+void collect_hits(kvq_engine *e, const KvqBatch &b, const OutBufs &ob,
                   const KvqCounters &c, cudaStream_t st, ScanTotals &tot)
 {
+    DevBuf &d_hits = ob.hits, &d_blob = ob.blob;
+    size_t &hit_cap = ob.hit_cap, &blob_cap = ob.blob_cap;
     unsigned long long nh = c.hit_count, nb = c.blob_used;
     if (nh > hit_cap || nb > blob_cap) {
         hit_cap = (size_t) (nh + nh / 4 + 1024); blob_cap = (size_t) (nb + nb / 4 + 4096);
         d_hits.ensure(hit_cap * sizeof(KvqHitRec)); d_blob.ensure(blob_cap);
         KvqParams p = e->tpl.par; p.accumulate = 0;
-        KvqOut o = make_out(e, d_ctr, d_hits, hit_cap, d_blob, blob_cap, d_longs, long_cap);
+        KvqOut o = make_out(e, ob);
         enqueue_kernels(e, b, p, o, st, nullptr, nullptr);
         CK(cudaStreamSynchronize(st));
-        tot.launches += 2;
+        tot.launches += 3;
     }
     if (nh == 0) return;
     const size_t h0 = tot.hits.size(), b0 = tot.blob.size();
@@ -866,12 +905,13 @@ void harvest_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
 {
     CK(cudaStreamSynchronize(s.stream));
     float ms = 0; CK(cudaEventElapsedTime(&ms, s.ev0, s.ev1)); tot.kernel_ms += ms;
-    const KvqCounters &c = *s.h_ctr.as<KvqCounters>();
-    add_counters(e, c, tot);
+    KvqCounters c = *s.h_ctr.as<KvqCounters>();
     KvqBatch b{s.d_data.as<uint8_t>(), s.hb.nbytes, s.d_seg.as<int64_t>(), (int) s.hb.cuts.size() - 1, s.hb.base_fpos};
     s.tiles.fill(b);
+    rerun_for_survivors(e, b, bufs_of(s), c, s.h_ctr, s.stream, tot);
+    add_counters(e, c, tot);
     if (e->tpl.par.want_hits)
-        collect_hits(e, b, s.d_ctr, s.d_hits, s.hit_cap, s.d_blob, s.blob_cap, s.d_longs, s.long_cap, c, s.stream, tot);
+        collect_hits(e, b, bufs_of(s), c, s.stream, tot);
     // live per-template counters for engine.stats()
     if (e->tpl.nseqs > 0) {
         std::vector<unsigned long long> a(2 * e->acc.ns);
@@ -1267,6 +1307,7 @@ int kvq_stage_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens
         }
         st->d_ctr.ensure(sizeof(KvqCounters));
         st->long_cap = (size_t) (at / 1024) + 64; st->d_longs.ensure(st->long_cap * sizeof(KvqLongRec));
+        st->surv_cap = initial_surv_cap(); st->d_surv.ensure(st->surv_cap * sizeof(KvqSurvRec));
         st->hit_cap = 1u << 18; st->d_hits.ensure(st->hit_cap * sizeof(KvqHitRec));
         st->blob_cap = 32u << 20; st->d_blob.ensure(st->blob_cap);
         *out = st.release();
@@ -1300,19 +1341,19 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         ScanTotals tot;
         KvqBatch b{st->d_data.as<uint8_t>(), st->nbytes, st->d_seg.as<int64_t>(), st->nseg, st->base_fpos};
         st->tiles.fill(b);
-        KvqOut o = make_out(e, st->d_ctr, st->d_hits, st->hit_cap, st->d_blob, st->blob_cap, st->d_longs, st->long_cap);
+        KvqOut o = make_out(e, bufs_of(*st));
         enqueue_kernels(e, b, e->tpl.par, o, s0.stream, s0.ev0, s0.ev1);
         CK(cudaMemcpyAsync(s0.h_ctr.p, st->d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s0.stream));
         mark();
         CK(cudaStreamSynchronize(s0.stream));
         mark();
         float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1));
-        tot.kernel_ms = ms; tot.launches = 2; tot.stream_bytes = st->nbytes; tot.d2h = sizeof(KvqCounters);
-        const KvqCounters &c = *s0.h_ctr.as<KvqCounters>();
+        tot.kernel_ms = ms; tot.launches = 3; tot.stream_bytes = st->nbytes; tot.d2h = sizeof(KvqCounters);
+        KvqCounters c = *s0.h_ctr.as<KvqCounters>();
+        rerun_for_survivors(e, b, bufs_of(*st), c, s0.h_ctr, s0.stream, tot);
         add_counters(e, c, tot);
         if (want_hits)
-            collect_hits(e, b, st->d_ctr, st->d_hits, st->hit_cap, st->d_blob, st->blob_cap, st->d_longs,
-                         st->long_cap, c, s0.stream, tot);
+            collect_hits(e, b, bufs_of(*st), c, s0.stream, tot);
         mark();
         if (tot.err_key != ~0ULL) throw KvqError(KVQ_ERR_FASTQ_FORMAT, format_error_message(tot.err_key));
         *out = finish_result(e, tot, now_ms() - t_begin);

@@ -111,12 +111,23 @@ struct KvqLongRec {                     // work for the long-record kernel
     int32_t rl;                         // kind 1: trimmed read length
 };
 
+struct KvqSurvRec {                     // work for the emit kernel, 32 bytes
+    int64_t read_off;                   // batch offset of the trimmed read
+    int32_t rl;
+    int32_t seq;                        // >= 0: candidate alignment that passed the code-space check;
+                                        // -1: match the read exhaustively against every seq; -2: against exh_list
+    int32_t d;                          // diagonal (seq index aligned with read[0])
+    int32_t kindpos;                    // seed that found it: kind << 16 | pos (T1 read offset / T2 slot)
+    int32_t pad[2];
+};
+
 struct KvqCounters {                    // zeroed before every batch launch (except the accumulators)
     unsigned long long hit_count;       // hits wanted (may exceed capacity)
     unsigned long long blob_used;
     unsigned long long long_count;
     unsigned long long err_key;         // min over format errors, ~0 = none (see scan_kernel.cu)
     unsigned long long records, bases, exhaustive_reads, candidates;
+    unsigned long long surv_count;      // survivor records wanted (may exceed capacity: then the emit kernel does nothing)
     unsigned long long rls[KVQ_HIST];
     long long longest;
     unsigned int tile_next;             // dynamic tile queue (tiles are claimed in stream order)
@@ -130,6 +141,7 @@ struct KvqOut {
     KvqHitRec *hits; unsigned long long hit_cap;
     uint8_t *blob; unsigned long long blob_cap;
     KvqLongRec *longs; unsigned long long long_cap;
+    KvqSurvRec *surv; unsigned long long surv_cap;
     unsigned long long *nseqhits, *nseqbasehits;        // [nseqs]
     unsigned long long *coverage;                       // [cov_total]
     unsigned long long *mutcount;                       // [cov_total][6]
@@ -139,5 +151,7 @@ struct KvqOut {
 int kvq_launch_scan(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
                     int sm_count, void *stream);
 int kvq_launch_long(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
+                    int sm_count, void *stream);
+int kvq_launch_emit(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
                     int sm_count, void *stream);
 int kvq_scan_smem_bytes(void);

@@ -165,6 +165,24 @@ __device__ __forceinline__ void report_format_error(const KvqOut &o, int64_t rec
     atomicMin(&o.ctr->err_key, key);
 }
 
+// Work for the emit kernel: the lanes with `want` append one record each (one atomic per warp).
+// Nothing cold runs inside the scan kernel -- no calls, no spills on its hot paths.
+__device__ __forceinline__ void push_survivors(const KvqOut &o, bool want, int64_t read_off, int rl, int seq, int d,
+                                               int kindpos, int lane)
+{
+    const uint32_t m = __ballot_sync(0xffffffffu, want);
+    if (!m) return;
+    unsigned long long base = 0;
+    if (lane == __ffs(m) - 1) base = atomicAdd(&o.ctr->surv_count, (unsigned long long) __popc(m));
+    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+    const unsigned long long at = base + (unsigned long long) __popc(m & ((1u << lane) - 1u));
+    if (want && at < o.surv_cap) {
+        uint4 *q = reinterpret_cast<uint4 *>(o.surv + at);
+        q[0] = make_uint4((uint32_t) read_off, (uint32_t) ((unsigned long long) read_off >> 32), (uint32_t) rl, (uint32_t) seq);
+        q[1] = make_uint4((uint32_t) d, (uint32_t) kindpos, 0u, 0u);
+    }
+}
+
 __device__ __forceinline__ void push_long(const KvqOut &o, int64_t start, int64_t seg_end, int kind, int rl)
 {
     unsigned long long i = atomicAdd(&o.ctr->long_count, 1ULL);
@@ -640,30 +658,9 @@ __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, 
                 surv = diag_rule(d, rl, sl, p.minoverlap, ro2, to2, L2, rule) != 0;
             }
         }
-        uint32_t m = __ballot_sync(0xffffffffu, surv);
-        while (m) {                                 // warp-wide: byte-exact confirm, dedupe, emit
-            const int w = __ffs(m) - 1;
-            m &= m - 1;
-            const int sq = (int) (__shfl_sync(0xffffffffu, en.x, w) & 0xFFFFFFu);
-            const uint32_t y = __shfl_sync(0xffffffffu, en.y, w);
-            const uint32_t poff = __shfl_sync(0xffffffffu, en.z, w);
-            const int dd = __shfl_sync(0xffffffffu, d, w);
-            const uint32_t bb = __shfl_sync(0xffffffffu, b, w);
-            const int bkind = (int) ((bb >> 10) & 1u), bpos = BIG && bkind ? (int) (bb >> 11) : (int) (bb & 1023u);
-            const int brd0 = __shfl_sync(0xffffffffu, rd0, w), brl = __shfl_sync(0xffffffffu, rl, w);
-            const int sl = (int) (y >> 16);
-            int ro, to, L, rule;
-            const int copies = diag_rule(dd, brl, sl, p.minoverlap, ro, to, L, rule);
-            const uint8_t *rdp = c.b.data + c.tc.a0 + brd0;
-            const uint8_t *tp = t.bytes + __ldg(t.byte_off + sq);
-            int e = 0;
-            for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
-            e = __reduce_add_sync(0xffffffffu, e);
-            if (e > p.maxerrors) continue;
-            if (!canonical_seed<BIG>(p, t, s.pk, brd0, t.packed + poff, brl, sl, dd, bkind, bpos)) continue;
-            emit_hit_warp(t, p, c.o, sq, dd, ro, to, L, brl, sl, c.b.base_fpos + c.tc.a0 + brd0, rdp, tp,
-                          copies, rule, lane);
-        }
+        // survivors go to the emit kernel (byte-exact confirm, canonical-seed dedupe, emission)
+        push_survivors(c.o, surv, c.tc.a0 + rd0, rl, (int) (en.x & 0xFFFFFFu), d,
+                       (kind << 16) | (BIG && kind ? (int) (b >> 11) : pos), lane);
     }
     return ncand;
 }
@@ -860,28 +857,11 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
             push_seeds<BIG>(s, c, hits, tag, posbase, q == maxnw, lane, ts);
         }
     }
-    // exhaustive matcher: reads the seed scheme does not cover against every template, the
-    // others against the templates it does not cover
-    const uint8_t *data = c.b.data + tc.a0;
-    uint32_t m = __ballot_sync(0xffffffffu, rdv != 0 && !seedable);
+    // exhaustive matcher (emit kernel): reads the seed scheme does not cover against every
+    // template, the others against the templates it does not cover
     ts.exh += (unsigned long long) (rdv != 0 && !seedable);
-    while (m) {
-        const int src = __ffs(m) - 1;
-        m &= m - 1;
-        const int brd0 = __shfl_sync(0xffffffffu, rd0, src), brl = __shfl_sync(0xffffffffu, rl, src);
-        for (int sq = 0; sq < t.nseqs; sq++)
-            exhaustive_pair(p, t, c.o, data + brd0, brl, c.b.base_fpos + tc.a0 + brd0, sq, lane);
-    }
-    if (t.n_exh > 0) {
-        m = __ballot_sync(0xffffffffu, seedable);
-        while (m) {
-            const int src = __ffs(m) - 1;
-            m &= m - 1;
-            const int brd0 = __shfl_sync(0xffffffffu, rd0, src), brl = __shfl_sync(0xffffffffu, rl, src);
-            for (int i = 0; i < t.n_exh; i++)
-                exhaustive_pair(p, t, c.o, data + brd0, brl, c.b.base_fpos + tc.a0 + brd0, __ldg(t.exh_list + i), lane);
-        }
-    }
+    push_survivors(c.o, rdv != 0 && !seedable, tc.a0 + rd0, rl, -1, 0, 0, lane);
+    if (t.n_exh > 0) push_survivors(c.o, seedable, tc.a0 + rd0, rl, -2, 0, 0, lane);
 }
 
 } // namespace
@@ -1037,6 +1017,7 @@ kvq_long_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
 {
     const int lane = threadIdx.x & 31;
     const unsigned long long n = o.ctr->long_count < o.long_cap ? o.ctr->long_count : o.long_cap;
+    if (o.ctr->surv_count > o.surv_cap) return;     // the batch is run again with a larger survivor queue
     for (;;) {
         unsigned int i = 0;
         if (lane == 0) i = atomicAdd(&o.ctr->long_next, 1u);
@@ -1079,6 +1060,61 @@ kvq_long_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
     }
 }
 
+// ---- emit kernel: one warp per survivor record of the scan kernel ------------------------------
+// seq >= 0: the candidate passed the Hamming check on 2-bit codes; confirm it on the raw bytes,
+// keep it if its seed is the canonical one of the diagonal, emit (hit record, hitseq, per-seq
+// counters, fused coverage).  seq < 0: exhaustive matching of the read.  Nothing happens when the
+// queue overflowed: the host re-runs the batch with a larger one.
+template <bool BIG>
+__global__ void __launch_bounds__(256)
+kvq_emit_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqTemplates t,
+                const __grid_constant__ KvqParams p, const __grid_constant__ KvqOut o)
+{
+    __shared__ uint32_t rpk_all[8][KVQ_MAXRL_FAST / 16 + 4];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    uint32_t *rpk = rpk_all[wib];
+    const unsigned long long n = o.ctr->surv_count;
+    if (n > o.surv_cap) return;
+    const unsigned long long nw = (unsigned long long) gridDim.x * 8;
+    for (unsigned long long i = (unsigned long long) blockIdx.x * 8 + wib; i < n; i += nw) {
+        const uint4 q0 = __ldg(reinterpret_cast<const uint4 *>(o.surv + i));
+        const uint4 q1 = __ldg(reinterpret_cast<const uint4 *>(o.surv + i) + 1);
+        const long long rd0 = (long long) (((unsigned long long) q0.y << 32) | q0.x);
+        const int rl = (int) q0.z, seq = (int) q0.w, d = (int) q1.x;
+        const uint8_t *rdp = b.data + rd0;
+        if (seq < 0) {
+            if (seq == -1)
+                for (int sq = 0; sq < t.nseqs; sq++) exhaustive_pair(p, t, o, rdp, rl, b.base_fpos + rd0, sq, lane);
+            else
+                for (int k = 0; k < t.n_exh; k++)
+                    exhaustive_pair(p, t, o, rdp, rl, b.base_fpos + rd0, __ldg(t.exh_list + k), lane);
+            continue;
+        }
+        const int sl = __ldg(t.len + seq);
+        int ro, to, L, rule;
+        const int copies = diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule);
+        const uint8_t *tp = t.bytes + __ldg(t.byte_off + seq);
+        int e = 0;
+        for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
+        e = __reduce_add_sync(0xffffffffu, e);
+        if (e > p.maxerrors || !copies) continue;
+        // 2-bit codes of the read for the canonical-seed rule
+        __syncwarp();
+        for (int w = lane; w < KVQ_MAXRL_FAST / 16 + 4; w += 32) {
+            uint32_t v = 0;
+            for (int k = 0; k < 16; k++) {
+                const int at = 16 * w + k;
+                if (at < rl) v |= KVQ_CODE(rdp[at]) << (2 * k);
+            }
+            rpk[w] = v;
+        }
+        __syncwarp();
+        if (!canonical_seed<BIG>(p, t, rpk, 0, t.packed + __ldg(t.packed_off + seq), rl, sl, d,
+                                 (int) (q1.y >> 16), (int) (q1.y & 0xFFFFu))) continue;
+        emit_hit_warp(t, p, o, seq, d, ro, to, L, rl, sl, b.base_fpos + rd0, rdp, tp, copies, rule, lane);
+    }
+}
+
 } // namespace
 
 int kvq_scan_smem_bytes(void) { return (int) sizeof(Smem); }
@@ -1096,6 +1132,14 @@ int kvq_launch_scan(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p
     if (grid > sm_count) grid = sm_count;
     if (grid < 1) grid = 1;
     k<<<grid, THREADS, sizeof(Smem), (cudaStream_t) stream>>>(b, t, p, o);
+    return (int) cudaGetLastError();
+}
+
+int kvq_launch_emit(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
+                    int sm_count, void *stream)
+{
+    if (p.t1x) kvq_emit_kernel<true><<<4 * sm_count, 256, 0, (cudaStream_t) stream>>>(b, t, p, o);
+    else kvq_emit_kernel<false><<<4 * sm_count, 256, 0, (cudaStream_t) stream>>>(b, t, p, o);
     return (int) cudaGetLastError();
 }
 

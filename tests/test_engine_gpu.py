@@ -356,6 +356,30 @@ def test_many_hits_overflow_buffers(gpu_engine, checker, tmp_path):
     assert_same_result(got, want, what='poly-A')
 
 
+def test_survivor_queue_overflow(checker, multi_chunk, tmp_path, monkeypatch):
+    """The scan kernel hands candidates to the emit kernel through a queue; when it overflows
+    the emit / long-record kernels do nothing and the batch is run again with a queue that fits
+    (file path and staged path, fused coverage must not be counted twice)."""
+    from kvarq_b200.engine import Engine
+    monkeypatch.setenv('KVQ_SURV_CAP', '16')
+    e = Engine(0)
+    e.config(**DEFAULT)
+    fn, seqs = multi_chunk['plain'], multi_chunk['seqs']
+    nplus = len(seqs) // 2
+    want = oracle(checker, fn, seqs, DEFAULT)
+    got = e.findseqs(fn, seqs, nplus=nplus)
+    assert_same_result(got, want, what='survivor overflow, file')
+    cov, mut = coverage_from_hits(want['hits'], want['hitseqs'], seqs, nplus)
+    assert got.coverage.tolist() == cov and got.mutcount.tolist() == mut
+    st = e.stage([np.frombuffer(open(fn, 'rb').read(), dtype=np.uint8)])
+    for _ in range(2):
+        got = e.scan_staged(st, seqs, nplus=nplus)
+        assert_same_result(got, want, what='survivor overflow, staged')
+        assert got.coverage.tolist() == cov and got.mutcount.tolist() == mut
+    st.free()
+    e.close()
+
+
 def test_api_errors_and_state(gpu_engine, tmp_path):
     engine = gpu_engine
     engine.config(maxerrors=1, minoverlap=33, minreadlength=44, nthreads=5, Amin='+', Azero='@')
