@@ -656,6 +656,9 @@ __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, 
             if (e <= p.maxerrors) {
                 int ro2, to2, L2, rule;
                 surv = diag_rule(d, rl, sl, p.minoverlap, ro2, to2, L2, rule) != 0;
+                // template inside read (rule c): some T1 piece fires for every accepted alignment and
+                // T1 comes first in the canonical order, so a T2 seed never emits such a diagonal
+                if (kind && d <= 0 && d + rl >= sl) surv = false;
             }
         }
         // survivors go to the emit kernel (byte-exact confirm, canonical-seed dedupe, emission)
@@ -1065,8 +1068,11 @@ kvq_long_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
 // keep it if its seed is the canonical one of the diagonal, emit (hit record, hitseq, per-seq
 // counters, fused coverage).  seq < 0: exhaustive matching of the read.  Nothing happens when the
 // queue overflowed: the host re-runs the batch with a larger one.
+#ifndef KVQ_EMIT_BLOCKS
+#define KVQ_EMIT_BLOCKS 8                 // resident blocks per SM (latency-bound: one warp per record, dependent loads)
+#endif
 template <bool BIG>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, KVQ_EMIT_BLOCKS)
 kvq_emit_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqTemplates t,
                 const __grid_constant__ KvqParams p, const __grid_constant__ KvqOut o)
 {
@@ -1100,8 +1106,9 @@ kvq_emit_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         if (e > p.maxerrors || !copies) continue;
         // 2-bit codes of the read for the canonical-seed rule
         __syncwarp();
-        for (int w = lane; w < KVQ_MAXRL_FAST / 16 + 4; w += 32) {
+        for (int w = lane; w < (rl + 15) / 16 + 2; w += 32) {
             uint32_t v = 0;
+#pragma unroll
             for (int k = 0; k < 16; k++) {
                 const int at = 16 * w + k;
                 if (at < rl) v |= KVQ_CODE(rdp[at]) << (2 * k);
@@ -1138,8 +1145,8 @@ int kvq_launch_scan(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p
 int kvq_launch_emit(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
                     int sm_count, void *stream)
 {
-    if (p.t1x) kvq_emit_kernel<true><<<4 * sm_count, 256, 0, (cudaStream_t) stream>>>(b, t, p, o);
-    else kvq_emit_kernel<false><<<4 * sm_count, 256, 0, (cudaStream_t) stream>>>(b, t, p, o);
+    if (p.t1x) kvq_emit_kernel<true><<<KVQ_EMIT_BLOCKS * sm_count, 256, 0, (cudaStream_t) stream>>>(b, t, p, o);
+    else kvq_emit_kernel<false><<<KVQ_EMIT_BLOCKS * sm_count, 256, 0, (cudaStream_t) stream>>>(b, t, p, o);
     return (int) cudaGetLastError();
 }
 
