@@ -26,7 +26,7 @@
 namespace {
 
 #ifndef KVQ_NWARPS
-#define KVQ_NWARPS 20
+#define KVQ_NWARPS 23                   // warps per CTA (one CTA per SM): 80 registers, 225 KB shared memory
 #endif
 #ifndef KVQ_PREFETCH
 #define KVQ_PREFETCH 1
