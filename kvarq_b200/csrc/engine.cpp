@@ -683,6 +683,18 @@ struct kvq_result {
 
 namespace {
 
+// A freed result is kept for the next scan: its vectors keep their capacity, so a scan repeated
+// on similar input does not page-fault fresh memory for every result array.
+std::mutex g_spare_mu;
+kvq_result *g_spare = nullptr;
+
+kvq_result *take_result()
+{
+    std::lock_guard<std::mutex> g(g_spare_mu);
+    kvq_result *r = g_spare; g_spare = nullptr;
+    return r ? r : new kvq_result();
+}
+
 struct Slot {                           // one batch in flight
     HostBatch hb; PinBuf pin;
     DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs, d_surv; size_t surv_cap = 0;
@@ -704,6 +716,12 @@ struct Accum {                          // device-wide accumulators of one scan,
 
 struct RawHit { KvqHitRec h; };
 
+struct HitKey { int64_t fpos; uint64_t k2; uint32_t idx; };         // sort key of a hit (finish_result)
+struct SortScratch {                    // reused from scan to scan: no fresh pages per result
+    std::vector<HitKey> keys, sorted; std::vector<uint32_t> start, bucket, at;
+    std::vector<KvqHitRec> hits; std::vector<char> blob;
+};
+
 } // namespace
 
 struct kvq_engine {
@@ -718,6 +736,7 @@ struct kvq_engine {
     Accum acc;
     TemplateSet tpl;
     PinBuf pin_out, pin_acc;                        // page-locked staging of the result copies
+    SortScratch scratch;
 
     void set_error(int cls, const std::string &m) { std::lock_guard<std::mutex> g(mu); err_cls = cls; err_msg = m; }
 };
@@ -727,6 +746,7 @@ struct kvq_staged {
     DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs, d_surv; size_t surv_cap = 0;
     TileBufs tiles;
     size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
+    size_t last_hits = 0, last_blob = 0;            // result sizes of the previous scan of this stream
     int64_t nbytes = 0, base_fpos = 0, parsed = 0, total = 0; int nseg = 0;
 };
 
@@ -766,6 +786,8 @@ struct ScanTotals {
     int64_t rls[KVQ_HIST]; int64_t longest = -1, records = 0, bases = 0, exh = 0, cands = 0;
     unsigned long long err_key = ~0ULL;
     double kernel_ms = 0; int64_t launches = 0, h2d = 0, d2h = 0, stream_bytes = 0;
+    bool acc_fetched = false;           // per-template accumulators already in e->pin_acc (copied behind the kernels)
+    size_t spec_hits = 0, spec_blob = 0; // hit records / hitseq bytes already in e->pin_out (copied behind the kernels)
     ScanTotals() { memset(rls, 0, sizeof(rls)); }
 };
 
@@ -857,7 +879,7 @@ void rerun_for_survivors(kvq_engine *e, const KvqBatch &b, const OutBufs &ob, Kv
     CK(cudaMemcpyAsync(h_ctr.p, ob.ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     c = *h_ctr.as<KvqCounters>();
-    tot.launches += 3;
+    tot.launches += 3; tot.acc_fetched = false; tot.spec_hits = tot.spec_blob = 0;
 }
 
 // Fetch hits of a finished batch (re-running it with larger buffers when they overflowed).
@@ -874,18 +896,23 @@ void collect_hits(kvq_engine *e, const KvqBatch &b, const OutBufs &ob,
         KvqOut o = make_out(e, ob);
         enqueue_kernels(e, b, p, o, st, nullptr, nullptr);
         CK(cudaStreamSynchronize(st));
-        tot.launches += 3;
+        tot.launches += 3; tot.spec_hits = tot.spec_blob = 0;
     }
     if (nh == 0) return;
     const size_t h0 = tot.hits.size(), b0 = tot.blob.size();
     tot.hits.resize(h0 + nh); tot.blob.resize(b0 + nb);
     // D2H through page-locked staging (DMA at full rate), then a plain copy into the result vectors
     const size_t hbytes = nh * sizeof(KvqHitRec);
-    e->pin_out.ensure(((hbytes + 255) & ~(size_t) 255) + nb + 256);
-    char *ph = e->pin_out.as<char>(), *pb = ph + ((hbytes + 255) & ~(size_t) 255);
-    CK(cudaMemcpyAsync(ph, d_hits.p, hbytes, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(pb, d_blob.p, nb, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    char *ph, *pb;
+    if (nh <= tot.spec_hits && nb <= tot.spec_blob) {       // already copied behind the kernels
+        ph = e->pin_out.as<char>(); pb = ph + ((tot.spec_hits * sizeof(KvqHitRec) + 255) & ~(size_t) 255);
+    } else {
+        e->pin_out.ensure(((hbytes + 255) & ~(size_t) 255) + nb + 256);
+        ph = e->pin_out.as<char>(); pb = ph + ((hbytes + 255) & ~(size_t) 255);
+        CK(cudaMemcpyAsync(ph, d_hits.p, hbytes, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(pb, d_blob.p, nb, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
     memcpy(tot.hits.data() + h0, ph, hbytes); memcpy(tot.blob.data() + b0, pb, nb);
     for (size_t i = h0; i < h0 + nh; i++) tot.hits[i].blob_off += (int64_t) b0;
     tot.d2h += (int64_t) (nh * sizeof(KvqHitRec) + nb);
@@ -962,11 +989,13 @@ void fill_stats(kvq_engine *e, kvq_stats_t &st, const int64_t *rls, int64_t long
 kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
 {
     const double t_fin = now_ms();
-    std::unique_ptr<kvq_result> r(new kvq_result());
+    std::unique_ptr<kvq_result> r(take_result());
     // reference emission order: sort 24-byte keys, not the records
     const size_t nh = tot.hits.size();
-    struct Key { int64_t fpos; uint64_t k2; uint32_t idx; };
-    std::vector<Key> keys(nh);
+    typedef HitKey Key;
+    SortScratch &sc = e->scratch;
+    std::vector<Key> &keys = sc.keys;
+    keys.resize(nh);
     for (size_t i = 0; i < nh; i++) {
         const KvqHitRec &h = tot.hits[i];
         const int o = h.rule == 0 ? h.seq_pos : h.rule == 1 ? -h.seq_pos : std::abs(h.seq_pos);
@@ -980,12 +1009,17 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
         // then a sort inside the (tiny) buckets
         int64_t lo = keys[0].fpos, hi = keys[0].fpos;
         for (const Key &k : keys) { lo = std::min(lo, k.fpos); hi = std::max(hi, k.fpos); }
-        const long double scale = (long double) nh / (long double) (hi - lo + 1);
-        std::vector<uint32_t> start(nh + 1, 0), bucket(nh);
-        for (size_t i = 0; i < nh; i++) { bucket[i] = (uint32_t) ((long double) (keys[i].fpos - lo) * scale); start[bucket[i] + 1]++; }
+        const double scale = (double) nh / (double) (hi - lo + 1);       // monotonic is all that is needed
+        std::vector<uint32_t> &start = sc.start, &bucket = sc.bucket, &at = sc.at;
+        start.assign(nh + 1, 0); bucket.resize(nh);
+        for (size_t i = 0; i < nh; i++) {
+            bucket[i] = std::min<uint32_t>((uint32_t) nh - 1, (uint32_t) ((double) (keys[i].fpos - lo) * scale));
+            start[bucket[i] + 1]++;
+        }
         for (size_t i = 0; i < nh; i++) start[i + 1] += start[i];
-        std::vector<Key> sorted(nh);
-        std::vector<uint32_t> at(start.begin(), start.end() - 1);
+        std::vector<Key> &sorted = sc.sorted;
+        sorted.resize(nh);
+        at.assign(start.begin(), start.end() - 1);
         for (size_t i = 0; i < nh; i++) sorted[at[bucket[i]]++] = keys[i];
         for (size_t bk = 0; bk < nh; bk++)
             if (start[bk + 1] - start[bk] > 1) std::sort(sorted.begin() + start[bk], sorted.begin() + start[bk + 1], before);
@@ -993,6 +1027,7 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
     } else {
         std::sort(keys.begin(), keys.end(), before);
     }
+    const double t_sorted = now_ms();
     r->hits.resize(nh); r->offsets.resize(nh + 1); r->blob.resize(tot.blob.size());
     int64_t at = 0;
     for (size_t i = 0; i < nh; i++) {
@@ -1003,14 +1038,17 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
         at += h.length;
     }
     r->offsets[nh] = at;
+    const double t_ordered = now_ms();
     fill_stats(e, r->stats, tot.rls, tot.longest, tot.records);
     const int ns = e->tpl.nseqs; const int64_t nc = e->tpl.cov_total;
     r->nseqhits.assign(ns, 0); r->nseqbasehits.assign(ns, 0);
     {
         const bool want_cov = e->tpl.nplus > 0 && nc > 0;
         const size_t words = want_cov ? e->acc.words() : 2 * e->acc.ns;
-        e->pin_acc.ensure(words * 8);
-        CK(cudaMemcpy(e->pin_acc.p, e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost));
+        if (!tot.acc_fetched) {
+            e->pin_acc.ensure(words * 8);
+            CK(cudaMemcpy(e->pin_acc.p, e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost));
+        }
         const int64_t *all = e->pin_acc.as<int64_t>();
         for (int i = 0; i < ns; i++) {
             r->nseqhits[i] = all[i]; r->nseqbasehits[i] = all[e->acc.ns + i];
@@ -1023,6 +1061,10 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
         }
     }
     tot.d2h += (int64_t) ns * 16;
+    if (getenv("KVQ_TRACE"))
+        fprintf(stderr, "[kvq trace] finish: sort %.3f reorder %.3f stats+accumulators %.3f\n",
+                t_sorted - t_fin, t_ordered - t_sorted, now_ms() - t_ordered);
+    tot.hits.clear(); tot.blob.clear(); sc.hits.swap(tot.hits); sc.blob.swap(tot.blob);     // capacity kept for the next scan
     r->timing.kernel_ms = tot.kernel_ms; r->timing.wall_ms = wall_ms + (now_ms() - t_fin); r->timing.launches = tot.launches;
     r->timing.h2d_bytes = tot.h2d; r->timing.d2h_bytes = tot.d2h; r->timing.bases = tot.bases;
     r->timing.stream_bytes = tot.stream_bytes; r->timing.exhaustive_reads = tot.exh; r->timing.candidates = tot.cands;
@@ -1229,7 +1271,21 @@ const int64_t *kvq_result_mutcount(const kvq_result *r, int64_t *n)
     return r && !r->mutcount.empty() ? r->mutcount.data() : nullptr;
 }
 const kvq_timing_t *kvq_result_timing(const kvq_result *r) { return r ? &r->timing : nullptr; }
-void kvq_result_free(kvq_result *r) { delete r; }
+void kvq_result_free(kvq_result *r)
+{
+    if (!r) return;
+    {
+        std::lock_guard<std::mutex> g(g_spare_mu);
+        if (!g_spare) {
+            r->hits.clear(); r->blob.clear(); r->offsets.clear();
+            r->nseqhits.clear(); r->nseqbasehits.clear(); r->coverage.clear(); r->mutcount.clear();
+            r->stats = kvq_stats_t{}; r->timing = kvq_timing_t{};
+            g_spare = r;
+            return;
+        }
+    }
+    delete r;
+}
 
 int kvq_stats_snapshot(kvq_engine *e, kvq_stats_t *out, int64_t *nseqhits, int64_t *nseqbasehits, int cap)
 {
@@ -1338,12 +1394,27 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         e->live.parsed = st->parsed; e->live.total = st->total;
         init_slots(e);                                  // borrow slot 0's stream and events
         Slot &s0 = e->slots[0];
-        ScanTotals tot;
+        ScanTotals tot; tot.acc_fetched = true;
+        tot.hits.swap(e->scratch.hits); tot.blob.swap(e->scratch.blob); tot.hits.clear(); tot.blob.clear();
         KvqBatch b{st->d_data.as<uint8_t>(), st->nbytes, st->d_seg.as<int64_t>(), st->nseg, st->base_fpos};
         st->tiles.fill(b);
         KvqOut o = make_out(e, bufs_of(*st));
         enqueue_kernels(e, b, e->tpl.par, o, s0.stream, s0.ev0, s0.ev1);
         CK(cudaMemcpyAsync(s0.h_ctr.p, st->d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s0.stream));
+        {   // the per-template accumulators ride behind the kernels instead of a blocking copy later
+            const bool want_cov = e->tpl.nplus > 0 && e->tpl.cov_total > 0;
+            const size_t words = want_cov ? e->acc.words() : 2 * e->acc.ns;
+            e->pin_acc.ensure(words * 8);
+            CK(cudaMemcpyAsync(e->pin_acc.p, e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost, s0.stream));
+        }
+        if (want_hits && st->last_hits) {   // ... and so do as many hits as the previous scan of this stream had (+25 %)
+            tot.spec_hits = std::min(st->hit_cap, st->last_hits + st->last_hits / 4 + 64);
+            tot.spec_blob = std::min(st->blob_cap, st->last_blob + st->last_blob / 4 + 4096);
+            const size_t hb = (tot.spec_hits * sizeof(KvqHitRec) + 255) & ~(size_t) 255;
+            e->pin_out.ensure(hb + tot.spec_blob + 256);
+            CK(cudaMemcpyAsync(e->pin_out.p, st->d_hits.p, tot.spec_hits * sizeof(KvqHitRec), cudaMemcpyDeviceToHost, s0.stream));
+            CK(cudaMemcpyAsync(e->pin_out.as<char>() + hb, st->d_blob.p, tot.spec_blob, cudaMemcpyDeviceToHost, s0.stream));
+        }
         mark();
         CK(cudaStreamSynchronize(s0.stream));
         mark();
@@ -1352,8 +1423,10 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         KvqCounters c = *s0.h_ctr.as<KvqCounters>();
         rerun_for_survivors(e, b, bufs_of(*st), c, s0.h_ctr, s0.stream, tot);
         add_counters(e, c, tot);
-        if (want_hits)
+        if (want_hits) {
             collect_hits(e, b, bufs_of(*st), c, s0.stream, tot);
+            st->last_hits = (size_t) c.hit_count; st->last_blob = (size_t) c.blob_used;
+        }
         mark();
         if (tot.err_key != ~0ULL) throw KvqError(KVQ_ERR_FASTQ_FORMAT, format_error_message(tot.err_key));
         *out = finish_result(e, tot, now_ms() - t_begin);
