@@ -23,7 +23,7 @@
 #define KVQ_P2_LONG 0x4000              // ... | flag: only templates longer than the short class can match here
 #define KVQ_ROW 1024                    // bytes one warp loads per step (32 lanes x 32 bytes)
 #ifndef KVQ_OWN_ROWS
-#define KVQ_OWN_ROWS 7
+#define KVQ_OWN_ROWS 10
 #endif
 #ifndef KVQ_T2L
 #define KVQ_T2L 1                       // separate T2 bitmap of the long templates for whole-read probes

@@ -26,7 +26,7 @@
 namespace {
 
 #ifndef KVQ_NWARPS
-#define KVQ_NWARPS 23                   // warps per CTA (one CTA per SM): 80 registers, 225 KB shared memory
+#define KVQ_NWARPS 23                   // warps per CTA (one CTA per SM): 80 registers, 216 KB shared memory
 #endif
 #ifndef KVQ_PREFETCH
 #define KVQ_PREFETCH 1
@@ -47,10 +47,8 @@ constexpr int DRAIN = 32 * NS;
 constexpr int SEEDQ = 2 * DRAIN;
 
 struct WarpSmem {
-    uint32_t nl[NWORDS + 1];                // newline plane, bit j of word w <=> byte 32 w + j is '\n'
-    uint32_t ge[NWORDS + 1];                // quality plane, byte >= Amin
-    uint32_t pk[2 * NWORDS + 4];            // code plane: 2 bits per byte, contiguous stream
-    uint16_t pre[NWORDS];                   // newlines of the region before word w
+    uint32_t ge[NWORDS + 1];                // quality plane, bit j of word w <=> byte 32 w + j is >= Amin
+    alignas(16) uint32_t pk[2 * NWORDS + 4]; // code plane: 2 bits per byte, contiguous stream (read as uint2)
     uint16_t nlpos[NLCAP];                  // positions of the newlines ranked [base, base + NLCAP)
     uint32_t rd[32];                        // reads of the round: start | length << 16 (0 = none)
     uint32_t seedq[SEEDQ];
@@ -245,7 +243,7 @@ __device__ __forceinline__ void reduce_row(WarpSmem &s, const TileCtx &t, const 
         nl_owned += __popc(own >= 32 ? nl : own <= 0 ? 0u : (nl & ((1u << own) - 1u)));
         cnt = __popc(nl);
     }
-    s.nl[w] = nl; s.ge[w] = ge;
+    s.ge[w] = ge;                                   // (the newline mask is not kept: ranks + the first NLCAP positions are)
     reinterpret_cast<uint2 *>(s.pk)[w] = pk;
     uint32_t inc = cnt;
 #pragma unroll
@@ -254,7 +252,6 @@ __device__ __forceinline__ void reduce_row(WarpSmem &s, const TileCtx &t, const 
         if (lane >= o) inc += n;
     }
     uint32_t rank = nl_total + inc - cnt;
-    s.pre[w] = (uint16_t) rank;
     nl_total += __shfl_sync(0xffffffffu, inc, 31);
     while (nl && rank < NLCAP) {                    // positions of the first NLCAP newlines (round 0)
         s.nlpos[rank++] = (uint16_t) ((w << 5) + __ffs(nl) - 1);
@@ -262,14 +259,30 @@ __device__ __forceinline__ void reduce_row(WarpSmem &s, const TileCtx &t, const 
     }
 }
 
-// positions of the newlines ranked [base, base + NLCAP), from the plane
-__device__ __forceinline__ void scatter_newlines(WarpSmem &s, int nrows, int base, int lane)
+// positions of the newlines ranked [base, base + NLCAP) -- only tiles with more than NLCAP
+// newlines (very short records) come here: the masks are computed again from the bytes (L1/L2)
+__device__ __forceinline__ void scatter_newlines(WarpSmem &s, const KvqBatch &b, const TileCtx &t, int nrows,
+                                                 int base, int lane)
 {
+    int total = 0;
 #pragma unroll 1
     for (int row = 0; row < nrows; row++) {
         const int w = row * 32 + lane;
-        uint32_t m = s.nl[w];
-        int rank = (int) s.pre[w] - base;
+        const Row r = load_row(b, t, row, lane);
+        uint32_t m = gather32(gather2(nl_bits(r.a.x), nl_bits(r.a.y)), gather2(nl_bits(r.a.z), nl_bits(r.a.w)),
+                              gather2(nl_bits(r.b.x), nl_bits(r.b.y)), gather2(nl_bits(r.b.z), nl_bits(r.b.w)));
+        const int lo = t.shift - (w << 5), hi = t.lim - (w << 5);
+        if (lo > 0) m &= lo >= 32 ? 0u : (0xFFFFFFFFu << lo);
+        if (hi < 32) m &= hi <= 0 ? 0u : ((1u << hi) - 1u);
+        const int cnt = __popc(m);
+        int inc = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += n;
+        }
+        int rank = total + inc - cnt - base;
+        total += __shfl_sync(0xffffffffu, inc, 31);
         while (m && rank < NLCAP) {
             if (rank >= 0) s.nlpos[rank] = (uint16_t) ((w << 5) + __ffs(m) - 1);
             rank++;
@@ -977,7 +990,7 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         for (int k0 = 0; k0 < nown; k0 += 32) {
             const int base = k0 > 0 ? 4 * k0 + off - 1 : 0;
             __syncwarp();
-            if (k0 > 0) scatter_newlines(s, nrows, base, lane);
+            if (k0 > 0) scatter_newlines(s, b, tc, nrows, base, lane);
             __syncwarp();
             run_round<BIG>(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
         }
