@@ -27,7 +27,7 @@ namespace {
 constexpr int64_t REF_CHUNK = 1024 * 1024;          // SCANBUFSIZE, workhorse.c:15
 constexpr int64_t BATCH_BYTES = 64ll << 20;         // stream bytes per GPU batch
 constexpr int64_t BATCH_PAD = 256;                  // readable slack behind a batch
-constexpr int NSLOT = 3;
+constexpr int NSLOT = 4;                // batches: one being cut by the producer, up to three on the GPU
 
 struct KvqError {
     int cls; std::string msg;
@@ -700,7 +700,7 @@ struct Slot {                           // one batch in flight
     DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs, d_surv; size_t surv_cap = 0;
     PinBuf h_ctr, h_seg, h_tiles;
     TileBufs tiles;
-    cudaStream_t stream = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t stream = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copied = nullptr;
     size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
     int64_t data_bytes = 0;
 };
@@ -733,6 +733,7 @@ struct kvq_engine {
     int err_cls = 0; std::string err_msg;
     LiveStats live;
     Slot slots[NSLOT]; bool slots_ready = false;
+    cudaStream_t copy_stream = nullptr;             // all batch uploads, back to back (concurrent H2D copies share the link badly)
     Accum acc;
     TemplateSet tpl;
     PinBuf pin_out, pin_acc;                        // page-locked staging of the result copies
@@ -777,7 +778,9 @@ void init_slots(kvq_engine *e)
         s.blob_cap = 32u << 20; s.d_blob.ensure(s.blob_cap);
         CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
         CK(cudaEventCreate(&s.ev0)); CK(cudaEventCreate(&s.ev1));
+        CK(cudaEventCreateWithFlags(&s.ev_copied, cudaEventDisableTiming));
     }
+    CK(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
     e->slots_ready = true;
 }
 
@@ -848,11 +851,13 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     s.d_seg.ensure(hb.cuts.size() * 8); s.h_seg.ensure(hb.cuts.size() * 8);
     memcpy(s.h_seg.p, hb.cuts.data(), hb.cuts.size() * 8);
     if (hb.borrowed) {
-        CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes, cudaMemcpyHostToDevice, s.stream));
-        CK(cudaMemsetAsync(s.d_data.as<char>() + hb.nbytes, 0, BATCH_PAD, s.stream));
+        CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes, cudaMemcpyHostToDevice, e->copy_stream));
+        CK(cudaMemsetAsync(s.d_data.as<char>() + hb.nbytes, 0, BATCH_PAD, e->copy_stream));
     } else {
-        CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes + BATCH_PAD, cudaMemcpyHostToDevice, s.stream));
+        CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes + BATCH_PAD, cudaMemcpyHostToDevice, e->copy_stream));
     }
+    CK(cudaEventRecord(s.ev_copied, e->copy_stream));
+    CK(cudaStreamWaitEvent(s.stream, s.ev_copied, 0));
     CK(cudaMemcpyAsync(s.d_seg.p, s.h_seg.p, hb.cuts.size() * 8, cudaMemcpyHostToDevice, s.stream));
     std::vector<longlong2> tiles;
     build_tiles(hb.cuts, tiles);
@@ -1072,11 +1077,12 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
 }
 
 // The whole streaming scan: a producer thread cuts the stream into pinned batches while this
-// thread keeps up to two batches in flight on the GPU.
+// thread keeps up to three batches in flight on the GPU.
 kvq_result *run_stream_scan(kvq_engine *e, std::vector<std::string> names,
                             std::vector<std::pair<const char *, int64_t>> mems)
 {
     const double t_begin = now_ms();
+    const bool trace_stream = getenv("KVQ_TRACE") != nullptr;
     init_slots(e);
     reset_accum(e);
     StreamCutter cutter(std::move(names), std::move(mems), &e->live);
@@ -1101,13 +1107,19 @@ kvq_result *run_stream_scan(kvq_engine *e, std::vector<std::string> names,
     std::deque<int> inflight;
     try {
         for (;;) {
+            const double tq0 = now_ms();
             int si = ready_q.pop();
             if (si < 0) break;
+            const double tq1 = now_ms();
             launch_slot(e, e->slots[si], tot);
+            const double tq2 = now_ms();
             inflight.push_back(si);
-            if ((int) inflight.size() >= 2) {
+            if ((int) inflight.size() >= NSLOT - 1) {      // keep the copy engine fed: two H2D copies queued behind the running one
                 int done = inflight.front(); inflight.pop_front();
                 harvest_slot(e, e->slots[done], tot);
+                if (trace_stream)
+                    fprintf(stderr, "[kvq trace] t %.3f wait-ready %.3f launch %.3f harvest %.3f\n",
+                            tq0 - t_begin, tq1 - tq0, tq2 - tq1, now_ms() - tq2);
                 free_q.push(done);
                 if (tot.err_key != ~0ULL) e->stop = 1;          // first format error ends the scan
             }
@@ -1212,7 +1224,9 @@ void kvq_destroy(kvq_engine *e)
         if (s.stream) cudaStreamDestroy(s.stream);
         if (s.ev0) cudaEventDestroy(s.ev0);
         if (s.ev1) cudaEventDestroy(s.ev1);
+        if (s.ev_copied) cudaEventDestroy(s.ev_copied);
     }
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     delete e;
 }
 
