@@ -424,6 +424,13 @@ void append_table(std::vector<std::pair<uint32_t, uint4>> &items, uint32_t nkeys
     }
 }
 
+// KVQ_EXACT_PHASE=1: no tile infers its line phase from its own line starts (tests of the exact path)
+int exact_phase_knob()
+{
+    const char *v = getenv("KVQ_EXACT_PHASE");
+    return v && atoi(v) > 0 ? 1 : 0;
+}
+
 struct TemplateSet {
     int nseqs = 0, nplus = 0; int64_t cov_total = 0;
     std::vector<int32_t> len;
@@ -449,7 +456,7 @@ struct TemplateSet {
             if (ok) {
                 put(lens, sizeof(int32_t) * (size_t) n);
                 for (int i = 0; i < n; i++) put(seqs[i], (size_t) lens[i]);
-                if (key == cache_key && d_bytes.p) { par.want_hits = 1; par.accumulate = 1; return; }
+                if (key == cache_key && d_bytes.p) { par.want_hits = 1; par.accumulate = 1; par.exact_phase = exact_phase_knob(); return; }
                 cache_key.swap(key);
             } else cache_key.clear();
         }
@@ -591,7 +598,7 @@ struct TemplateSet {
         par.maxerrors = E; par.minoverlap = O; par.minreadlength = cfg.minreadlength;
         par.amin = (int) (signed char) cfg.Amin;
         par.seed_ok = seed_ok; par.npieces = pieces < 1 ? 1 : pieces; par.max_seqlen = max_len;
-        par.want_hits = 1; par.accumulate = 1;
+        par.want_hits = 1; par.accumulate = 1; par.exact_phase = exact_phase_knob();
         par.t1x = t1x_on ? KVQ_T1X_K * pieces : 0;
         par.min_seed_rl = KVQ_SEED_K * par.npieces;
         par.div_magic = (uint32_t) ((65536 + par.npieces - 1) / par.npieces);
@@ -871,20 +878,26 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     tot.stream_bytes += hb.nbytes;
 }
 
-// The survivor queue of the scan kernel overflowed: the emit and long-record kernels did nothing.
-// Run the batch again with a queue that fits (its size is known now) and take the counters of
-// that run.
+// The survivor queue of the scan kernel overflowed, or a tile's inferred line phase was
+// contradicted (malformed input): the emit and long-record kernels did nothing.  Run the batch
+// again with a queue that fits (its size is known now) / with exact line phases and take the
+// counters of that run.
 void rerun_for_survivors(kvq_engine *e, const KvqBatch &b, const OutBufs &ob, KvqCounters &c, PinBuf &h_ctr,
                          cudaStream_t st, ScanTotals &tot)
 {
-    if (c.surv_count <= ob.surv_cap) return;
-    ob.surv_cap = (size_t) (c.surv_count + c.surv_count / 8 + 1024);
-    ob.surv.ensure(ob.surv_cap * sizeof(KvqSurvRec));
-    enqueue_kernels(e, b, e->tpl.par, make_out(e, ob), st, nullptr, nullptr);
-    CK(cudaMemcpyAsync(h_ctr.p, ob.ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    c = *h_ctr.as<KvqCounters>();
-    tot.launches += 3; tot.acc_fetched = false; tot.spec_hits = tot.spec_blob = 0;
+    KvqParams p = e->tpl.par;
+    for (int it = 0; it < 4 && (c.surv_count > ob.surv_cap || c.phase_retry); it++) {
+        if (c.phase_retry) p.exact_phase = 1;
+        if (c.surv_count > ob.surv_cap) {
+            ob.surv_cap = (size_t) (c.surv_count + c.surv_count / 8 + 1024);
+            ob.surv.ensure(ob.surv_cap * sizeof(KvqSurvRec));
+        }
+        enqueue_kernels(e, b, p, make_out(e, ob), st, nullptr, nullptr);
+        CK(cudaMemcpyAsync(h_ctr.p, ob.ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        c = *h_ctr.as<KvqCounters>();
+        tot.launches += 3; tot.acc_fetched = false; tot.spec_hits = tot.spec_blob = 0;
+    }
 }
 
 // Fetch hits of a finished batch (re-running it with larger buffers when they overflowed).

@@ -51,6 +51,8 @@ struct KvqParams {
     int32_t o_piece[KVQ_MAX_PIECES];    // floor(j * minoverlap / npieces)
     int32_t n2max;                      // T2 probe slots per read: 3 * npieces (5 * npieces for large sets)
     int32_t accumulate;                 // 0: re-run after a buffer overflow, counters already taken
+    int32_t exact_phase;                // 1: every tile waits for its line phase from the look-back chain (re-run after a
+                                        //    tile's locally inferred phase was contradicted: malformed input)
 };
 
 struct KvqTemplates {
@@ -133,7 +135,8 @@ struct KvqCounters {                    // zeroed before every batch launch (exc
     unsigned int tile_next;             // dynamic tile queue (tiles are claimed in stream order)
     unsigned int long_next;
     unsigned int overflow_rounds;
-    unsigned int pad;
+    unsigned int phase_retry;           // tiles whose inferred line phase was contradicted by the newline counts: the emit and
+                                        // long-record kernels do nothing, the host re-runs the batch with exact_phase
 };
 
 struct KvqOut {

@@ -291,32 +291,6 @@ __device__ __forceinline__ void scatter_newlines(WarpSmem &s, const KvqBatch &b,
     }
 }
 
-// Newlines of the bytes a tile owns, from global memory (the look-ahead pass: the count of tile
-// N+1 is published before tile N is processed, so nobody ever waits long in the look-back).
-__device__ __forceinline__ int count_owned_newlines(const KvqBatch &b, int64_t a0, int shift, int tile_end, int lane)
-{
-    uint32_t cnt = 0;
-    const uint4 *src = reinterpret_cast<const uint4 *>(b.data + a0);
-#if KVQ_PREFETCH
-    for (int x = lane * 128; x < tile_end; x += 32 * 128)           // whole tile on its way to L2
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(b.data + a0 + x));
-#endif
-#pragma unroll 3
-    for (int row = 0; row <= OWN_ROWS; row++) {
-        const int w = row * 32 + lane;
-        if ((w << 5) < tile_end) {
-            const uint4 a = __ldg(src + 2 * w), c = __ldg(src + 2 * w + 1);
-            uint32_t nl = gather32(gather2(nl_bits(a.x), nl_bits(a.y)), gather2(nl_bits(a.z), nl_bits(a.w)),
-                                   gather2(nl_bits(c.x), nl_bits(c.y)), gather2(nl_bits(c.z), nl_bits(c.w)));
-            const int lo = shift - (w << 5), hi = tile_end - (w << 5);
-            if (lo > 0) nl &= 0xFFFFFFFFu << lo;
-            if (hi < 32) nl &= (1u << hi) - 1u;
-            cnt += __popc(nl);
-        }
-    }
-    return (int) __reduce_add_sync(0xffffffffu, cnt);
-}
-
 // Decoupled look-back over the tiles of one segment, 32 predecessors per step.  Status word:
 // bit3 = inclusive prefix, bit2 = tile aggregate, bits 1:0 = newline count mod 4.  Tiles are
 // claimed in stream order, so a predecessor is always resident or finished.
@@ -339,6 +313,36 @@ __device__ __forceinline__ int resolve_phase(const KvqBatch &b, int tile, int fi
     acc &= 3;
     if (lane == 0) st[tile] = 8u | (uint32_t) ((acc + n_tile) & 3);
     return acc;
+}
+
+// Line phase of a tile from its own line starts.  In a stream the reference accepts, every line
+// 0 of a record starts with '@' and every line 2 with '+' (workhorse.c:1037-1048 checks nothing
+// else), so the true phase passes this test on the first lines of the tile; when it is the ONLY
+// phase that passes, it is the phase -- no waiting for the predecessors' newline counts.
+// Returns -1 when the test is not decisive (fewer than a record's worth of lines, or quality
+// lines that happen to start with '@').  The caller still checks the phase against the counts
+// after the tile is done; a contradiction (malformed input: the reference raises) re-runs the
+// batch with exact phases, so a wrong guess never reaches a result.
+__device__ __forceinline__ int infer_phase(const WarpSmem &s, const KvqBatch &b, const TileCtx &t, int n_all, int lane)
+{
+    __syncwarp();                                   // nlpos[] of this tile
+    const int m = n_all < 32 ? n_all : 32;
+    uint8_t ch = 0; bool v = false;
+    if (lane < m) {
+        const int64_t at = t.a0 + (int64_t) s.nlpos[lane] + 1;      // first byte of the line after newline `lane`
+        if (at < t.seg_end) { ch = __ldg(b.data + at); v = true; }
+    }
+    const uint32_t valid = __ballot_sync(0xffffffffu, v);
+    const uint32_t not_at = valid & ~__ballot_sync(0xffffffffu, ch == '@');
+    const uint32_t not_plus = valid & ~__ballot_sync(0xffffffffu, ch == '+');
+    int found = -1, nfound = 0;
+#pragma unroll
+    for (int ph = 0; ph < 4; ph++) {
+        // the line after newline i is line (ph + i + 1) & 3 of its record
+        const uint32_t l0 = 0x11111111u << ((3 - ph) & 3), l2 = 0x11111111u << ((1 - ph) & 3);
+        if (!((l0 & not_at) | (l2 & not_plus))) { found = ph; nfound++; }
+    }
+    return nfound == 1 ? found : -1;
 }
 
 // ---- P2 ---------------------------------------------------------------------------------------
@@ -918,28 +922,30 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
     const uint32_t cl = (uint32_t) (p.amin & 0x7F) * 0x01010101u;
     const uint32_t *tpk = (!BIG && t.packed_words <= KVQ_TPK_SMEM_WORDS) ? sh.tpk : t.packed;
 
-    // Tile geometry + look-ahead: claim the next tile, count the newlines of the bytes it owns
-    // and publish them (status word, see resolve_phase) before the current tile is processed.
-    struct Claim { int tile; int n_tile; int first; int64_t t0, seg_end; };
+    // Tile geometry: claim the next tile and start its bytes on their way to L2.
+    struct Claim { int tile; int first; int64_t t0, seg_end; };
     auto claim = [&]() -> Claim {
         int tile = 0;
         if (lane == 0) tile = (int) atomicAdd(&o.ctr->tile_next, 1u);
         tile = __shfl_sync(0xffffffffu, tile, 0);
-        if (tile >= b.ntiles) return Claim{-1, 0, 0, 0, 0};
+        if (tile >= b.ntiles) return Claim{-1, 0, 0, 0};
         const longlong2 ti = __ldg(b.tile_info + tile);            // {start, segment end | first << 62}
         const int64_t t0 = ti.x, seg_end = ti.y & ~(1ll << 62);
         const int first = (int) ((ti.y >> 62) & 1);
-        const int64_t a0 = t0 & ~(int64_t) 31;
-        const int64_t t1 = t0 + KVQ_TILE < seg_end ? t0 + KVQ_TILE : seg_end;
-        const int n = count_owned_newlines(b, a0, (int) (t0 - a0), (int) (t1 - a0), lane);
-        if (lane == 0)
-            ((volatile uint32_t *) b.tile_status)[tile] = (first ? 8u : 4u) | (uint32_t) (n & 3);
-        return Claim{tile, n, first, t0, seg_end};
+#if KVQ_PREFETCH
+        {
+            const int64_t a0 = t0 & ~(int64_t) 31;
+            const int64_t t1 = t0 + KVQ_TILE + KVQ_ROW < seg_end ? t0 + KVQ_TILE + KVQ_ROW : seg_end;
+            for (int64_t x = a0 + lane * 128; x < t1; x += 32 * 128)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(b.data + x));
+        }
+#endif
+        return Claim{tile, first, t0, seg_end};
     };
 
-    Claim cur{-2, 0, 0, 0, 0};                      // -2: nothing claimed yet, -1: queue exhausted
+    Claim cur{-2, 0, 0, 0};                         // -2: nothing claimed yet, -1: queue exhausted
     for (;;) {
-        const Claim nxt = claim();                  // the one look-ahead site (code size matters here)
+        const Claim nxt = claim();
         if (cur.tile >= 0) {
         const int tile = cur.tile;
         const int64_t t0 = cur.t0, seg_end = cur.seg_end;
@@ -954,33 +960,43 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         tc.seg_end = seg_end;
         const Ctx c{b, t, p, o, tc, tpk};
 
-        // line phase of the tile (its count was published one tile ago), then the owned records
-        const int n_tile = cur.n_tile;
-        const int phase = resolve_phase(b, tile, tc.first, n_tile, lane);
-        // newline rank -> record-relative numbering (see parse_record)
-        const int off = tc.first ? 0 : ((3 - phase) & 3) + 1;
-        const int vmax_tile = n_tile - 1 - off;
-        int nown = 0;
-        if (tc.first || vmax_tile >= -1) nown = (vmax_tile + 1) / 4 + 1;
-        const int need = nown > 0 ? 4 * (nown - 1) + 3 + off : -1;  // rank of the last newline the tile needs
-
-        // P1: rows 0 .. OWN_ROWS (the tile plus one row of spill) with two rows of loads in
-        // flight, then further spill rows while the last owned record is incomplete
-        uint32_t n_all = 0, n_own = 0;
-        int nrows = 0;
+        // P1: rows 0 .. OWN_ROWS (the tile plus one row of spill) in pairs -- two register sets
+        // taking turns, one row being reduced while the other is in flight.  After row OWN_ROWS
+        // the newlines the tile owns are counted: the count is published for the look-back
+        // chain and the line phase of the tile settled (see settle_phase); further spill rows
+        // follow while the last owned record is incomplete.
+        static_assert(OWN_ROWS % 2 == 0 && EXTRA_ROWS == 2, "row pairs");
+        uint32_t n_all = 0, n_own = 0;                  // n_own: per-lane partial counts
+        int nrows = 0, off = 0, nown = 0, phase = 0, n_tile = 0;
+        bool inferred = false;
         {
-            Row r0 = load_row(b, tc, 0, lane), r1 = load_row(b, tc, 1, lane);
+            Row ra = load_row(b, tc, 0, lane), rb = load_row(b, tc, 1, lane);
 #pragma unroll 1
-            for (int row = 0; row < MAX_ROWS; row++) {
-                if (row > OWN_ROWS) {
-                    if (need < (int) n_all || row * KVQ_ROW >= tc.lim) break;
-                    r0 = load_row(b, tc, row, lane);
-                }
-                Row r2 = r1;
-                if (row + 2 <= OWN_ROWS) r2 = load_row(b, tc, row + 2, lane);
-                reduce_row<NEG>(s, tc, r0, row, lane, cl, n_all, n_own);
-                r0 = r1; r1 = r2;
+            for (int row = 0; row < MAX_ROWS; row += 2) {
+                reduce_row<NEG>(s, tc, ra, row, lane, cl, n_all, n_own);
                 nrows = row + 1;
+                if (row + 2 <= OWN_ROWS) ra = load_row(b, tc, row + 2, lane);
+                if (row == OWN_ROWS) {
+                    // line phase of the tile = newlines of its segment before it, mod 4
+                    n_tile = (int) __reduce_add_sync(0xffffffffu, n_own);
+                    if (lane == 0)
+                        ((volatile uint32_t *) b.tile_status)[tile] = (tc.first ? 8u : 4u) | (uint32_t) (n_tile & 3);
+                    if (!tc.first) {
+                        phase = p.exact_phase ? -1 : infer_phase(s, b, tc, (int) n_all, lane);
+                        inferred = phase >= 0;
+                        if (!inferred) phase = resolve_phase(b, tile, 0, n_tile, lane);
+                    }
+                    // newline rank -> record-relative numbering (see parse_record)
+                    off = tc.first ? 0 : ((3 - phase) & 3) + 1;
+                    const int vmax_tile = n_tile - 1 - off;
+                    if (tc.first || vmax_tile >= -1) nown = (vmax_tile + 1) / 4 + 1;
+                    const int need = nown > 0 ? 4 * (nown - 1) + 3 + off : -1;  // rank of the last newline the tile needs
+                    if (need < (int) n_all || (row + 1) * KVQ_ROW >= tc.lim) break;
+                    rb = load_row(b, tc, row + 1, lane);
+                }
+                reduce_row<NEG>(s, tc, rb, row + 1, lane, cl, n_all, n_own);
+                nrows = row + 2;
+                if (row + 3 <= OWN_ROWS) rb = load_row(b, tc, row + 3, lane);
             }
         }
         const bool at_seg_end = tc.a0 + (int64_t) nrows * KVQ_ROW >= seg_end;
@@ -994,6 +1010,11 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
             __syncwarp();
             run_round<BIG>(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
         }
+        // an inferred phase is checked against the newline counts of the predecessors (all
+        // published by now: nobody waits here); a contradiction means malformed input -- the
+        // batch is run again with exact phases
+        if (inferred && resolve_phase(b, tile, 0, n_tile, lane) != phase && lane == 0)
+            atomicAdd(&o.ctr->phase_retry, 1u);
         __syncwarp();                               // planes are reused by the next tile
         }
         cur = nxt;
@@ -1033,7 +1054,7 @@ kvq_long_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
 {
     const int lane = threadIdx.x & 31;
     const unsigned long long n = o.ctr->long_count < o.long_cap ? o.ctr->long_count : o.long_cap;
-    if (o.ctr->surv_count > o.surv_cap) return;     // the batch is run again with a larger survivor queue
+    if (o.ctr->surv_count > o.surv_cap || o.ctr->phase_retry) return;   // the batch is run again
     for (;;) {
         unsigned int i = 0;
         if (lane == 0) i = atomicAdd(&o.ctr->long_next, 1u);
@@ -1093,7 +1114,7 @@ kvq_emit_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     uint32_t *rpk = rpk_all[wib];
     const unsigned long long n = o.ctr->surv_count;
-    if (n > o.surv_cap) return;
+    if (n > o.surv_cap || o.ctr->phase_retry) return;
     const unsigned long long nw = (unsigned long long) gridDim.x * 8;
     for (unsigned long long i = (unsigned long long) blockIdx.x * 8 + wib; i < n; i += nw) {
         const uint4 q0 = __ldg(reinterpret_cast<const uint4 *>(o.surv + i));

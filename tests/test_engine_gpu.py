@@ -343,6 +343,65 @@ def test_long_and_odd_records(gpu_engine, checker, tmp_path):
         assert_same_result(got, want, what='tiny %r' % text[:10])
 
 
+def test_line_phase_inference(gpu_engine, checker, tmp_path, monkeypatch):
+    """A tile takes its line phase (newlines of the segment before it, mod 4) from its own line
+    starts when only one phase makes every line 0 start with '@' and every line 2 with '+', and
+    checks it against the newline counts afterwards.  Well-formed streams whose quality lines
+    start with '@' / '+' (inference not decisive: the tile waits for the counts), and malformed
+    ones (a missing or an extra line shifts the phase of everything behind it: the batch is run
+    again with exact phases) must give the reference's result or the reference's exception."""
+    rng = random.Random(11)
+    rs = lambda n: ''.join(rng.choice('ACGT') for _ in range(n))
+    tpl = rs(60)
+    seqs = [tpl, synth.revcomp(tpl.encode()).decode()]
+
+    def records(n, q0=lambda i: None):
+        out = []
+        for i in range(n):
+            L = rng.randint(60, 160)
+            sq = list(rs(L))
+            if i % 5 == 0:
+                a = rng.randint(0, L - 30); sq[a:a + 60] = list(tpl)
+            sq = ''.join(sq)[:L]
+            q = ''.join(rng.choice('5?II') for _ in range(L))
+            if q0(i):
+                q = q0(i) + q[1:]
+            out.append('@r%d\n%s\n+\n%s\n' % (i, sq, q))
+        return out
+
+    cases = {}
+    cases['clean'] = records(3000)
+    cases['quality starts with @'] = records(3000, lambda i: '@')
+    cases['quality starts with +'] = records(3000, lambda i: '+')
+    cases['some quality lines start with @ or +'] = records(3000, lambda i: '@+'[i % 2] if i % 3 == 0 else None)
+    r = records(3000); r[1700] = r[1700].replace('\n+\n', '\n'); cases['a record without its + line'] = r
+    r = records(3000); r[900] = r[900] + '\n'; cases['an empty line between two records'] = r
+    r = records(3000); r[2500] = '_' + r[2500][1:]; cases['a late record without @'] = r
+    r = records(3000); r.append('garbage\n+\nmore garbage'); cases['junk partial record at the end'] = r
+    r = records(3000, lambda i: '@'); r[1200] = r[1200].replace('\n+\n', '\n-\n'); cases['bad + line among @ quality lines'] = r
+    cfg = dict(maxerrors=1, minoverlap=20, minreadlength=20, Amin='5')
+    fn = str(tmp_path / 'phase.fastq')
+    for name, recs in cases.items():
+        open(fn, 'w').write(''.join(recs))
+        try:
+            want, werr = oracle(checker, fn, seqs, cfg), None
+        except checker.OracleError as o:
+            want, werr = None, o.msg
+        for exact in ('0', '1'):
+            monkeypatch.setenv('KVQ_EXACT_PHASE', exact)
+            gpu_engine.config(**cfg)
+            what = '%s (exact phases: %s)' % (name, exact)
+            if werr is None:
+                got = gpu_engine.findseqs(fn, seqs)
+                assert len(want['hits']) > 300, what
+                assert_same_result(got, want, what=what)
+            else:
+                with pytest.raises(FastqFileFormatException) as e:
+                    gpu_engine.findseqs(fn, seqs)
+                assert str(e.value) == werr, what
+    monkeypatch.delenv('KVQ_EXACT_PHASE')
+
+
 def test_many_hits_overflow_buffers(gpu_engine, checker, tmp_path):
     """poly-A reads against a poly-A template: far more hits than reads; exercises the hit
     buffer regrow + re-run path"""
