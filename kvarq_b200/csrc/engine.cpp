@@ -388,6 +388,8 @@ struct SeedTable {
             const uint32_t b0 = off[k], b1 = off[k + 1];
             if (b0 == b1) continue;
             const uint32_t more = b1 - b0 - 1;
+            if (more > 65000u)                  // (a seed word of the scan kernel counts bucket entries in 16 bits)
+                throw KvqError(KVQ_ERR_RUNTIME, "template set not supported: more than 65000 templates share one 8-mer at the same seed class");
             if (more >= KVQ_HEAD_MORE) ovf.push_back(make_uint4(more, 0, 0, 0));
             uint4 f = ent[b0];
             f.x |= (more >= KVQ_HEAD_MORE ? KVQ_HEAD_MORE : more) << 24; f.w = (uint32_t) ovf.size();

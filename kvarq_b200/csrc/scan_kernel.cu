@@ -685,17 +685,69 @@ __device__ __forceinline__ int drain_seeds(WarpSmem &s, const Ctx &c, int base, 
     return ncand;
 }
 
-// Drain the first n seeds of the stack 64 at a time.
-template <bool BIG>
-__device__ __forceinline__ void drain_chunks(WarpSmem &s, const Ctx &c, int n, int lane, ThreadStats &ts)
+// Small sets (a few hundred templates, most buckets hold one entry): one CANDIDATE per seed and
+// pass.  A seed word carries the index k of the bucket entry it stands for (bits 31:16, 0 = the
+// head); a seed whose bucket has further entries goes back on the stack as (seed, k + 1) -- into
+// the slots this pass has just emptied -- and is verified together with whatever comes next, so
+// the (few) overflow entries never cost a pass of their own with most lanes idle.
+__device__ __forceinline__ int drain_lean(WarpSmem &s, const Ctx &c, int base, int n, int lane, ThreadStats &ts)
 {
-    for (int done = 0; done < n; done += DRAIN)
-        ts.cands += (unsigned long long) drain_seeds<BIG>(s, c, done, min(DRAIN, n - done), lane);
+    const KvqTemplates &t = c.t; const KvqParams &p = c.p;
+    const bool act = lane < n;
+    uint32_t sd = 0;
+    int d = 0, rd0 = 0, rl = 0, pos = 0, kind = 0, seq = 0;
+    bool surv = false, again = false;
+    if (act) {
+        sd = s.seedq[base + lane];
+        const uint32_t rdv = s.rd[sd & 31];
+        pos = (int) ((sd >> 5) & 1023);
+        kind = (int) ((sd >> 15) & 1u);
+        const uint32_t k = sd >> 16;
+        rd0 = (int) (rdv & 0xFFFFu); rl = (int) (rdv >> 16);
+        if (kind) pos = __ldg(t.p2_tab + rl * KVQ_P2W + pos) & KVQ_P2_POS;      // T2 seeds carry their probe slot
+        const uint32_t hidx = extract16(s.pk, rd0 + pos) & 0xFFFFu;
+        const uint4 *ent = kind ? t.t2_ent : t.t1_ent;
+        uint4 en = __ldg((kind ? t.t2_first : t.t1_first) + hidx);
+        uint32_t more = en.x >> 24;
+        if (more == KVQ_HEAD_MORE) more = __ldg(&ent[en.w - 1].x);
+        again = k < more;
+        if (k) en = __ldg(ent + en.w + k - 1);
+        ts.cands++;
+        const int sl = (int) (en.y >> 16);
+        d = (int) (en.y & 0xFFFFu) - pos;
+        seq = (int) (en.x & 0xFFFFFFu);
+        // overlap of the diagonal; Hamming distance in code space first (a lower bound of the
+        // byte distance, most candidates die on the first word), the acceptance rule after
+        const int ro = d < 0 ? -d : 0, to = d > 0 ? d : 0;
+        const int L = min(rl - ro, sl - to);
+        const uint32_t *tpk = c.tpk + en.z;
+        int e = 0;
+        for (int j = 0; j < L && e <= p.maxerrors; j += 16) {
+            uint32_t xw = extract16(s.pk, rd0 + ro + j) ^ extract16_t(tpk, to + j);
+            uint32_t m = (xw | (xw >> 1)) & 0x55555555u;
+            if (L - j < 16) m &= (1u << (2 * (L - j))) - 1u;
+            e += __popc(m);
+        }
+        if (e <= p.maxerrors) {
+            int ro2, to2, L2, rule;
+            surv = diag_rule(d, rl, sl, p.minoverlap, ro2, to2, L2, rule) != 0;
+            // template inside read (rule c): some T1 piece fires for every accepted alignment and
+            // T1 comes first in the canonical order, so a T2 seed never emits such a diagonal
+            if (kind && d <= 0 && d + rl >= sl) surv = false;
+        }
+    }
+    // survivors go to the emit kernel (byte-exact confirm, canonical-seed dedupe, emission)
+    push_survivors(c.o, surv, c.tc.a0 + rd0, rl, seq, d, (kind << 16) | pos, lane);
+    const uint32_t m = __ballot_sync(0xffffffffu, again);
+    __syncwarp();                                   // every lane has read its seed
+    if (again) s.seedq[base + __popc(m & ((1u << lane) - 1u))] = sd + 0x10000u;
+    __syncwarp();
+    return __popc(m);
 }
 
 // Push the set bits of every lane's `hits` (bit j = read offset posbase + j) on the seed stack:
-// a lane reserves room with one shared-memory atomic.  Whenever 32 seeds are waiting they are
-// drained with all lanes busy; what does not fit the stack waits for the drain.
+// a lane reserves room with one shared-memory atomic.  Whenever 32 seeds are waiting the top 32
+// are drained with all lanes busy; what does not fit the stack waits for the drain.
 template <bool BIG>
 __device__ __forceinline__ void push_seeds(WarpSmem &s, const Ctx &c, uint32_t hits, uint32_t tag,
                                            int posbase, bool flush, int lane, ThreadStats &ts)
@@ -713,17 +765,15 @@ __device__ __forceinline__ void push_seeds(WarpSmem &s, const Ctx &c, uint32_t h
         const uint32_t q = s.qn;
         const uint32_t left = __ballot_sync(0xffffffffu, hits != 0);       // only when the stack is full
         if (q < DRAIN && !left && !(flush && q)) break;
-        const int stored = q < SEEDQ ? (int) q : SEEDQ;
-        const int take = (left || flush) ? stored : (stored & ~(DRAIN - 1));
-        drain_chunks<BIG>(s, c, take, lane, ts);
-        const int rem = stored - take;                                      // < DRAIN, moves to the front
-        uint32_t keep[NS];
-#pragma unroll
-        for (int u = 0; u < NS; u++) keep[u] = lane + 32 * u < rem ? s.seedq[take + lane + 32 * u] : 0u;
+        int stored = q < SEEDQ ? (int) q : SEEDQ;
+        const bool all = flush && !left;
+        while (stored >= DRAIN || (all && stored > 0)) {
+            const int n = stored < DRAIN ? stored : DRAIN, base = stored - n;
+            if (BIG) { ts.cands += (unsigned long long) drain_seeds<true>(s, c, base, n, lane); stored = base; }
+            else stored = base + drain_lean(s, c, base, n, lane, ts);
+        }
         __syncwarp();
-#pragma unroll
-        for (int u = 0; u < NS; u++) if (lane + 32 * u < rem) s.seedq[lane + 32 * u] = keep[u];
-        if (lane == 0) s.qn = (uint32_t) rem;
+        if (lane == 0) s.qn = (uint32_t) stored;
         __syncwarp();
         if (!left) break;
     }
