@@ -1027,15 +1027,19 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
                 nrows = row + 1;
                 if (row + 2 <= OWN_ROWS) ra = load_row(b, tc, row + 2, lane);
                 if (row == OWN_ROWS) {
-                    // line phase of the tile = newlines of its segment before it, mod 4
+                    // line phase of the tile = newlines of its segment before it, mod 4.  A tile that
+                    // infers its phase publishes phase + count as its inclusive prefix right away
+                    // (status bit 3) and compares its phase with the predecessor's prefix when it is
+                    // done: every neighbouring pair consistent <=> every inferred phase right (the
+                    // first tile of a segment is exact).  A tile that cannot infer publishes its
+                    // count (bit 2) and walks back to the nearest prefix.
                     n_tile = (int) __reduce_add_sync(0xffffffffu, n_own);
+                    if (!tc.first && !p.exact_phase) phase = infer_phase(s, b, tc, (int) n_all, lane);
+                    inferred = !tc.first && !p.exact_phase && phase >= 0;
                     if (lane == 0)
-                        ((volatile uint32_t *) b.tile_status)[tile] = (tc.first ? 8u : 4u) | (uint32_t) (n_tile & 3);
-                    if (!tc.first) {
-                        phase = p.exact_phase ? -1 : infer_phase(s, b, tc, (int) n_all, lane);
-                        inferred = phase >= 0;
-                        if (!inferred) phase = resolve_phase(b, tile, 0, n_tile, lane);
-                    }
+                        ((volatile uint32_t *) b.tile_status)[tile] =
+                            (tc.first || inferred) ? 8u | (uint32_t) ((phase + n_tile) & 3) : 4u | (uint32_t) (n_tile & 3);
+                    if (!tc.first && !inferred) phase = resolve_phase(b, tile, 0, n_tile, lane);
                     // newline rank -> record-relative numbering (see parse_record)
                     off = tc.first ? 0 : ((3 - phase) & 3) + 1;
                     const int vmax_tile = n_tile - 1 - off;
@@ -1060,11 +1064,14 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
             __syncwarp();
             run_round<BIG>(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
         }
-        // an inferred phase is checked against the newline counts of the predecessors (all
-        // published by now: nobody waits here); a contradiction means malformed input -- the
-        // batch is run again with exact phases
-        if (inferred && resolve_phase(b, tile, 0, n_tile, lane) != phase && lane == 0)
-            atomicAdd(&o.ctr->phase_retry, 1u);
+        // an inferred phase is checked against the predecessor's prefix (published long ago:
+        // nobody waits here); a contradiction means malformed input -- the batch is run again
+        // with exact phases
+        if (inferred) {
+            uint32_t v;
+            while (!((v = ((volatile uint32_t *) b.tile_status)[tile - 1]) & 8u)) __nanosleep(40);
+            if ((int) (v & 3u) != phase && lane == 0) atomicAdd(&o.ctr->phase_retry, 1u);
+        }
         __syncwarp();                               // planes are reused by the next tile
         }
         cur = nxt;
