@@ -506,7 +506,7 @@ struct TemplateSet {
         const int OX = KVQ_T1X_K * pieces;                          // overlaps >= OX hold E+1 disjoint 12-mers
         std::vector<std::vector<std::pair<uint32_t, uint4>>> itH(pieces), itT(pieces);
         std::vector<std::pair<uint32_t, uint4>> itX;
-        std::vector<uint32_t> t2e, t2x; std::vector<uint8_t> t1mask;
+        std::vector<uint32_t> t2e, t2x; std::vector<uint8_t> t1mask, t1roles(KVQ_NKEYS, 0);
         if (t1x_on) t1mask.assign(KVQ_NKEYS, 0);
         if (t1x_on) { t2e.assign(KVQ_BITMAP_WORDS, 0); t2x.assign(KVQ_T1X_WORDS, 0); }
         int max_len = 0;
@@ -526,6 +526,9 @@ struct TemplateSet {
             for (int j = 0; j < pieces; j++) {
                 const int toff = (int) ((int64_t) j * sl / pieces);
                 it1.push_back({kmer_key(s + toff), entry(toff)});
+                if (sl / pieces >= KVQ_T1_LONG) {       // small sets: roles of the piece's two 8-mers (scan_kernel.cu, probe_roles)
+                    t1roles[kmer_key(s + toff)] |= 2; t1roles[kmer_key(s + toff + KVQ_SEED_K)] |= 4;
+                } else t1roles[kmer_key(s + toff)] |= 1;
                 if (t1x_on)                             // probe filter: the 3 code bits after the 8-mer (bases 8, 9)
                     t1mask[kmer_key(s + toff)] |= sl / pieces >= KVQ_T1X_K
                         ? (uint8_t) (1u << (code_of(s[toff + 8]) | ((code_of(s[toff + 9]) & 1u) << 2))) : (uint8_t) 0xFF;
@@ -582,7 +585,7 @@ struct TemplateSet {
 
         upload(d_bytes, bytes); upload(d_boff, boff); upload(d_packed, packed, 4); upload(d_poff, poff);
         upload(d_len, len); upload(d_seedable, seedable); upload(d_exh, exh);
-        upload(d_bm1, t1x_on ? t1mask : t1.present); upload(d_off1, t1.off); upload(d_ent1, t1.ovf); upload(d_first1, t1.first);
+        upload(d_bm1, t1x_on ? t1mask : t1roles); upload(d_off1, t1.off); upload(d_ent1, t1.ovf); upload(d_first1, t1.first);
         upload(d_bm2, t2.bitmap); upload(d_off2, t2.off); upload(d_ent2, t2.ovf); upload(d_first2, t2.first);
         upload(d_bm2l, bm2l); if (t1x_on) { upload(d_t1x, t1x); upload(d_t2e, t2e); upload(d_t2x, t2x); }
         upload(d_covoff, covoff);

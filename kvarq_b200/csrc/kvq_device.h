@@ -7,6 +7,7 @@
 #define KVQ_SEED_K 8                    // seed length in bases (16-bit keys)
 #define KVQ_NKEYS (1 << (2 * KVQ_SEED_K))
 #define KVQ_BITMAP_WORDS (KVQ_NKEYS / 32)
+#define KVQ_T1_LONG 16                  // small sets: pieces at least this long fire with their first 16 bases (two 8-mers 8 apart)
 #define KVQ_T1X_K 12                   // T1 second level: a piece's first 12 bases (24-bit key), bitmap in L2
 #define KVQ_T1X_MIN_PIECES 2048         // template sets with more T1 pieces run the kernel variant with the second level
 #define KVQ_T1X_WORDS ((1 << (2 * KVQ_T1X_K)) / 32)

@@ -510,6 +510,8 @@ __device__ __noinline__ bool canonical_seed(const KvqParams &p, const KvqTemplat
         if (x16 & 0xFFFFu) continue;
         // second level (drain_seeds): where 12 bases fit both the piece and the read they must match too
         if (BIG && sl >= p.t1x && (pj + KVQ_T1X_K > rl || (x16 & 0xFFFFFFu))) continue;
+        // small sets (probe_roles): a piece of 16 bases or more fires with its first 16 bases in the read
+        if (!BIG && sl >= KVQ_T1_LONG * p.npieces && (pj + KVQ_T1_LONG > rl || x16)) continue;
         return kind == 0 && pos == pj;
     }
     const int16_t *p2 = t.p2_tab + rl * KVQ_P2W;
@@ -806,6 +808,34 @@ __device__ __forceinline__ uint32_t probe_word(const uint8_t *t1, uint32_t x0, u
     return hits;
 }
 
+// Small sets: the byte of a key holds the ROLES of the 8-mer -- bit 0: first 8-mer of a piece
+// shorter than 16 bases (fires alone), bit 1: first 8-mer of a longer piece, bit 2: second
+// 8-mer (bases 8..15) of a longer piece.  A longer piece fires only where both its 8-mers are
+// found 8 offsets apart (its first 16 bases lie in the read and match: see canonical_seed), which
+// removes nearly every chance 8-mer match before it becomes a seed.  Roles of the 32 offsets of
+// one 32-byte word, one 4-bit field per offset, 8 offsets per register.
+struct Roles { uint32_t g0, g1, g2, g3; };
+__device__ __forceinline__ Roles probe_roles(const uint8_t *t1, uint32_t x0, uint32_t x1, uint32_t x2)
+{
+    Roles r{0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const uint32_t sa = j ? funnel_r(x0, x1, 2 * j) : x0;       // bases j .. j+15
+        const uint32_t sb = j ? funnel_r(x1, x2, 2 * j) : x1;       // bases 16+j .. 31+j
+        r.g0 += (uint32_t) t1[sa & 0xFFFFu] << (4 * j);
+        r.g1 += (uint32_t) t1[sa >> 16] << (4 * j);
+        r.g2 += (uint32_t) t1[sb & 0xFFFFu] << (4 * j);
+        r.g3 += (uint32_t) t1[sb >> 16] << (4 * j);
+    }
+    return r;
+}
+// 8 offsets (fields of a) -> 8 bits: fires alone, or longer-piece key with the second 8-mer 8 offsets on (same field of nxt)
+__device__ __forceinline__ uint32_t fire8(uint32_t a, uint32_t nxt)
+{
+    const uint32_t f = (a | ((a >> 1) & (nxt >> 2))) & 0x11111111u;
+    return __dp4a(((f | (f >> 3)) & 0x03030303u), 0x40100401u, 0u);
+}
+
 } // namespace
 
 namespace {
@@ -908,23 +938,38 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
             }
         }
         // T1: every read offset rd0 .. rd0 + rl - 8, one 32-byte word of the code plane per step;
-        // the last step pushes the T2 seeds and flushes the stack (one push / drain site)
+        // the last step pushes the T2 seeds and flushes the stack (one push / drain site).
+        // Small sets decide the last 8 offsets of a word one step later (they need the roles of
+        // the next word's first 8 offsets): the window of a step starts 8 offsets before its word.
         const int w0 = rd0 >> 5, plast = rd0 + rl - KVQ_SEED_K;
         const int nw = seedable ? (plast >> 5) - w0 + 1 : 0;
         const int maxnw = __reduce_max_sync(0xffffffffu, nw);
-        for (int q = 0; q <= maxnw; q++) {
+        const int last = BIG ? maxnw : maxnw + 1;
+        uint32_t carry = 0;
+        for (int q = 0; q <= last; q++) {
             uint32_t hits = 0, tag = (uint32_t) lane;
             const int w = w0 + q;
-            int posbase = (w << 5) - rd0;
-            if (q < nw) {
-                const uint2 x = reinterpret_cast<const uint2 *>(s.pk)[w];
-                hits = probe_word<BIG>(sh.t1, x.x, x.y, s.pk[2 * w + 2]);
-                const int lo = rd0 - (w << 5), hi = plast - (w << 5);
-                if (lo > 0) hits &= 0xFFFFFFFFu << lo;
-                if (hi < 31) hits &= (2u << hi) - 1u;
+            const int wb = BIG ? (w << 5) : (w << 5) - 8;           // coordinate of bit 0 of `hits`
+            int posbase = wb - rd0;
+            if (BIG ? q < nw : (nw > 0 && q <= nw)) {
+                if (BIG) {
+                    const uint2 x = reinterpret_cast<const uint2 *>(s.pk)[w];
+                    hits = probe_word<BIG>(sh.t1, x.x, x.y, s.pk[2 * w + 2]);
+                } else {
+                    Roles r{0u, 0u, 0u, 0u};
+                    if (q < nw) {
+                        const uint2 x = reinterpret_cast<const uint2 *>(s.pk)[w];
+                        r = probe_roles(sh.t1, x.x, x.y, s.pk[2 * w + 2]);
+                    }
+                    hits = fire8(carry, r.g0) | (fire8(r.g0, r.g1) << 8) | (fire8(r.g1, r.g2) << 16) | (fire8(r.g2, r.g3) << 24);
+                    carry = r.g3;
+                }
+                const int lo = rd0 - wb, hi = plast - wb;
+                if (lo > 0) hits &= lo >= 32 ? 0u : 0xFFFFFFFFu << lo;
+                if (hi < 31) hits &= hi < 0 ? 0u : (2u << hi) - 1u;
             }
-            if (q == maxnw) { hits = hit2; tag |= 1u << 15; posbase = 0; }
-            push_seeds<BIG>(s, c, hits, tag, posbase, q == maxnw, lane, ts);
+            if (q == last) { hits = hit2; tag |= 1u << 15; posbase = 0; }
+            push_seeds<BIG>(s, c, hits, tag, posbase, q == last, lane, ts);
         }
     }
     // exhaustive matcher (emit kernel): reads the seed scheme does not cover against every
