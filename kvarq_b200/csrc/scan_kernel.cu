@@ -34,6 +34,12 @@ namespace {
 #ifndef KVQ_NS
 #define KVQ_NS 1
 #endif
+#ifndef KVQ_FMASK
+#define KVQ_FMASK 1
+#endif
+#ifndef KVQ_ROW_SETS
+#define KVQ_ROW_SETS 3                  // register sets the rows of a tile rotate through (rows in flight + 1)
+#endif
 constexpr int NWARPS = KVQ_NWARPS;          // warps per CTA (shared memory bound)
 constexpr int THREADS = NWARPS * 32;
 constexpr int OWN_ROWS = KVQ_OWN_ROWS;
@@ -965,8 +971,14 @@ __device__ void run_round(WarpSmem &s, Smem &sh, const Ctx &c, int k0, int nown,
                     carry = r.g3;
                 }
                 const int lo = rd0 - wb, hi = plast - wb;
+#if KVQ_FMASK
+                // bits lo .. hi of the window (clamping funnel shifts: a shift of 32 or more gives 0)
+                hits &= __funnelshift_lc(0u, 0xFFFFFFFFu, (uint32_t) max(lo, 0))
+                      & __funnelshift_rc(0xFFFFFFFFu, 0u, (uint32_t) max(31 - hi, 0));
+#else
                 if (lo > 0) hits &= lo >= 32 ? 0u : 0xFFFFFFFFu << lo;
                 if (hi < 31) hits &= hi < 0 ? 0u : (2u << hi) - 1u;
+#endif
             }
             if (q == last) { hits = hit2; tag |= 1u << 15; posbase = 0; }
             push_seeds<BIG>(s, c, hits, tag, posbase, q == last, lane, ts);
@@ -1055,8 +1067,8 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         tc.seg_end = seg_end;
         const Ctx c{b, t, p, o, tc, tpk};
 
-        // P1: rows 0 .. OWN_ROWS (the tile plus one row of spill) in pairs -- two register sets
-        // taking turns, one row being reduced while the other is in flight.  After row OWN_ROWS
+        // P1: rows 0 .. OWN_ROWS (the tile plus one row of spill) through three register sets
+        // taking turns, one row being reduced while two are in flight.  After row OWN_ROWS
         // the newlines the tile owns are counted: the count is published for the look-back
         // chain and the line phase of the tile settled (see settle_phase); further spill rows
         // follow while the last owned record is incomplete.
@@ -1064,6 +1076,49 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         uint32_t n_all = 0, n_own = 0;                  // n_own: per-lane partial counts
         int nrows = 0, off = 0, nown = 0, phase = 0, n_tile = 0;
         bool inferred = false;
+        // settles the phase after row OWN_ROWS; true if spill row `next` is needed
+        auto settle = [&](int next) -> bool {
+            // line phase of the tile = newlines of its segment before it, mod 4.  A tile that
+            // infers its phase publishes phase + count as its inclusive prefix right away
+            // (status bit 3) and compares its phase with the predecessor's prefix when it is
+            // done: every neighbouring pair consistent <=> every inferred phase right (the
+            // first tile of a segment is exact).  A tile that cannot infer publishes its
+            // count (bit 2) and walks back to the nearest prefix.
+            n_tile = (int) __reduce_add_sync(0xffffffffu, n_own);
+            if (!tc.first && !p.exact_phase) phase = infer_phase(s, b, tc, (int) n_all, lane);
+            inferred = !tc.first && !p.exact_phase && phase >= 0;
+            if (lane == 0)
+                ((volatile uint32_t *) b.tile_status)[tile] =
+                    (tc.first || inferred) ? 8u | (uint32_t) ((phase + n_tile) & 3) : 4u | (uint32_t) (n_tile & 3);
+            if (!tc.first && !inferred) phase = resolve_phase(b, tile, 0, n_tile, lane);
+            // newline rank -> record-relative numbering (see parse_record)
+            off = tc.first ? 0 : ((3 - phase) & 3) + 1;
+            const int vmax_tile = n_tile - 1 - off;
+            if (tc.first || vmax_tile >= -1) nown = (vmax_tile + 1) / 4 + 1;
+            const int need = nown > 0 ? 4 * (nown - 1) + 3 + off : -1;  // rank of the last newline the tile needs
+            return !(need < (int) n_all || next * KVQ_ROW >= tc.lim);
+        };
+#if KVQ_ROW_SETS == 3
+        {
+            static_assert((OWN_ROWS + 2) % 3 == 0, "row triples");
+            Row ra = load_row(b, tc, 0, lane), rb = load_row(b, tc, 1, lane), rc = load_row(b, tc, 2, lane);
+#pragma unroll 1
+            for (int row = 0; row < MAX_ROWS; row += 3) {
+                reduce_row<NEG>(s, tc, ra, row, lane, cl, n_all, n_own);
+                if (row + 3 <= OWN_ROWS) ra = load_row(b, tc, row + 3, lane);
+                reduce_row<NEG>(s, tc, rb, row + 1, lane, cl, n_all, n_own);
+                nrows = row + 2;
+                if (row + 4 <= OWN_ROWS) rb = load_row(b, tc, row + 4, lane);
+                if (row + 1 == OWN_ROWS) {
+                    if (!settle(row + 2)) break;
+                    rc = load_row(b, tc, row + 2, lane);
+                }
+                reduce_row<NEG>(s, tc, rc, row + 2, lane, cl, n_all, n_own);
+                nrows = row + 3;
+                if (row + 5 <= OWN_ROWS) rc = load_row(b, tc, row + 5, lane);
+            }
+        }
+#else
         {
             Row ra = load_row(b, tc, 0, lane), rb = load_row(b, tc, 1, lane);
 #pragma unroll 1
@@ -1072,25 +1127,7 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
                 nrows = row + 1;
                 if (row + 2 <= OWN_ROWS) ra = load_row(b, tc, row + 2, lane);
                 if (row == OWN_ROWS) {
-                    // line phase of the tile = newlines of its segment before it, mod 4.  A tile that
-                    // infers its phase publishes phase + count as its inclusive prefix right away
-                    // (status bit 3) and compares its phase with the predecessor's prefix when it is
-                    // done: every neighbouring pair consistent <=> every inferred phase right (the
-                    // first tile of a segment is exact).  A tile that cannot infer publishes its
-                    // count (bit 2) and walks back to the nearest prefix.
-                    n_tile = (int) __reduce_add_sync(0xffffffffu, n_own);
-                    if (!tc.first && !p.exact_phase) phase = infer_phase(s, b, tc, (int) n_all, lane);
-                    inferred = !tc.first && !p.exact_phase && phase >= 0;
-                    if (lane == 0)
-                        ((volatile uint32_t *) b.tile_status)[tile] =
-                            (tc.first || inferred) ? 8u | (uint32_t) ((phase + n_tile) & 3) : 4u | (uint32_t) (n_tile & 3);
-                    if (!tc.first && !inferred) phase = resolve_phase(b, tile, 0, n_tile, lane);
-                    // newline rank -> record-relative numbering (see parse_record)
-                    off = tc.first ? 0 : ((3 - phase) & 3) + 1;
-                    const int vmax_tile = n_tile - 1 - off;
-                    if (tc.first || vmax_tile >= -1) nown = (vmax_tile + 1) / 4 + 1;
-                    const int need = nown > 0 ? 4 * (nown - 1) + 3 + off : -1;  // rank of the last newline the tile needs
-                    if (need < (int) n_all || (row + 1) * KVQ_ROW >= tc.lim) break;
+                    if (!settle(row + 1)) break;
                     rb = load_row(b, tc, row + 1, lane);
                 }
                 reduce_row<NEG>(s, tc, rb, row + 1, lane, cl, n_all, n_own);
@@ -1098,6 +1135,7 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
                 if (row + 3 <= OWN_ROWS) rb = load_row(b, tc, row + 3, lane);
             }
         }
+#endif
         const bool at_seg_end = tc.a0 + (int64_t) nrows * KVQ_ROW >= seg_end;
 #ifdef KVQ_ONLY_P1
         if (n_all == 0x7fffffff)
