@@ -748,7 +748,7 @@ struct kvq_engine {
     cudaStream_t copy_stream = nullptr;             // all batch uploads, back to back (concurrent H2D copies share the link badly)
     Accum acc;
     TemplateSet tpl;
-    PinBuf pin_out, pin_acc;                        // page-locked staging of the result copies
+    PinBuf pin_out, pin_acc, pin_ord;               // page-locked staging of the result copies
     SortScratch scratch;
 
     void set_error(int cls, const std::string &m) { std::lock_guard<std::mutex> g(mu); err_cls = cls; err_msg = m; }
@@ -760,6 +760,8 @@ struct kvq_staged {
     TileBufs tiles;
     size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
     size_t last_hits = 0, last_blob = 0;            // result sizes of the previous scan of this stream
+    // hits put into the reference's order on the device (KvqOrder)
+    DevBuf o_keys, o_bkt, o_start, o_cursor, o_members, o_lens, o_src, o_hits, o_offsets, o_blob, o_status;
     int64_t nbytes = 0, base_fpos = 0, parsed = 0, total = 0; int nseg = 0;
 };
 
@@ -803,6 +805,8 @@ struct ScanTotals {
     double kernel_ms = 0; int64_t launches = 0, h2d = 0, d2h = 0, stream_bytes = 0;
     bool acc_fetched = false;           // per-template accumulators already in e->pin_acc (copied behind the kernels)
     size_t spec_hits = 0, spec_blob = 0; // hit records / hitseq bytes already in e->pin_out (copied behind the kernels)
+    // hits already in the reference's order (ordered on the device): page-locked staging, see kvq_scan_staged
+    const KvqHitOut *s_hits = nullptr; const long long *s_off = nullptr; const char *s_blob = nullptr; size_t s_n = 0, s_nb = 0;
     ScanTotals() { memset(rls, 0, sizeof(rls)); }
 };
 
@@ -1051,6 +1055,13 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
         std::sort(keys.begin(), keys.end(), before);
     }
     const double t_sorted = now_ms();
+    static_assert(sizeof(KvqHitOut) == sizeof(kvq_hit_t) && sizeof(kvq_hit_t) == 24, "device hit layout == kvq_hit_t");
+    if (tot.s_hits) {                   // ordered on the device: three plain copies
+        r->hits.resize(tot.s_n); r->offsets.resize(tot.s_n + 1); r->blob.resize(tot.s_nb);
+        if (tot.s_n) memcpy(r->hits.data(), tot.s_hits, tot.s_n * sizeof(kvq_hit_t));
+        memcpy(r->offsets.data(), tot.s_off, (tot.s_n + 1) * sizeof(int64_t));
+        if (tot.s_nb) memcpy(r->blob.data(), tot.s_blob, tot.s_nb);
+    } else {
     r->hits.resize(nh); r->offsets.resize(nh + 1); r->blob.resize(tot.blob.size());
     int64_t at = 0;
     for (size_t i = 0; i < nh; i++) {
@@ -1061,6 +1072,7 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
         at += h.length;
     }
     r->offsets[nh] = at;
+    }
     const double t_ordered = now_ms();
     fill_stats(e, r->stats, tot.rls, tot.longest, tot.records);
     const int ns = e->tpl.nseqs; const int64_t nc = e->tpl.cov_total;
@@ -1439,7 +1451,39 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
             e->pin_acc.ensure(words * 8);
             CK(cudaMemcpyAsync(e->pin_acc.p, e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost, s0.stream));
         }
-        if (want_hits && st->last_hits) {   // ... and so do as many hits as the previous scan of this stream had (+25 %)
+        // the hits are put into the reference's order on the device (KvqOrder) and ride behind the
+        // kernels too: as many as the previous scan of this stream had (+25 %)
+        static const bool host_order = getenv("KVQ_HOST_ORDER") != nullptr;
+        const bool dev_order = want_hits && !host_order && st->nbytes > 0;
+        KvqOrder ord{};
+        size_t oh = 0, oo = 0, ob = 0;          // staging layout: hits | offsets | blob
+        auto fetch_ordered = [&](size_t nh, size_t nb) {
+            oh = 0; oo = (nh * sizeof(KvqHitOut) + 255) & ~(size_t) 255; ob = oo + (((nh + 1) * 8 + 255) & ~(size_t) 255);
+            e->pin_out.ensure(ob + nb + 256);
+            char *pin = e->pin_out.as<char>();
+            if (nh) CK(cudaMemcpyAsync(pin + oh, ord.hits, nh * sizeof(KvqHitOut), cudaMemcpyDeviceToHost, s0.stream));
+            CK(cudaMemcpyAsync(pin + oo, ord.offsets, (nh + 1) * 8, cudaMemcpyDeviceToHost, s0.stream));
+            if (nb) CK(cudaMemcpyAsync(pin + ob, ord.blob, nb, cudaMemcpyDeviceToHost, s0.stream));
+        };
+        if (dev_order) {
+            const size_t cap = std::min<size_t>(st->hit_cap, KVQ_ORDER_MAX);
+            st->o_keys.ensure(cap * 16); st->o_bkt.ensure(cap * 4); st->o_start.ensure((cap + 1) * 4); st->o_cursor.ensure((cap + 1) * 4);
+            st->o_members.ensure(cap * 4); st->o_lens.ensure((cap + 1) * 4); st->o_src.ensure(cap * 8); st->o_hits.ensure(cap * sizeof(KvqHitOut));
+            st->o_offsets.ensure((cap + 1) * 8); st->o_blob.ensure(st->blob_cap); st->o_status.ensure(16);
+            ord.keys = st->o_keys.as<ulonglong2>(); ord.bkt = st->o_bkt.as<uint32_t>(); ord.start = st->o_start.as<uint32_t>();
+            ord.cursor = st->o_cursor.as<uint32_t>(); ord.members = st->o_members.as<uint32_t>(); ord.lens = st->o_lens.as<uint32_t>();
+            ord.src = st->o_src.as<unsigned long long>(); ord.hits = st->o_hits.as<KvqHitOut>(); ord.offsets = st->o_offsets.as<long long>();
+            ord.blob = st->o_blob.as<uint8_t>(); ord.status = st->o_status.as<uint32_t>();
+            ord.cap = (uint32_t) cap; ord.blob_cap = st->blob_cap; ord.span = st->nbytes;
+            cuda_check((cudaError_t) kvq_launch_order(b, o, ord, s0.stream), "order kernels launch");
+            e->pin_ord.ensure(16);
+            CK(cudaMemcpyAsync(e->pin_ord.p, ord.status, 4, cudaMemcpyDeviceToHost, s0.stream));
+            if (st->last_hits) {
+                tot.spec_hits = std::min(cap, st->last_hits + st->last_hits / 4 + 64);
+                tot.spec_blob = std::min(st->blob_cap, st->last_blob + st->last_blob / 4 + 4096);
+                fetch_ordered(tot.spec_hits, tot.spec_blob);
+            }
+        } else if (want_hits && st->last_hits) {
             tot.spec_hits = std::min(st->hit_cap, st->last_hits + st->last_hits / 4 + 64);
             tot.spec_blob = std::min(st->blob_cap, st->last_blob + st->last_blob / 4 + 4096);
             const size_t hb = (tot.spec_hits * sizeof(KvqHitRec) + 255) & ~(size_t) 255;
@@ -1453,10 +1497,27 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1));
         tot.kernel_ms = ms; tot.launches = 3; tot.stream_bytes = st->nbytes; tot.d2h = sizeof(KvqCounters);
         KvqCounters c = *s0.h_ctr.as<KvqCounters>();
+        const int64_t launches0 = tot.launches;
         rerun_for_survivors(e, b, bufs_of(*st), c, s0.h_ctr, s0.stream, tot);
         add_counters(e, c, tot);
         if (want_hits) {
-            collect_hits(e, b, bufs_of(*st), c, s0.stream, tot);
+            // ordered on the device unless the batch had to be run again or a buffer overflowed
+            const bool ordered = dev_order && tot.launches == launches0 && c.hit_count <= st->hit_cap && c.blob_used <= st->blob_cap
+                              && *e->pin_ord.as<uint32_t>() == (uint32_t) c.hit_count && c.hit_count <= ord.cap;
+            if (ordered) {
+                const size_t nh = (size_t) c.hit_count, nb = (size_t) c.blob_used;
+                if (!(nh <= tot.spec_hits && nb <= tot.spec_blob && st->last_hits)) {
+                    fetch_ordered(nh, nb);
+                    CK(cudaStreamSynchronize(s0.stream));
+                }
+                const char *pin = e->pin_out.as<char>();
+                tot.s_hits = reinterpret_cast<const KvqHitOut *>(pin + oh); tot.s_off = reinterpret_cast<const long long *>(pin + oo);
+                tot.s_blob = pin + ob; tot.s_n = nh; tot.s_nb = nb;
+                tot.launches += 6; tot.d2h += (int64_t) (nh * sizeof(KvqHitOut) + (nh + 1) * 8 + nb + 4);
+            } else {
+                if (dev_order) tot.spec_hits = tot.spec_blob = 0;       // the staging holds ordered arrays, not raw records
+                collect_hits(e, b, bufs_of(*st), c, s0.stream, tot);
+            }
             st->last_hits = (size_t) c.hit_count; st->last_blob = (size_t) c.blob_used;
         }
         mark();

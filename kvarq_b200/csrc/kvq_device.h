@@ -159,3 +159,34 @@ int kvq_launch_long(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p
 int kvq_launch_emit(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p, const KvqOut &o,
                     int sm_count, void *stream);
 int kvq_scan_smem_bytes(void);
+
+// ---- result marshalling on the device (HBM-resident scans): the hits of a batch in the reference's
+// nthreads=1 order (workhorse.c:1107-1175: file order, template, rules (a) (b) shifts descending,
+// (c)/(d) ascending), hitseqs back to back in that order.  Bucket sort over the stream position
+// (as many buckets as hits), rank inside the (tiny) buckets by comparing full keys.
+#define KVQ_ORDER_MAX 65536             // more hits than this: the host sorts (engine.cpp, finish_result)
+
+struct KvqHitOut {                      // == kvq_hit_t (include/kvarq_b200.h)
+    int32_t seq_nr, seq_pos;
+    int64_t file_pos;
+    int32_t length, readlength;
+};
+
+struct KvqOrder {
+    ulonglong2 *keys;                   // [cap] {file_pos, seq_nr << 34 | rule << 32 | shift key}
+    uint32_t *bkt;                      // [cap] bucket of hit i
+    uint32_t *start;                    // [cap + 1] bucket starts (exclusive scan of the counts; zeroed before the launch)
+    uint32_t *cursor;                   // [cap + 1]
+    uint32_t *members;                  // [cap] hit indices grouped by bucket
+    uint32_t *lens;                     // [cap + 1] hitseq offsets by rank (scan of the lengths), 32-bit: cap * 512 bytes at most
+    unsigned long long *src;            // [cap] blob offset of the hit with rank r
+    KvqHitOut *hits;                    // [cap] by rank
+    long long *offsets;                 // [cap + 1] by rank
+    uint8_t *blob;                      // [blob_cap] hitseqs by rank
+    uint32_t *status;                   // [0] number of ordered hits, 0xFFFFFFFF = not ordered (overflow, re-run pending, too many)
+    uint32_t cap; uint32_t pad;
+    unsigned long long blob_cap;
+    long long span;                     // stream bytes of the batch (bucket scale)
+};
+
+int kvq_launch_order(const KvqBatch &b, const KvqOut &o, const KvqOrder &ord, void *stream);

@@ -1330,3 +1330,138 @@ int kvq_launch_long(const KvqBatch &b, const KvqTemplates &t, const KvqParams &p
     kvq_long_kernel<<<sm_count, 256, 0, (cudaStream_t) stream>>>(b, t, p, o);
     return (int) cudaGetLastError();
 }
+
+// ---- hits in the reference's order, on the device (see KvqOrder) -------------------------------
+namespace {
+
+// hits to order, or 0 when the host has to do it (buffers overflowed, batch will be run again, too many)
+__device__ __forceinline__ uint32_t order_n(const KvqOut &o, const KvqOrder &ord)
+{
+    const KvqCounters &c = *o.ctr;
+    if (c.surv_count > o.surv_cap || c.phase_retry || c.hit_count > o.hit_cap || c.blob_used > o.blob_cap ||
+        c.hit_count > ord.cap || c.blob_used > ord.blob_cap)
+        return 0;
+    return (uint32_t) c.hit_count;
+}
+
+__device__ __forceinline__ bool key_before(const ulonglong2 &a, uint32_t ia, const ulonglong2 &b, uint32_t ib)
+{
+    return a.x != b.x ? a.x < b.x : a.y != b.y ? a.y < b.y : ia < ib;
+}
+
+__global__ void __launch_bounds__(256)
+kvq_order_count(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqOut o, const __grid_constant__ KvqOrder ord)
+{
+    const uint32_t n = order_n(o, ord);
+    if (blockIdx.x == 0 && threadIdx.x == 0) ord.status[0] = n ? n : (o.ctr->hit_count == 0 ? 0u : 0xFFFFFFFFu);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const KvqHitRec h = o.hits[i];
+        const int sh = h.rule == 0 ? h.seq_pos : h.rule == 1 ? -h.seq_pos : (h.seq_pos < 0 ? -h.seq_pos : h.seq_pos);
+        ulonglong2 k;
+        k.x = (unsigned long long) h.file_pos;
+        k.y = ((unsigned long long) (uint32_t) h.seq_nr << 34) | ((unsigned long long) (uint32_t) h.rule << 32)
+            | (unsigned long long) (uint32_t) (sh + (1 << 30));
+        ord.keys[i] = k;
+        const unsigned long long rel = (unsigned long long) (h.file_pos - b.base_fpos);
+        unsigned long long bk = rel * n / (unsigned long long) (ord.span + 1);
+        if (bk >= n) bk = n - 1;
+        ord.bkt[i] = (uint32_t) bk;
+        atomicAdd(&ord.start[bk + 1], 1u);
+    }
+}
+
+// one block: x[0 .. n] -> inclusive prefix sums in place (x[0] stays), copy to y when given
+__device__ __forceinline__ void block_scan(uint32_t *x, uint32_t *y, uint32_t n)
+{
+    __shared__ uint32_t part[1024];
+    const uint32_t per = (n + 1 + 1023) / 1024, lo = threadIdx.x * per, hi = min(lo + per, n + 1);
+    uint32_t sum = 0;
+    for (uint32_t i = lo; i < hi; i++) sum += x[i];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        const uint32_t v = threadIdx.x >= d ? part[threadIdx.x - d] : 0u;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = part[threadIdx.x] - sum;
+    for (uint32_t i = lo; i < hi; i++) { run += x[i]; x[i] = run; if (y) y[i] = run; }
+}
+
+__global__ void __launch_bounds__(1024)
+kvq_order_scan_starts(const __grid_constant__ KvqOut o, const __grid_constant__ KvqOrder ord)
+{
+    const uint32_t n = order_n(o, ord);
+    if (n) block_scan(ord.start, ord.cursor, n);
+}
+
+__global__ void __launch_bounds__(256)
+kvq_order_place(const __grid_constant__ KvqOut o, const __grid_constant__ KvqOrder ord)
+{
+    const uint32_t n = order_n(o, ord);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        ord.members[atomicAdd(&ord.cursor[ord.bkt[i]], 1u)] = i;
+}
+
+__global__ void __launch_bounds__(256)
+kvq_order_rank(const __grid_constant__ KvqOut o, const __grid_constant__ KvqOrder ord)
+{
+    const uint32_t n = order_n(o, ord);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t bk = ord.bkt[i];
+        const ulonglong2 me = ord.keys[i];
+        uint32_t r = ord.start[bk];
+        for (uint32_t m = ord.start[bk]; m < ord.start[bk + 1]; m++) {
+            const uint32_t j = ord.members[m];
+            if (j != i && key_before(ord.keys[j], j, me, i)) r++;
+        }
+        const KvqHitRec h = o.hits[i];
+        KvqHitOut q; q.seq_nr = h.seq_nr; q.seq_pos = h.seq_pos; q.file_pos = h.file_pos; q.length = h.length; q.readlength = h.readlength;
+        ord.hits[r] = q;
+        ord.src[r] = (unsigned long long) h.blob_off;
+        ord.lens[r + 1] = (uint32_t) h.length;
+        if (i == 0) ord.lens[0] = 0;
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+kvq_order_scan_lens(const __grid_constant__ KvqOut o, const __grid_constant__ KvqOrder ord)
+{
+    const uint32_t n = order_n(o, ord);
+    if (n) block_scan(ord.lens, nullptr, n);
+}
+
+__global__ void __launch_bounds__(256)
+kvq_order_copy(const __grid_constant__ KvqOut o, const __grid_constant__ KvqOrder ord)
+{
+    const uint32_t n = order_n(o, ord);
+    const int lane = threadIdx.x & 31;
+    const uint32_t nw = gridDim.x * (blockDim.x >> 5);
+    for (uint32_t r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n; r += nw) {
+        const uint32_t at = ord.lens[r], len = ord.lens[r + 1] - at;
+        const uint8_t *from = o.blob + ord.src[r];
+        for (uint32_t x = lane; x < len; x += 32) ord.blob[at + x] = from[x];
+        if (lane == 0) {
+            ord.offsets[r] = (long long) at;
+            if (r + 1 == n) ord.offsets[n] = (long long) ord.lens[n];
+        }
+    }
+}
+
+} // namespace
+
+int kvq_launch_order(const KvqBatch &b, const KvqOut &o, const KvqOrder &ord, void *stream)
+{
+    cudaStream_t st = (cudaStream_t) stream;
+    cudaError_t e = cudaMemsetAsync(ord.start, 0, ((size_t) ord.cap + 1) * 4, st);
+    if (e != cudaSuccess) return (int) e;
+    const int g = (int) ((ord.cap + 255) / 256);
+    kvq_order_count<<<g, 256, 0, st>>>(b, o, ord);
+    kvq_order_scan_starts<<<1, 1024, 0, st>>>(o, ord);
+    kvq_order_place<<<g, 256, 0, st>>>(o, ord);
+    kvq_order_rank<<<g, 256, 0, st>>>(o, ord);
+    kvq_order_scan_lens<<<1, 1024, 0, st>>>(o, ord);
+    kvq_order_copy<<<296, 256, 0, st>>>(o, ord);
+    return (int) cudaGetLastError();
+}

@@ -415,6 +415,47 @@ def test_many_hits_overflow_buffers(gpu_engine, checker, tmp_path):
     assert_same_result(got, want, what='poly-A')
 
 
+def test_staged_hits_ordered_on_device(checker, tmp_path):
+    """HBM-resident scans put their hits into the reference's order on the device (bucket sort over
+    the stream position, ties -- several hits of one read, duplicate hits -- by template / rule /
+    shift): repeated scans (result copies sized by the previous scan), a template set that makes
+    most reads hit several templates, more hits than the device path takes (host sort), no hits."""
+    from kvarq_b200.engine import Engine
+    rng = random.Random(23)
+    rs = lambda n: ''.join(rng.choice('ACGT') for _ in range(n))
+    core = rs(90)
+    tpls = [core[a:a + 45] for a in (0, 10, 20, 30, 45)] + [core]
+    seqs = tpls + [synth.revcomp(t.encode()).decode() for t in tpls]
+    recs = []
+    for i in range(6000):
+        L = rng.randint(40, 150)
+        sq = list(rs(L))
+        if i % 2 == 0:
+            a = rng.randint(0, max(0, L - 40)); b0 = rng.randint(0, 50)
+            sq[a:a + 90 - b0] = list(core[b0:]); sq = sq[:L]
+        recs.append('@r%d\n%s\n+\n%s\n' % (i, ''.join(sq), 'I' * len(sq)))
+    cfg = dict(maxerrors=1, minoverlap=20, minreadlength=20, Amin='5')
+    e = Engine(0)
+    e.config(**cfg)
+    cases = {'several templates per read': (''.join(recs), seqs),
+             'no hits': (''.join(recs[1::2]), [rs(60)]),
+             'more hits than the device orders': (''.join('@p%d\n%s\n+\n%s\n' % (i, 'A' * 150, 'I' * 150) for i in range(1500)), ['A' * 60])}
+    for name, (text, sq) in cases.items():
+        fn = str(tmp_path / 'ord.fastq')
+        open(fn, 'w').write(text)
+        want = oracle(checker, fn, sq, cfg, impl='oracle' if 'more hits' in name else None)
+        if 'several' in name:
+            assert len(want['hits']) > 5000
+        if 'more hits' in name:
+            assert len(want['hits']) > 65536
+        st = e.stage([np.frombuffer(text.encode(), dtype=np.uint8)])
+        for rep in range(3):
+            got = e.scan_staged(st, sq, nplus=0)
+            assert_same_result(got, want, what='%s, scan %d' % (name, rep))
+        st.free()
+    e.close()
+
+
 def test_survivor_queue_overflow(checker, multi_chunk, tmp_path, monkeypatch):
     """The scan kernel hands candidates to the emit kernel through a queue; when it overflows
     the emit / long-record kernels do nothing and the batch is run again with a queue that fits
