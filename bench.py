@@ -213,6 +213,7 @@ def main():
         import torch.distributed as dist
         torch.cuda.set_device(local)
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')        # stdout carries the one JSON line only
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
 
     def barrier():
