@@ -117,8 +117,20 @@ const char *skip_gzip_header(FILE *fd, int dist)
 }
 
 // .gz input: raw inflate of every member (workhorse.c:781-885), zlib instead of miniz
+// File position of the reference's reader as a function of the inflated bytes delivered: `pos`
+// holds from output offset `out` on.  A read of compressed input (at_end = false) happens when more
+// output is wanted, so a fill that ends exactly at `out` has not issued it yet; the reposition behind
+// a member's end (at_end = true) happens in the call that delivers the member's last byte.
+struct GzEvent { int64_t out, pos; bool at_end; };
+
 struct GzFileSource : Source {
     FILE *fd; int64_t size, remaining; z_stream zs; std::vector<unsigned char> in;
+    int64_t produced = 0; std::vector<GzEvent> *log = nullptr; std::mutex *log_mu = nullptr;   // (GzAhead)
+    void note(int64_t got, bool at_end) {
+        if (!log) return;
+        std::lock_guard<std::mutex> g(*log_mu);
+        log->push_back(GzEvent{produced + got, (int64_t) ftell(fd), at_end});
+    }
     explicit GzFileSource(const char *name) : in(REF_CHUNK) {
         fd = fopen(name, "rb");
         if (!fd) throw KvqError(KVQ_ERR_IO, "cannot open file");
@@ -142,6 +154,7 @@ struct GzFileSource : Source {
                 if ((int64_t) fread(in.data(), 1, m, fd) != m)
                     throw KvqError(KVQ_ERR_IO, "could not read enough bytes from .fastq.gz");
                 zs.next_in = in.data(); zs.avail_in = (unsigned) m; remaining -= m;
+                note(got, false);
             }
             unsigned before = zs.avail_out;
             int st = inflate(&zs, Z_SYNC_FLUSH);
@@ -154,20 +167,114 @@ struct GzFileSource : Source {
                 fseek(fd, -((long) zs.avail_in), SEEK_CUR);
                 remaining += zs.avail_in;
                 long pos = ftell(fd);
-                if (skip_gzip_header(fd, 10) != nullptr) { remaining = 0; zs.avail_in = 0; break; }
+                if (skip_gzip_header(fd, 10) != nullptr) { remaining = 0; zs.avail_in = 0; note(got, true); break; }
                 remaining -= ftell(fd) - pos;
                 inflateReset2(&zs, -15);
                 zs.avail_in = 0;
+                note(got, true);
             } else if (st == Z_STREAM_END) {
                 break;
             }
         } while (remaining + zs.avail_in > 10 && zs.avail_out > 0);
         *filled = (zs.avail_out == 0);
+        produced += got;
         return got;
     }
     int64_t disk_size() const override { return size; }
     int64_t disk_pos() const override { return ftell(fd); }
     bool compressed() const override { return true; }
+};
+
+// A .gz file inflated ahead of the scan by its own host thread (zlib, one stream per file): the
+// files of a scan -- the two mates of a paired-end run, the lanes of a sample -- inflate side by
+// side instead of one after the other, and inflate overlaps the cutting of the batches.  What the
+// scan sees is byte for byte what GzFileSource delivers, including the reference's file position
+// after every fill (GzEvent), which feeds the size estimate of engine.stats().
+class GzAhead : public Source {
+public:
+    static constexpr int64_t BLOCK = 4ll << 20, LIMIT = 1ll << 30;      // read-ahead per file
+    explicit GzAhead(const std::string &name) : name_(name) { th_ = std::thread([this] { run(); }); }
+    ~GzAhead() override {
+        { std::lock_guard<std::mutex> g(mu_); cancel_ = true; }
+        cv_.notify_all();
+        if (th_.joinable()) th_.join();
+    }
+    void wait_opened() {                // errors of fastq_open_next surface where the reference raises them
+        std::unique_lock<std::mutex> g(mu_);
+        cv_.wait(g, [&] { return opened_; });
+        if (open_failed_) std::rethrow_exception(err_);
+    }
+    int64_t fill(char *dst, int64_t cap, bool *filled) override {
+        int64_t got = 0;
+        std::unique_lock<std::mutex> g(mu_);
+        while (got < cap) {
+            cv_.wait(g, [&] { return !blocks_.empty() || done_; });
+            if (blocks_.empty()) {
+                if (err_) std::rethrow_exception(err_);
+                break;
+            }
+            std::vector<char> &bk = blocks_.front();
+            const int64_t m = std::min<int64_t>(cap - got, (int64_t) bk.size() - front_off_);
+            g.unlock();
+            memcpy(dst + got, bk.data() + front_off_, (size_t) m);
+            g.lock();
+            got += m; front_off_ += m; buffered_ -= m;
+            if (front_off_ == (int64_t) bk.size()) { blocks_.pop_front(); front_off_ = 0; cv_.notify_all(); }
+        }
+        consumed_ += got;
+        while (ev_at_ < events_.size() &&
+               (events_[ev_at_].out < consumed_ || (events_[ev_at_].at_end && events_[ev_at_].out == consumed_)))
+            pos_ = events_[ev_at_++].pos;
+        *filled = (got == cap);
+        return got;
+    }
+    int64_t disk_size() const override { return size_; }
+    int64_t disk_pos() const override { return pos_; }
+    bool compressed() const override { return true; }
+private:
+    void run() {
+        try {
+            GzFileSource src(name_.c_str());
+            {
+                std::lock_guard<std::mutex> g(mu_);
+                size_ = src.size; pos_ = src.disk_pos(); opened_ = true;
+            }
+            src.log = &events_; src.log_mu = &mu_;
+            cv_.notify_all();
+            for (;;) {
+                {
+                    std::unique_lock<std::mutex> g(mu_);
+                    cv_.wait(g, [&] { return buffered_ < LIMIT || cancel_; });
+                    if (cancel_) break;
+                }
+                std::vector<char> bk((size_t) BLOCK);
+                bool filled = false;
+                const int64_t got = src.fill(bk.data(), BLOCK, &filled);
+                bk.resize((size_t) got);
+                {
+                    std::lock_guard<std::mutex> g(mu_);
+                    if (got) { blocks_.push_back(std::move(bk)); buffered_ += got; }
+                    if (!filled) done_ = true;
+                }
+                cv_.notify_all();
+                if (!filled) break;
+            }
+        } catch (...) {
+            std::lock_guard<std::mutex> g(mu_);
+            err_ = std::current_exception();
+            if (!opened_) { open_failed_ = true; opened_ = true; }
+            done_ = true;
+            cv_.notify_all();
+        }
+    }
+    std::string name_;
+    std::thread th_;
+    std::mutex mu_; std::condition_variable cv_;
+    std::deque<std::vector<char>> blocks_; int64_t front_off_ = 0, buffered_ = 0, consumed_ = 0;
+    std::vector<GzEvent> events_; size_t ev_at_ = 0;
+    int64_t size_ = 0, pos_ = 0;
+    bool opened_ = false, open_failed_ = false, done_ = false, cancel_ = false;
+    std::exception_ptr err_;
 };
 
 bool has_gz_suffix(const std::string &s)
@@ -236,6 +343,8 @@ public:
         }
         live_->parsed = 0; live_->total = size_all_;
         if (nfiles_ == 0) { finished_ = true; return; }
+        ahead_.resize(names_.size());
+        start_ahead();
         open_next();
     }
 
@@ -302,7 +411,10 @@ private:
         const int i = next_file_++;
         if (!names_.empty()) {
             if (has_gz_suffix(names_[i])) {
-                src_.reset(new GzFileSource(names_[i].c_str()));
+                if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i]));
+                ahead_[i]->wait_opened();
+                src_ = std::move(ahead_[i]);
+                start_ahead();
                 compressed_ = true;
                 live_->total = live_->total * 3;                            // "random guess", :625
             } else {
@@ -315,6 +427,18 @@ private:
         }
     }
 
+    // up to AHEAD .gz files of the list inflate ahead of the one being scanned
+    void start_ahead()
+    {
+        int running = 0;
+        for (size_t i = (size_t) next_file_; i < names_.size() && running < AHEAD; i++) {
+            if (!has_gz_suffix(names_[i])) break;                           // (a plain file after .gz is an error anyway)
+            if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i]));
+            running++;
+        }
+    }
+    static constexpr int AHEAD = 4;
+    std::vector<std::unique_ptr<GzAhead>> ahead_;
     std::vector<std::string> names_;
     std::vector<std::pair<const char *, int64_t>> mems_;
     LiveStats *live_;

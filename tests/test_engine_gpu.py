@@ -279,6 +279,35 @@ def test_multi_chunk_streams(gpu_engine, checker, multi_chunk, kind):
     assert_same_result(got, want, what=kind)
 
 
+def test_many_gz_files_inflated_side_by_side(gpu_engine, checker, multi_chunk, tmp_path):
+    """.gz files of one scan are inflated ahead by one host thread each (up to 4 at a time): five
+    files -- single-member, multi-member, one tiny, one empty stream -- must give the reference's
+    hits and stats (continuing file_pos, float size estimate from the reference's file position)."""
+    fq = multi_chunk['bytes']
+    cuts = [0]
+    for frac in (0.17, 0.45, 0.46, 0.8):
+        cuts.append(fq.index(b'\n@SYN', int(len(fq) * frac)) + 1)
+    cuts.append(len(fq))
+    files = []
+    for k in range(5):
+        part = fq[cuts[k]:cuts[k + 1]]
+        fn = str(tmp_path / ('lane%d.fastq.gz' % k))
+        if k == 1:
+            half = part.index(b'\n@SYN', len(part) // 2) + 1
+            open(fn, 'wb').write(gzip.compress(part[:half], 6) + gzip.compress(b'', 6) + gzip.compress(part[half:], 1))
+        else:
+            open(fn, 'wb').write(gzip.compress(part, 6))
+        files.append(fn)
+    gpu_engine.config(**DEFAULT)
+    got = gpu_engine.findseqs(files, multi_chunk['seqs'])
+    want = oracle(checker, files, multi_chunk['seqs'], DEFAULT)
+    assert len(want['hits']) > 50
+    assert_same_result(got, want, what='five gz files')
+    open(files[2], 'wb').write(b'not a gzip file')
+    with pytest.raises(IOError):
+        gpu_engine.findseqs(files, multi_chunk['seqs'])
+
+
 def test_fused_coverage(gpu_engine, checker, multi_chunk):
     """K6: coverage + alternate-base counts == Coverage.apply_hit over the reference's hits"""
     from kvarq_b200.engine import Engine
