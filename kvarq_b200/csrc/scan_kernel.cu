@@ -1370,23 +1370,41 @@ kvq_order_count(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqO
     }
 }
 
-// one block: x[0 .. n] -> inclusive prefix sums in place (x[0] stays), copy to y when given
+// one block of 1024 threads: x[0 .. n] -> inclusive prefix sums in place (x[0] stays), copy to y
+// when given.  Tiles of 1024 elements, coalesced; warp scans by shuffles, one carry between tiles.
 __device__ __forceinline__ void block_scan(uint32_t *x, uint32_t *y, uint32_t n)
 {
-    __shared__ uint32_t part[1024];
-    const uint32_t per = (n + 1 + 1023) / 1024, lo = threadIdx.x * per, hi = min(lo + per, n + 1);
-    uint32_t sum = 0;
-    for (uint32_t i = lo; i < hi; i++) sum += x[i];
-    part[threadIdx.x] = sum;
-    __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {
-        const uint32_t v = threadIdx.x >= d ? part[threadIdx.x - d] : 0u;
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t carry_s;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base <= n; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i <= n ? x[i] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += u;
+        }
+        if (lane == 31) wsum[wid] = inc;
         __syncthreads();
-        part[threadIdx.x] += v;
+        if (wid == 0) {
+            uint32_t w = wsum[lane], winc = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, winc, d);
+                if (lane >= d) winc += u;
+            }
+            wsum[lane] = winc - w;                  // exclusive prefix of the warp totals
+            if (lane == 31) carry_s = winc;         // tile total
+        }
+        __syncthreads();
+        const uint32_t r = carry + wsum[wid] + inc;
+        if (i <= n) { x[i] = r; if (y) y[i] = r; }
+        carry += carry_s;
         __syncthreads();
     }
-    uint32_t run = part[threadIdx.x] - sum;
-    for (uint32_t i = lo; i < hi; i++) { run += x[i]; x[i] = run; if (y) y[i] = run; }
 }
 
 __global__ void __launch_bounds__(1024)
