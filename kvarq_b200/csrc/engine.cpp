@@ -1627,7 +1627,7 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         if (want_hits) {
             // ordered on the device unless the batch had to be run again or a buffer overflowed
             const bool ordered = dev_order && tot.launches == launches0 && c.hit_count <= st->hit_cap && c.blob_used <= st->blob_cap
-                              && *e->pin_ord.as<uint32_t>() == (uint32_t) c.hit_count && c.hit_count <= ord.cap;
+                              && *e->pin_ord.as<uint32_t>() == (uint32_t) c.hit_count && c.hit_count <= ord.cap && c.hit_count > 0;
             if (ordered) {
                 const size_t nh = (size_t) c.hit_count, nb = (size_t) c.blob_used;
                 if (!(nh <= tot.spec_hits && nb <= tot.spec_blob && st->last_hits)) {
