@@ -37,6 +37,25 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# stdout carries the one JSON line and nothing else: libraries that write to fd 1 on their own (NCCL's
+# version banner) are sent to stderr, the line goes out through a private copy of the original stdout
+_OUT = None
+
+
+def claim_stdout():
+    global _OUT
+    if _OUT is None:
+        sys.stdout.flush()
+        _OUT = os.fdopen(os.dup(1), 'w')
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    out = _OUT or sys.stdout
+    out.write(json.dumps(obj) + '\n')
+    out.flush()
+
+
 def peaks():
     try:
         p = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
@@ -170,7 +189,7 @@ def run_reference_arm(args, rank, world):
     val = bases / t / 1e9
     kind = 'reference' if impl == 'ref' else 'port'
     sample = '%d steps x first-%d-record slices of the 3M-read workload, nthreads=%d' % (args.steps, per_step, cores)
-    print(json.dumps({
+    emit({
         'impl': 'reference', 'metric': 'Gbp scanned/sec', 'value': val, 'unit': 'Gbp/s', 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * t / args.steps,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'u8', 'data': 'synthetic',
@@ -178,7 +197,7 @@ def run_reference_arm(args, rank, world):
         'cpu_baseline': {'value': val, 'unit': 'Gbp/s', 'cores': cores, 'kind': kind, 'sample': sample},
         'e2e': {'value': val, 'unit': 'Gbp/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
-    }), flush=True)
+    })
 
 
 def workload_config():
@@ -197,6 +216,7 @@ def main():
     ap.add_argument('--e2e-steps', type=int, default=0, help='0 = min(steps, 3)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()
+    claim_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
 
     rank = int(os.environ.get('RANK', '0'))
@@ -213,7 +233,6 @@ def main():
         import torch.distributed as dist
         torch.cuda.set_device(local)
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
-        os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')        # stdout carries the one JSON line only
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
 
     def barrier():
@@ -320,7 +339,7 @@ def main():
             traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))['dram_bytes_per_launch']
         except Exception:
             pass
-        print(json.dumps({
+        emit({
             'metric': 'Gbp scanned/sec', 'value': value, 'unit': 'Gbp/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'u8', 'data': 'synthetic',
@@ -334,7 +353,7 @@ def main():
                     'd2h_bytes_per_step': d2h_e // e2e_steps, 'steps': e2e_steps},
             'gpu_launches': launches, 'clocks': clocks,
             'hits_per_step': r.nhits, 'records_per_step': r['stats']['records_parsed'],
-        }), flush=True)
+        })
     eng.release_pinned(fq_pin)
     staged.free()
     eng.close()
