@@ -222,8 +222,8 @@ def test_random_seeded_configs(gpu_engine, checker, tmp_path):
     that partial overlaps, multiple seeds per diagonal and near-misses are frequent."""
     rng = random.Random(99)
     fn = str(tmp_path / 's.fastq')
-    for trial in range(40):
-        E = rng.choice([0, 1, 2]); O = rng.choice([8 * (E + 1), 25, 30, 40]); R = rng.choice([10, 25, 40])
+    for trial in range(70 * int(os.environ.get('KVQ_STRESS', 1))):     # KVQ_STRESS=n: n times the trials
+        E = rng.choice([0, 1, 2, 3]); O = rng.choice([8 * (E + 1), 25, 30, 40]); R = rng.choice([10, 25, 40])
         alpha = rng.choice(['AC', 'ACGT', 'ACGTN', 'ACGTacgt.'])
         master = ''.join(rng.choice(alpha) for _ in range(400))
         seqs = []
