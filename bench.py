@@ -153,6 +153,32 @@ def cpu_scan(fq_bytes, seqs, nthreads, tmpdir, tag):
     return dt, r, impl
 
 
+def prefix_parity(eng, pre, seqs, nplus, cpu_result, impl, cores, tmpdir):
+    """The CPU leg's per-template counters / histogram / record count against a GPU scan of the
+    same prefix (outside every timed region).  The reference's own C races with nthreads > 1
+    (csrc/workhorse.c:953-955: a chunk-boundary record can be scanned twice), so when that run
+    differs the deterministic port (oracle/kvarq_oracle.c, pinned to the reference at nthreads=1)
+    is run on the same bytes and decides."""
+    keys = ('nseqhits', 'nseqbasehits', 'readlengths', 'records_parsed')
+    g = eng.findseqs_mem([pre], seqs, nplus=nplus, want_hits=False)['stats']
+    same = lambda st: all(list(g[k]) == list(st[k]) if k != 'records_parsed' else g[k] == st[k] for k in keys)
+    if same(cpu_result['stats']):
+        return 'equal'
+    if impl == 'ref':
+        from oracle import checker
+        fn = os.path.join(tmpdir, 'kvq_cpu_parity_%d.fastq' % os.getpid())
+        with open(fn, 'wb') as f:
+            f.write(pre.tobytes())
+        try:
+            o = checker.findseqs(fn, seqs, nthreads=cores, impl='oracle', want_hits=False, **CFG)
+        finally:
+            os.remove(fn)
+        if same(o['stats']):
+            return ('equal (vs the deterministic port; the reference C at nthreads=%d raced: records_parsed %d vs %d)'
+                    % (cores, cpu_result['stats']['records_parsed'], g['records_parsed']))
+    return 'DIFFERS'
+
+
 def sample_bytes(fq, nreads):
     """First nreads records of the (fixed-width per decade) synthetic FastQ."""
     import numpy as np
@@ -321,15 +347,19 @@ def main():
 
     # ---- CPU baseline on rank 0 at N=1 -------------------------------------------------------
     cpu = None
+    parity_prefix = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         n = int(min(READS, max(5000, 15.0 * cores / 0.00075 * 0.6)))
         tmp = '/dev/shm' if os.path.isdir('/dev/shm') else '/tmp'
-        cdt, cr, impl = cpu_scan(sample_bytes(fq, n).tobytes(), seqs, cores, tmp, 'base')
+        pre = sample_bytes(fq, n)
+        cdt, cr, impl = cpu_scan(pre.tobytes(), seqs, cores, tmp, 'base')
         cpu = {'value': n * READLEN / cdt / 1e9, 'unit': 'Gbp/s', 'cores': cores,
                'kind': 'reference' if impl == 'ref' else 'port',
                'sample': 'first %d of %d records, nthreads=%d, %.1f s' % (n, READS, cores, cdt)}
         log('[cpu] %s' % cpu)
+        parity_prefix = prefix_parity(eng, pre, seqs, ts.nplus, cr, impl, cores, tmp)
+        log('[parity] prefix of %d records: %s' % (n, parity_prefix))
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -348,7 +378,7 @@ def main():
                          'frac': achieved / peak, 'traffic': traffic, 'peak_source': peak_src,
                          'kernel': 'kvq_scan_kernel', 'kernel_ms_per_step': kms,
                          'algorithmic_bytes_per_launch': stream_bytes},
-            'cpu_baseline': cpu,
+            'cpu_baseline': cpu, 'parity_prefix': parity_prefix,
             'e2e': {'value': e2e, 'unit': 'Gbp/s', 'h2d_bytes_per_step': h2d // e2e_steps,
                     'd2h_bytes_per_step': d2h_e // e2e_steps, 'steps': e2e_steps},
             'gpu_launches': launches, 'clocks': clocks,

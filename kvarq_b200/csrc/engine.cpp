@@ -561,14 +561,14 @@ struct TemplateSet {
     int nseqs = 0, nplus = 0; int64_t cov_total = 0;
     std::vector<int32_t> len;
     KvqTemplates dev{}; KvqParams par{};
-    DevBuf d_bytes, d_boff, d_packed, d_poff, d_len, d_seedable, d_exh;
-    DevBuf d_bm1, d_off1, d_ent1, d_bm2, d_off2, d_ent2, d_covoff, d_p2, d_bm2l, d_first1, d_first2, d_t1x, d_t2e, d_t2x;
+    DevBuf d_bytes, d_boff, d_packed, d_poff, d_len, d_exh;
+    DevBuf d_bm1, d_ent1, d_bm2, d_ent2, d_covoff, d_p2, d_bm2l, d_first1, d_first2, d_t1x, d_t2e, d_t2x;
 
     static unsigned char comp(unsigned char c) {
         switch (c) { case 'A': return 'T'; case 'T': return 'A'; case 'C': return 'G'; case 'G': return 'C'; default: return c; }
     }
 
-    std::vector<char> cache_key;
+    std::vector<char> cache_key, pending_key;
 
     void build(const char *const *seqs, const int32_t *lens, int n, int np, const kvq_config_t &cfg)
     {
@@ -583,8 +583,9 @@ struct TemplateSet {
                 put(lens, sizeof(int32_t) * (size_t) n);
                 for (int i = 0; i < n; i++) put(seqs[i], (size_t) lens[i]);
                 if (key == cache_key && d_bytes.p) { par.want_hits = 1; par.accumulate = 1; par.exact_phase = exact_phase_knob(); return; }
-                cache_key.swap(key);
-            } else cache_key.clear();
+                pending_key.swap(key);
+            } else pending_key.clear();
+            cache_key.clear();          // committed as the last statement: a build that throws leaves no key behind
         }
         nseqs = n; nplus = np; len.assign(lens, lens + n);
         for (int i = 0; i < n; i++)
@@ -708,18 +709,18 @@ struct TemplateSet {
         cov_total = np > 0 ? covoff[np] : 0;
 
         upload(d_bytes, bytes); upload(d_boff, boff); upload(d_packed, packed, 4); upload(d_poff, poff);
-        upload(d_len, len); upload(d_seedable, seedable); upload(d_exh, exh);
-        upload(d_bm1, t1x_on ? t1mask : t1roles); upload(d_off1, t1.off); upload(d_ent1, t1.ovf); upload(d_first1, t1.first);
-        upload(d_bm2, t2.bitmap); upload(d_off2, t2.off); upload(d_ent2, t2.ovf); upload(d_first2, t2.first);
+        upload(d_len, len); upload(d_exh, exh);
+        upload(d_bm1, t1x_on ? t1mask : t1roles); upload(d_ent1, t1.ovf); upload(d_first1, t1.first);
+        upload(d_bm2, t2.bitmap); upload(d_ent2, t2.ovf); upload(d_first2, t2.first);
         upload(d_bm2l, bm2l); if (t1x_on) { upload(d_t1x, t1x); upload(d_t2e, t2e); upload(d_t2x, t2x); }
         upload(d_covoff, covoff);
 
         dev.bytes = d_bytes.as<uint8_t>(); dev.byte_off = d_boff.as<uint32_t>();
         dev.packed = d_packed.as<uint32_t>(); dev.packed_off = d_poff.as<uint32_t>(); dev.packed_words = (int32_t) packed.size();
-        dev.len = d_len.as<int32_t>(); dev.seedable = d_seedable.as<uint8_t>();
+        dev.len = d_len.as<int32_t>();
         dev.exh_list = d_exh.as<int32_t>(); dev.nseqs = n; dev.n_exh = (int) exh.size();
-        dev.t1_present = d_bm1.as<uint8_t>(); dev.t1_off = d_off1.as<uint32_t>(); dev.t1_ent = d_ent1.as<uint4>();
-        dev.t2_bitmap = d_bm2.as<uint32_t>(); dev.t2_off = d_off2.as<uint32_t>(); dev.t2_ent = d_ent2.as<uint4>();
+        dev.t1_present = d_bm1.as<uint8_t>(); dev.t1_ent = d_ent1.as<uint4>();
+        dev.t2_bitmap = d_bm2.as<uint32_t>(); dev.t2_ent = d_ent2.as<uint4>();
         dev.t1_first = d_first1.as<uint4>(); dev.t2_first = d_first2.as<uint4>();
         dev.t2l_bitmap = d_bm2l.as<uint32_t>(); dev.t1x_bitmap = d_t1x.as<uint32_t>(); dev.t2e_bitmap = d_t2e.as<uint32_t>(); dev.t2x_bitmap = d_t2x.as<uint32_t>();
         dev.cov_off = d_covoff.as<uint32_t>(); dev.nplus = np;
@@ -730,10 +731,6 @@ struct TemplateSet {
         par.want_hits = 1; par.accumulate = 1; par.exact_phase = exact_phase_knob();
         par.t1x = t1x_on ? KVQ_T1X_K * pieces : 0;
         par.min_seed_rl = KVQ_SEED_K * par.npieces;
-        par.div_magic = (uint32_t) ((65536 + par.npieces - 1) / par.npieces);
-        for (int x = 0; x < 8192; x++)                  // the kernels divide by multiplication
-            if ((int) (((uint32_t) x * par.div_magic) >> 16) != x / par.npieces)
-                throw KvqError(KVQ_ERR_RUNTIME, "internal: reciprocal division is inexact");
         for (int j = 0; j < KVQ_MAX_PIECES; j++) par.o_piece[j] = (int) ((int64_t) j * O / par.npieces);
         par.n2max = (t1x_on ? 5 : 3) * par.npieces;
         // Fixed read offsets probed against T2, per trimmed read length: E+1 pieces of the whole read
@@ -772,6 +769,10 @@ struct TemplateSet {
             }
         upload(d_p2, p2);
         dev.p2_tab = d_p2.as<int16_t>();
+        // the uploads above are synchronous copies from pageable memory on the legacy stream; the scan
+        // kernels run on non-blocking streams, so make sure every table has landed before they start
+        CK(cudaDeviceSynchronize());
+        cache_key.swap(pending_key);
     }
 };
 
@@ -834,7 +835,7 @@ kvq_result *take_result()
 struct Slot {                           // one batch in flight
     HostBatch hb; PinBuf pin;
     DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs, d_surv; size_t surv_cap = 0;
-    PinBuf h_ctr, h_seg, h_tiles;
+    PinBuf h_ctr, h_seg, h_tiles, h_live;
     TileBufs tiles;
     cudaStream_t stream = nullptr; cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copied = nullptr;
     size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
@@ -872,7 +873,7 @@ struct kvq_engine {
     cudaStream_t copy_stream = nullptr;             // all batch uploads, back to back (concurrent H2D copies share the link badly)
     Accum acc;
     TemplateSet tpl;
-    PinBuf pin_out, pin_acc, pin_ord;               // page-locked staging of the result copies
+    PinBuf pin_out, pin_acc, pin_ord, pin_ctr2;               // page-locked staging of the result copies
     SortScratch scratch;
 
     void set_error(int cls, const std::string &m) { std::lock_guard<std::mutex> g(mu); err_cls = cls; err_msg = m; }
@@ -961,12 +962,14 @@ KvqOut make_out(kvq_engine *e, const OutBufs &ob)
     return o;
 }
 
-void reset_accum(kvq_engine *e)
+// Zeroes the accumulators on `st`: the stream the scan kernels run on, or one they wait for
+// (the slot streams of a streaming scan wait for the copy stream's events).
+void reset_accum(kvq_engine *e, cudaStream_t st)
 {
     const TemplateSet &t = e->tpl;
     e->acc.ns = (size_t) std::max(1, t.nseqs); e->acc.nc = (size_t) std::max<int64_t>(1, t.cov_total);
     e->acc.d_all.ensure(e->acc.words() * 8);
-    CK(cudaMemset(e->acc.d_all.p, 0, e->acc.words() * 8));
+    CK(cudaMemsetAsync(e->acc.d_all.p, 0, e->acc.words() * 8, st));
 }
 
 // enqueue memset + scan + emit + long-record kernels for one batch already resident on the device
@@ -1007,6 +1010,8 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     KvqOut o = make_out(e, bufs_of(s));
     enqueue_kernels(e, b, e->tpl.par, o, s.stream, s.ev0, s.ev1);
     CK(cudaMemcpyAsync(s.h_ctr.p, s.d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s.stream));
+    s.h_live.ensure(2 * e->acc.ns * 8);
+    CK(cudaMemcpyAsync(s.h_live.p, e->acc.d_all.p, 2 * e->acc.ns * 8, cudaMemcpyDeviceToHost, s.stream));
     tot.launches += 3; tot.h2d += hb.nbytes + (int64_t) hb.cuts.size() * 8; tot.d2h += sizeof(KvqCounters);
     tot.stream_bytes += hb.nbytes;
 }
@@ -1015,8 +1020,8 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
 // contradicted (malformed input): the emit and long-record kernels did nothing.  Run the batch
 // again with a queue that fits (its size is known now) / with exact line phases and take the
 // counters of that run.
-void rerun_for_survivors(kvq_engine *e, const KvqBatch &b, const OutBufs &ob, KvqCounters &c, PinBuf &h_ctr,
-                         cudaStream_t st, ScanTotals &tot)
+KvqParams rerun_for_survivors(kvq_engine *e, const KvqBatch &b, const OutBufs &ob, KvqCounters &c, PinBuf &h_ctr,
+                              cudaStream_t st, ScanTotals &tot)
 {
     KvqParams p = e->tpl.par;
     for (int it = 0; it < 4 && (c.surv_count > ob.surv_cap || c.phase_retry); it++) {
@@ -1031,10 +1036,13 @@ void rerun_for_survivors(kvq_engine *e, const KvqBatch &b, const OutBufs &ob, Kv
         c = *h_ctr.as<KvqCounters>();
         tot.launches += 3; tot.acc_fetched = false; tot.spec_hits = tot.spec_blob = 0;
     }
+    if (c.surv_count > ob.surv_cap || c.phase_retry)
+        throw KvqError(KVQ_ERR_RUNTIME, "internal: batch still incomplete after re-running it (survivor queue / line phases)");
+    return p;                               // the parameters the counters in `c` were produced with
 }
 
 // Fetch hits of a finished batch (re-running it with larger buffers when they overflowed).
-void collect_hits(kvq_engine *e, const KvqBatch &b, const OutBufs &ob,
+void collect_hits(kvq_engine *e, const KvqBatch &b, const OutBufs &ob, const KvqParams &used,
                   const KvqCounters &c, cudaStream_t st, ScanTotals &tot)
 {
     DevBuf &d_hits = ob.hits, &d_blob = ob.blob;
@@ -1043,10 +1051,17 @@ void collect_hits(kvq_engine *e, const KvqBatch &b, const OutBufs &ob,
     if (nh > hit_cap || nb > blob_cap) {
         hit_cap = (size_t) (nh + nh / 4 + 1024); blob_cap = (size_t) (nb + nb / 4 + 4096);
         d_hits.ensure(hit_cap * sizeof(KvqHitRec)); d_blob.ensure(blob_cap);
-        KvqParams p = e->tpl.par; p.accumulate = 0;
+        KvqParams p = used; p.accumulate = 0;   // (keeps exact_phase when the batch needed it)
         KvqOut o = make_out(e, ob);
         enqueue_kernels(e, b, p, o, st, nullptr, nullptr);
+        e->pin_ctr2.ensure(sizeof(KvqCounters));
+        CK(cudaMemcpyAsync(e->pin_ctr2.p, ob.ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
+        {
+            const KvqCounters &c2 = *e->pin_ctr2.as<KvqCounters>();
+            if (c2.phase_retry || c2.surv_count > ob.surv_cap || c2.hit_count != nh)
+                throw KvqError(KVQ_ERR_RUNTIME, "internal: re-run with larger hit buffers did not reproduce the batch");
+        }
         tot.launches += 3; tot.spec_hits = tot.spec_blob = 0;
     }
     if (nh == 0) return;
@@ -1086,14 +1101,13 @@ void harvest_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     KvqCounters c = *s.h_ctr.as<KvqCounters>();
     KvqBatch b{s.d_data.as<uint8_t>(), s.hb.nbytes, s.d_seg.as<int64_t>(), (int) s.hb.cuts.size() - 1, s.hb.base_fpos};
     s.tiles.fill(b);
-    rerun_for_survivors(e, b, bufs_of(s), c, s.h_ctr, s.stream, tot);
+    const KvqParams used = rerun_for_survivors(e, b, bufs_of(s), c, s.h_ctr, s.stream, tot);
     add_counters(e, c, tot);
     if (e->tpl.par.want_hits)
-        collect_hits(e, b, bufs_of(s), c, s.stream, tot);
-    // live per-template counters for engine.stats()
+        collect_hits(e, b, bufs_of(s), used, c, s.stream, tot);
+    // live per-template counters for engine.stats(): copied behind the batch's kernels (launch_slot)
     if (e->tpl.nseqs > 0) {
-        std::vector<unsigned long long> a(2 * e->acc.ns);
-        CK(cudaMemcpy(a.data(), e->acc.d_all.p, a.size() * 8, cudaMemcpyDeviceToHost));
+        const unsigned long long *a = s.h_live.as<unsigned long long>();
         for (int i = 0; i < e->tpl.nseqs; i++) { e->live.seqhits[i] = (int64_t) a[i]; e->live.seqbasehits[i] = (int64_t) a[e->acc.ns + i]; }
     }
 }
@@ -1238,7 +1252,7 @@ kvq_result *run_stream_scan(kvq_engine *e, std::vector<std::string> names,
     const double t_begin = now_ms();
     const bool trace_stream = getenv("KVQ_TRACE") != nullptr;
     init_slots(e);
-    reset_accum(e);
+    reset_accum(e, e->copy_stream);         // every slot stream waits for an event recorded later on this stream
     StreamCutter cutter(std::move(names), std::move(mems), &e->live);
     ScanTotals tot;
     Chan<int> free_q, ready_q;
@@ -1557,11 +1571,11 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         e->tpl.build(seqs, seqlens, nseqs, nplus, cfg);
         e->tpl.par.want_hits = want_hits ? 1 : 0;
         mark();
-        reset_accum(e);
-        mark();
-        e->live.parsed = st->parsed; e->live.total = st->total;
         init_slots(e);                                  // borrow slot 0's stream and events
         Slot &s0 = e->slots[0];
+        reset_accum(e, s0.stream);
+        mark();
+        e->live.parsed = st->parsed; e->live.total = st->total;
         ScanTotals tot; tot.acc_fetched = true;
         tot.hits.swap(e->scratch.hits); tot.blob.swap(e->scratch.blob); tot.hits.clear(); tot.blob.clear();
         KvqBatch b{st->d_data.as<uint8_t>(), st->nbytes, st->d_seg.as<int64_t>(), st->nseg, st->base_fpos};
@@ -1622,7 +1636,7 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         tot.kernel_ms = ms; tot.launches = 3; tot.stream_bytes = st->nbytes; tot.d2h = sizeof(KvqCounters);
         KvqCounters c = *s0.h_ctr.as<KvqCounters>();
         const int64_t launches0 = tot.launches;
-        rerun_for_survivors(e, b, bufs_of(*st), c, s0.h_ctr, s0.stream, tot);
+        const KvqParams used = rerun_for_survivors(e, b, bufs_of(*st), c, s0.h_ctr, s0.stream, tot);
         add_counters(e, c, tot);
         if (want_hits) {
             // ordered on the device unless the batch had to be run again or a buffer overflowed
@@ -1640,7 +1654,7 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
                 tot.launches += 6; tot.d2h += (int64_t) (nh * sizeof(KvqHitOut) + (nh + 1) * 8 + nb + 4);
             } else {
                 if (dev_order) tot.spec_hits = tot.spec_blob = 0;       // the staging holds ordered arrays, not raw records
-                collect_hits(e, b, bufs_of(*st), c, s0.stream, tot);
+                collect_hits(e, b, bufs_of(*st), used, c, s0.stream, tot);
             }
             st->last_hits = (size_t) c.hit_count; st->last_blob = (size_t) c.blob_used;
         }

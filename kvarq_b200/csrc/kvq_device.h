@@ -48,7 +48,6 @@ struct KvqParams {
     int32_t max_seqlen;                 // longest template (decides the whole-read T2 probes)
     int32_t want_hits;                  // 0: count only (no hit records / blob written)
     int32_t min_seed_rl;                // KVQ_SEED_K * npieces: shortest read the seed scheme covers
-    uint32_t div_magic;                 // floor(x / npieces) == (x * div_magic) >> 16 for x < 8192
     int32_t o_piece[KVQ_MAX_PIECES];    // floor(j * minoverlap / npieces)
     int32_t n2max;                      // T2 probe slots per read: 3 * npieces (5 * npieces for large sets)
     int32_t accumulate;                 // 0: re-run after a buffer overflow, counters already taken
@@ -63,7 +62,6 @@ struct KvqTemplates {
     const uint32_t *packed_off;         // [nseqs+1] word offsets
     int32_t packed_words;               // words in packed[]
     const int32_t *len;                 // [nseqs]
-    const uint8_t *seedable;            // [nseqs]
     const int32_t *exh_list;            // indices of non-seedable seqs
     int32_t nseqs, n_exh;
     // seed tables: presence per 16-bit key (T1: one byte per key, T2: one bit per key), CSR
@@ -72,7 +70,7 @@ struct KvqTemplates {
     // `more` further entries of the bucket start at *_ent[overflow index] (more == 255: the count is
     // in *_ent[overflow index - 1].x)
     const uint4 *t1_first, *t2_first;
-    const uint8_t *t1_present; const uint32_t *t1_off; const uint4 *t1_ent;   // template-piece seeds
+    const uint8_t *t1_present; const uint4 *t1_ent;   // template-piece seeds
     const uint32_t *t2l_bitmap;         // T2 presence restricted to templates longer than short_max
     const uint32_t *t1x_bitmap;         // 2^24 bits: 12-mers that start a piece of a template with pieces >= 12 bases
     // large sets (KvqParams.t1x != 0): t2_first / t2_ent hold every T2 class back to back --
@@ -80,7 +78,7 @@ struct KvqTemplates {
     // [X: 12-mers at all offsets, 2^KVQ_X_HASH_BITS heads]; overflow indices are global in t2_ent.
     const uint32_t *t2e_bitmap;         // union of the H_j / T_j keys (staged in shared memory)
     const uint32_t *t2x_bitmap;         // 2^24 bits: 12-mers at any template offset
-    const uint32_t *t2_bitmap, *t2_off; const uint4 *t2_ent;                  // every template offset
+    const uint32_t *t2_bitmap; const uint4 *t2_ent;                  // every template offset
     const int16_t *p2_tab;              // [KVQ_MAXRL_FAST+1][KVQ_P2W] T2 probe offsets per read length, -1 = unused
     const uint32_t *cov_off;            // [nplus+1] offset of each plus template in coverage[]
     int32_t nplus;                      // 0 = no fused coverage

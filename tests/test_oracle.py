@@ -153,3 +153,52 @@ def test_synth_is_deterministic():
     assert synth.count_bases(a) == 123400
     ts = synth.mtbc_templates(synth.genome(300000, seed=2))
     assert ts.nplus == 132 and sum(len(s) for s in ts.plus) == 6318      # 6 318 bp per strand
+
+
+def test_restatement_vs_reference_large_mixed_set(checker, tmp_path):
+    """The large-set template shapes of the GPU tests (>= 2048 seed pieces: 25 / 51 / 611-bp classes
+    mixed) are checked on the GPU against the restatement; here the restatement itself is pinned
+    to the reference's own C on that shape."""
+    if not checker.available('ref'):
+        pytest.skip('oracle/_ref not built')
+    g = synth.genome(40000, seed=51)
+    rng = np.random.RandomState(52)
+    comp = bytes.maketrans(b'ACGT', b'TGCA')
+    plus = [bytes(g[p:p + 25]) for p in sorted(rng.choice(len(g) - 700, 250, replace=False))]
+    plus += [bytes(g[p:p + 51]) for p in sorted(rng.choice(len(g) - 700, 450, replace=False))]
+    plus += [bytes(g[p:p + n]) for p, n in ((1000, 131), (9000, 611), (20000, 53), (30000, 36))]
+    seqs = [s.decode() for s in plus] + [s.translate(comp)[::-1].decode() for s in plus]
+    assert 3 * len(seqs) >= 2048
+    fn = str(tmp_path / 'mixed.fastq')
+    fq = [synth.fastq_reads(g, 500, readlen=150, seed=53, qmean0=30.0, qdrop=26.0, qsd=5.0).tobytes(),
+          synth.fastq_reads(g, 300, readlen=60, seed=54, qmean0=26.0, qdrop=14.0, qsd=6.0, first_index=5000).tobytes()]
+    open(fn, 'wb').write(b''.join(fq))
+    for cfg in (DEFAULT, dict(DEFAULT, maxerrors=1, minoverlap=20)):
+        a = run(checker, 'ref', fn, seqs, cfg)
+        b = run(checker, 'oracle', fn, seqs, cfg, nthreads=4)
+        assert len(a['hits']) > 300
+        assert_same_result(b, a, what='large mixed set %r' % (cfg,))
+
+
+def test_restatement_vs_reference_negative_amin(checker, tmp_path):
+    """Amin >= 0x80 (a negative signed char): the restatement follows the reference's signed
+    compare (workhorse.c:1058), incl. runs left open by a '\\n' that is itself >= Amin."""
+    if not checker.available('ref'):
+        pytest.skip('oracle/_ref not built')
+    rng = random.Random(3)
+    g = synth.genome(20000, seed=5)
+    tpl = bytes(g[3000:3051])
+    recs = []
+    for i in range(400):
+        L = rng.randint(30, 120)
+        a = rng.randrange(2900, 3100)
+        q = bytes(rng.choices([0x85, 0x9f, 0xa0, 0xc8, 0xff, 0x49, 0x21], [1, 1, 5, 5, 5, 20, 3], k=L))
+        recs.append(b'@n%d\n%s\n+\n%s\n' % (i, bytes(g[a:a + L]), q))
+    fn = str(tmp_path / 'neg.fastq')
+    open(fn, 'wb').write(b''.join(recs))
+    for amin in ('\x80', '\xa0', '\xff'):
+        cfg = dict(DEFAULT, Amin=amin)
+        a = run(checker, 'ref', fn, [tpl], cfg)
+        b = run(checker, 'oracle', fn, [tpl], cfg, nthreads=2)
+        assert_same_result(b, a, what='Amin=%r' % amin)
+    assert len(a['stats']['readlengths']) > 1
