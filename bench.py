@@ -311,8 +311,8 @@ def main():
     total_bases = allsum(bases * args.steps)
     value = total_bases / dt / 1e9
     kms = allmax(kernel_ms / args.steps)
-    log('[rank %d] resident: %.3f ms/step wall, %.3f ms/step inside the C call, %.3f ms/step kernels, %d hits, %d records' %
-        (rank, 1e3 * dt / args.steps, call_ms / args.steps, kernel_ms / args.steps, r.nhits, r['stats']['records_parsed']))
+    log('[rank %d] resident: %.3f ms/step wall, %.3f ms/step inside the C call, %.3f ms/step kernels, %d hits, %d records, %d candidates' %
+        (rank, 1e3 * dt / args.steps, call_ms / args.steps, kernel_ms / args.steps, r.nhits, r['stats']['records_parsed'], r.timing['candidates']))
 
     # ---- one NCCL all-reduce of the per-template counters (north_star; not in the timed region) --
     if dist is not None:

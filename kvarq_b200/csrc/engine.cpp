@@ -26,7 +26,8 @@ namespace {
 
 constexpr int64_t REF_CHUNK = 1024 * 1024;          // SCANBUFSIZE, workhorse.c:15
 constexpr int64_t BATCH_BYTES = 64ll << 20;         // stream bytes per GPU batch
-constexpr int64_t BATCH_PAD = 256;                  // readable slack behind a batch
+constexpr int64_t BATCH_PAD = 256;                  // zeroed slack behind a batch on the host side
+constexpr int64_t DEV_PAD = (KVQ_OWN_ROWS + 3) * KVQ_ROW;   // zeroed slack behind a batch in HBM: every tile loads all its rows unconditionally
 constexpr int NSLOT = 4;                // batches: one being cut by the producer, up to three on the GPU
 
 struct KvqError {
@@ -732,7 +733,7 @@ struct TemplateSet {
         par.t1x = t1x_on ? KVQ_T1X_K * pieces : 0;
         par.min_seed_rl = KVQ_SEED_K * par.npieces;
         for (int j = 0; j < KVQ_MAX_PIECES; j++) par.o_piece[j] = (int) ((int64_t) j * O / par.npieces);
-        par.n2max = (t1x_on ? 5 : 3) * par.npieces;
+        par.n2max = (t1x_on ? 5 : 3) * par.npieces; par.nl_byte = '\n';
         // Fixed read offsets probed against T2, per trimmed read length: E+1 pieces of the whole read
         // (rule d, only if some template is at least as long), of its first minoverlap bases
         // (rule b) and of its last minoverlap bases (rule a); duplicates removed.
@@ -906,7 +907,7 @@ void init_slots(kvq_engine *e)
     for (auto &s : e->slots) {
         s.pin.ensure(BATCH_BYTES + BATCH_PAD);
         s.hb.own = s.pin.as<char>(); s.hb.data = s.hb.own;
-        s.d_data.ensure(BATCH_BYTES + BATCH_PAD);
+        s.d_data.ensure(BATCH_BYTES + DEV_PAD);
         const size_t nseg_max = (size_t) (BATCH_BYTES / 4096) + 64;     // cuts are >= 1 byte apart; see launch
         s.d_seg.ensure(nseg_max * sizeof(int64_t)); s.h_seg.ensure(nseg_max * sizeof(int64_t));
         s.d_ctr.ensure(sizeof(KvqCounters)); s.h_ctr.ensure(sizeof(KvqCounters));
@@ -993,12 +994,8 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     const int nseg = (int) hb.cuts.size() - 1;
     s.d_seg.ensure(hb.cuts.size() * 8); s.h_seg.ensure(hb.cuts.size() * 8);
     memcpy(s.h_seg.p, hb.cuts.data(), hb.cuts.size() * 8);
-    if (hb.borrowed) {
-        CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes, cudaMemcpyHostToDevice, e->copy_stream));
-        CK(cudaMemsetAsync(s.d_data.as<char>() + hb.nbytes, 0, BATCH_PAD, e->copy_stream));
-    } else {
-        CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes + BATCH_PAD, cudaMemcpyHostToDevice, e->copy_stream));
-    }
+    CK(cudaMemcpyAsync(s.d_data.p, hb.data, hb.nbytes, cudaMemcpyHostToDevice, e->copy_stream));
+    CK(cudaMemsetAsync(s.d_data.as<char>() + hb.nbytes, 0, DEV_PAD, e->copy_stream));
     CK(cudaEventRecord(s.ev_copied, e->copy_stream));
     CK(cudaStreamWaitEvent(s.stream, s.ev_copied, 0));
     CK(cudaMemcpyAsync(s.d_seg.p, s.h_seg.p, hb.cuts.size() * 8, cudaMemcpyHostToDevice, s.stream));
@@ -1518,7 +1515,7 @@ int kvq_stage_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens
         for (int i = 0; i < nbufs; i++) { mems.push_back({bufs[i], buflens[i]}); total += buflens[i]; }
         std::unique_ptr<kvq_staged> st(new kvq_staged());
         st->e = e;
-        st->d_data.ensure((size_t) total + BATCH_PAD + 256);
+        st->d_data.ensure((size_t) total + DEV_PAD + 256);
         LiveStats live; live.reset(0);
         StreamCutter cutter(std::vector<std::string>(), std::move(mems), &live);
         std::vector<char> tmp((size_t) (BATCH_BYTES + BATCH_PAD));
@@ -1532,7 +1529,7 @@ int kvq_stage_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens
             for (size_t k = 1; k < hb.cuts.size(); k++) cuts.push_back(at + hb.cuts[k]);
             at += hb.nbytes;
         }
-        CK(cudaMemset(st->d_data.as<char>() + at, 0, BATCH_PAD));
+        CK(cudaMemset(st->d_data.as<char>() + at, 0, DEV_PAD));
         st->nbytes = at; st->nseg = (int) cuts.size() - 1;
         st->parsed = live.parsed; st->total = live.total;
         st->d_seg.ensure(cuts.size() * 8);

@@ -49,6 +49,7 @@ struct KvqParams {
     int32_t want_hits;                  // 0: count only (no hit records / blob written)
     int32_t min_seed_rl;                // KVQ_SEED_K * npieces: shortest read the seed scheme covers
     int32_t o_piece[KVQ_MAX_PIECES];    // floor(j * minoverlap / npieces)
+    int32_t nl_byte;                    // '\n' (a parameter, not an immediate: see nl_bits in scan_kernel.cu)
     int32_t n2max;                      // T2 probe slots per read: 3 * npieces (5 * npieces for large sets)
     int32_t accumulate;                 // 0: re-run after a buffer overflow, counters already taken
     int32_t exact_phase;                // 1: every tile waits for its line phase from the look-back chain (re-run after a
@@ -85,7 +86,7 @@ struct KvqTemplates {
 };
 
 struct KvqBatch {
-    const uint8_t *data;                // batch bytes, 16-byte aligned, readable 64 B past nbytes
+    const uint8_t *data;                // batch bytes, 16-byte aligned, followed by (KVQ_OWN_ROWS + 3) KiB of zeroed slack
     int64_t nbytes;
     const int64_t *seg_off;             // [nseg+1] record-aligned cuts (reference chunk emulation)
     int32_t nseg;

@@ -37,6 +37,9 @@ namespace {
 #ifndef KVQ_FMASK
 #define KVQ_FMASK 1
 #endif
+#ifndef KVQ_OLD_P1
+#define KVQ_OLD_P1 0                    // 1: per-row newline ranking (round 1), for A/B timing
+#endif
 #ifndef KVQ_ROW_SETS
 #define KVQ_ROW_SETS 3                  // register sets the rows of a tile rotate through (rows in flight + 1)
 #endif
@@ -85,9 +88,11 @@ __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t 
 
 // ---- byte planes: 4 bytes -> flags in bit 7 of every byte, gathered with dot products -------
 // bit7 of every byte of w that equals '\n'
-__device__ __forceinline__ uint32_t nl_bits(uint32_t w)
+// `c` = 0x0A0A0A0A held in a register (not an immediate: a LOP3 takes one immediate, with two the
+// xor and the and are two instructions)
+__device__ __forceinline__ uint32_t nl_bits(uint32_t w, uint32_t c)
 {
-    uint32_t s = ((w ^ 0x0A0A0A0Au) & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;   // bit7: low 7 bits differ from '\n'
+    uint32_t s = ((w ^ c) & 0x7F7F7F7Fu) + 0x7F7F7F7Fu;             // bit7: low 7 bits differ from '\n'
     return ~(s | w) & 0x80808080u;
 }
 // bit7 of every byte b of w with (signed char) b >= amin, amin >= 0.  cl = amin * 0x01010101
@@ -205,26 +210,106 @@ struct Row { uint4 a, b; };
 
 __device__ __forceinline__ Row load_row(const KvqBatch &b, const TileCtx &t, int row, int lane)
 {
+    // unconditional: the batch is followed by zeroed slack for a whole tile (engine.cpp, DEV_PAD); bytes
+    // beyond the segment only reach the planes, never a result (newlines there are masked, reads end before)
     Row r;
-    const int w = row * 32 + lane;
-    if ((w << 5) < t.lim) {
-        const uint4 *src = reinterpret_cast<const uint4 *>(b.data + t.a0) + 2 * w;
-        r.a = __ldg(src); r.b = __ldg(src + 1);
-    } else {
-        r.a = make_uint4(0, 0, 0, 0); r.b = r.a;
-    }
+    const uint4 *src = reinterpret_cast<const uint4 *>(b.data + t.a0) + 2 * (row * 32 + lane);
+    r.a = __ldg(src); r.b = __ldg(src + 1);
     return r;
 }
 
+// Reduce one 32-byte word per lane to the planes: quality-pass mask and 2-bit codes go to their
+// planes in shared memory, the newline mask (restricted to the tile's segment) is returned;
+// rank_rows() turns the masks of three rows into ranked newline positions.
+template <bool NEG>
+__device__ __forceinline__ uint32_t reduce_row(WarpSmem &s, const TileCtx &t, const Row &r, int row, int lane,
+                                               uint32_t cl, uint32_t cnl)
+{
+    const int w = row * 32 + lane;
+    uint32_t nl = gather32(gather2(nl_bits(r.a.x, cnl), nl_bits(r.a.y, cnl)), gather2(nl_bits(r.a.z, cnl), nl_bits(r.a.w, cnl)),
+                           gather2(nl_bits(r.b.x, cnl), nl_bits(r.b.y, cnl)), gather2(nl_bits(r.b.z, cnl), nl_bits(r.b.w, cnl)));
+    uint32_t ge;
+    if (NEG)
+        ge = gather32(gather2(ge_bits_neg(r.a.x, cl), ge_bits_neg(r.a.y, cl)), gather2(ge_bits_neg(r.a.z, cl), ge_bits_neg(r.a.w, cl)),
+                      gather2(ge_bits_neg(r.b.x, cl), ge_bits_neg(r.b.y, cl)), gather2(ge_bits_neg(r.b.z, cl), ge_bits_neg(r.b.w, cl)));
+    else
+        ge = gather32(gather2(ge_bits_pos(r.a.x, cl), ge_bits_pos(r.a.y, cl)), gather2(ge_bits_pos(r.a.z, cl), ge_bits_pos(r.a.w, cl)),
+                      gather2(ge_bits_pos(r.b.x, cl), ge_bits_pos(r.b.y, cl)), gather2(ge_bits_pos(r.b.z, cl), ge_bits_pos(r.b.w, cl)));
+    uint2 pk;
+    pk.x = pack8(r.a.x, r.a.y) | (pack8(r.a.z, r.a.w) << 16);
+    pk.y = pack8(r.b.x, r.b.y) | (pack8(r.b.z, r.b.w) << 16);
+    if (row == 0 || (row + 1) * KVQ_ROW > t.lim) {  // warp-uniform: newlines outside [shift, lim) belong to other tiles' segments
+        const int lo = t.shift - (w << 5), hi = t.lim - (w << 5);
+        if (lo > 0) nl &= lo >= 32 ? 0u : (0xFFFFFFFFu << lo);
+        if (hi < 32) nl &= hi <= 0 ? 0u : ((1u << hi) - 1u);
+    }
+    s.ge[w] = ge;
+    reinterpret_cast<uint2 *>(s.pk)[w] = pk;
+    return nl;
+}
+
+// the first two newlines of a word get their positions stored straight away (most words hold
+// none or one, "\n+\n" gives two); what is left stays in `nl`
+__device__ __forceinline__ void store_two(WarpSmem &s, uint32_t &nl, uint32_t rank, int wb)
+{
+    if (nl && rank < NLCAP) s.nlpos[rank] = (uint16_t) (wb + 31 - __clz(nl & (0u - nl)));
+    nl &= nl - 1;
+    if (nl && rank + 1 < NLCAP) s.nlpos[rank + 1] = (uint16_t) (wb + 31 - __clz(nl & (0u - nl)));
+    nl &= nl - 1;
+}
+
+// Newline masks of three rows (one word per lane and row) -> ranks and positions.  One shuffle
+// scan serves the three rows: their per-lane counts (<= 32) travel in 11-bit fields of one word.
+// Updates the running newline count of the tile and the lane's share of the newlines the tile
+// owns (coordinates below tile_end; only the last rows of a tile can lie beyond it).
+__device__ __forceinline__ void rank_rows(WarpSmem &s, const TileCtx &t, uint32_t nl0, uint32_t nl1, uint32_t nl2, int row0,
+                                          bool last, int lane, uint32_t &nl_total, uint32_t &nl_owned)
+{
+    const uint32_t c0 = __popc(nl0), c1 = __popc(nl1), c2 = __popc(nl2);
+    const uint32_t packed = c0 | (c1 << 11) | (c2 << 22);
+    uint32_t inc = packed;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    const uint32_t tot = __shfl_sync(0xffffffffu, inc, 31), excl = inc - packed;
+    const uint32_t t0 = tot & 0x7FFu, t1 = (tot >> 11) & 0x7FFu, t2 = tot >> 22;
+    const uint32_t r0 = nl_total + (excl & 0x7FFu), r1 = nl_total + t0 + ((excl >> 11) & 0x7FFu),
+                   r2 = nl_total + t0 + t1 + (excl >> 22);
+    nl_total += t0 + t1 + t2;
+    const int wb = (row0 * 32 + lane) << 5;         // tile coordinate of the lane's word in row0
+    if (!last) nl_owned += c0 + c1 + c2;            // rows below OWN_ROWS - 1: beyond tile_end only what lim has masked already
+    else {
+        const int e0 = t.tile_end - wb;
+        nl_owned += (uint32_t) (__popc(nl0 & __funnelshift_rc(0xFFFFFFFFu, 0u, (uint32_t) max(32 - max(e0, 0), 0)))
+                              + __popc(nl1 & __funnelshift_rc(0xFFFFFFFFu, 0u, (uint32_t) max(32 - max(e0 - KVQ_ROW, 0), 0)))
+                              + __popc(nl2 & __funnelshift_rc(0xFFFFFFFFu, 0u, (uint32_t) max(32 - max(e0 - 2 * KVQ_ROW, 0), 0))));
+    }
+    // positions of the first NLCAP newlines (round 0)
+    store_two(s, nl0, r0, wb);
+    store_two(s, nl1, r1, wb + KVQ_ROW);
+    store_two(s, nl2, r2, wb + 2 * KVQ_ROW);
+    if (__any_sync(0xffffffffu, (nl0 | nl1 | nl2) != 0)) {      // short lines: more than two newlines in 32 bytes
+        uint32_t q = r0 + 2;
+        while (nl0 && q < NLCAP) { s.nlpos[q++] = (uint16_t) (wb + 31 - __clz(nl0 & (0u - nl0))); nl0 &= nl0 - 1; }
+        q = r1 + 2;
+        while (nl1 && q < NLCAP) { s.nlpos[q++] = (uint16_t) (wb + KVQ_ROW + 31 - __clz(nl1 & (0u - nl1))); nl1 &= nl1 - 1; }
+        q = r2 + 2;
+        while (nl2 && q < NLCAP) { s.nlpos[q++] = (uint16_t) (wb + 2 * KVQ_ROW + 31 - __clz(nl2 & (0u - nl2))); nl2 &= nl2 - 1; }
+    }
+}
+
+#if KVQ_OLD_P1
 // Reduce one 32-byte word per lane to the three planes and rank its newlines (exclusive prefix
 // kept per word, running total in `nl_total`, those owned by the tile in `nl_owned`).
 template <bool NEG>
-__device__ __forceinline__ void reduce_row(WarpSmem &s, const TileCtx &t, const Row &r, int row, int lane,
-                                           uint32_t cl, uint32_t &nl_total, uint32_t &nl_owned)
+__device__ __forceinline__ void reduce_row_old(WarpSmem &s, const TileCtx &t, const Row &r, int row, int lane,
+                                           uint32_t cl, uint32_t cnl, uint32_t &nl_total, uint32_t &nl_owned)
 {
     const int w = row * 32 + lane;
-    uint32_t nl = gather32(gather2(nl_bits(r.a.x), nl_bits(r.a.y)), gather2(nl_bits(r.a.z), nl_bits(r.a.w)),
-                           gather2(nl_bits(r.b.x), nl_bits(r.b.y)), gather2(nl_bits(r.b.z), nl_bits(r.b.w)));
+    uint32_t nl = gather32(gather2(nl_bits(r.a.x, cnl), nl_bits(r.a.y, cnl)), gather2(nl_bits(r.a.z, cnl), nl_bits(r.a.w, cnl)),
+                           gather2(nl_bits(r.b.x, cnl), nl_bits(r.b.y, cnl)), gather2(nl_bits(r.b.z, cnl), nl_bits(r.b.w, cnl)));
     uint32_t ge;
     if (NEG)
         ge = gather32(gather2(ge_bits_neg(r.a.x, cl), ge_bits_neg(r.a.y, cl)), gather2(ge_bits_neg(r.a.z, cl), ge_bits_neg(r.a.w, cl)),
@@ -265,18 +350,20 @@ __device__ __forceinline__ void reduce_row(WarpSmem &s, const TileCtx &t, const 
     }
 }
 
+#endif
+
 // positions of the newlines ranked [base, base + NLCAP) -- only tiles with more than NLCAP
 // newlines (very short records) come here: the masks are computed again from the bytes (L1/L2)
 __device__ __forceinline__ void scatter_newlines(WarpSmem &s, const KvqBatch &b, const TileCtx &t, int nrows,
-                                                 int base, int lane)
+                                                 int base, int lane, uint32_t cnl)
 {
     int total = 0;
 #pragma unroll 1
     for (int row = 0; row < nrows; row++) {
         const int w = row * 32 + lane;
         const Row r = load_row(b, t, row, lane);
-        uint32_t m = gather32(gather2(nl_bits(r.a.x), nl_bits(r.a.y)), gather2(nl_bits(r.a.z), nl_bits(r.a.w)),
-                              gather2(nl_bits(r.b.x), nl_bits(r.b.y)), gather2(nl_bits(r.b.z), nl_bits(r.b.w)));
+        uint32_t m = gather32(gather2(nl_bits(r.a.x, cnl), nl_bits(r.a.y, cnl)), gather2(nl_bits(r.a.z, cnl), nl_bits(r.a.w, cnl)),
+                              gather2(nl_bits(r.b.x, cnl), nl_bits(r.b.y, cnl)), gather2(nl_bits(r.b.z, cnl), nl_bits(r.b.w, cnl)));
         const int lo = t.shift - (w << 5), hi = t.lim - (w << 5);
         if (lo > 0) m &= lo >= 32 ? 0u : (0xFFFFFFFFu << lo);
         if (hi < 32) m &= hi <= 0 ? 0u : ((1u << hi) - 1u);
@@ -1027,6 +1114,7 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
     __syncthreads();
     ThreadStats ts{0, 0, 0, 0};
     const uint32_t cl = (uint32_t) (p.amin & 0x7F) * 0x01010101u;
+    const uint32_t cnl = (uint32_t) p.nl_byte * 0x01010101u;        // '\n' x 4, from a parameter so that it lives in a register
     const uint32_t *tpk = (!BIG && t.packed_words <= KVQ_TPK_SMEM_WORDS) ? sh.tpk : t.packed;
 
     // Tile geometry: claim the next tile and start its bytes on their way to L2.
@@ -1098,41 +1186,49 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
             const int need = nown > 0 ? 4 * (nown - 1) + 3 + off : -1;  // rank of the last newline the tile needs
             return !(need < (int) n_all || next * KVQ_ROW >= tc.lim);
         };
-#if KVQ_ROW_SETS == 3
+#if KVQ_OLD_P1
         {
-            static_assert((OWN_ROWS + 2) % 3 == 0, "row triples");
             Row ra = load_row(b, tc, 0, lane), rb = load_row(b, tc, 1, lane), rc = load_row(b, tc, 2, lane);
 #pragma unroll 1
             for (int row = 0; row < MAX_ROWS; row += 3) {
-                reduce_row<NEG>(s, tc, ra, row, lane, cl, n_all, n_own);
+                reduce_row_old<NEG>(s, tc, ra, row, lane, cl, cnl, n_all, n_own);
                 if (row + 3 <= OWN_ROWS) ra = load_row(b, tc, row + 3, lane);
-                reduce_row<NEG>(s, tc, rb, row + 1, lane, cl, n_all, n_own);
+                reduce_row_old<NEG>(s, tc, rb, row + 1, lane, cl, cnl, n_all, n_own);
                 nrows = row + 2;
                 if (row + 4 <= OWN_ROWS) rb = load_row(b, tc, row + 4, lane);
                 if (row + 1 == OWN_ROWS) {
                     if (!settle(row + 2)) break;
                     rc = load_row(b, tc, row + 2, lane);
                 }
-                reduce_row<NEG>(s, tc, rc, row + 2, lane, cl, n_all, n_own);
+                reduce_row_old<NEG>(s, tc, rc, row + 2, lane, cl, cnl, n_all, n_own);
                 nrows = row + 3;
                 if (row + 5 <= OWN_ROWS) rc = load_row(b, tc, row + 5, lane);
             }
         }
 #else
         {
-            Row ra = load_row(b, tc, 0, lane), rb = load_row(b, tc, 1, lane);
+            static_assert((OWN_ROWS + 2) % 3 == 0 && KVQ_ROW_SETS == 3, "row triples");
+            Row ra = load_row(b, tc, 0, lane), rb = load_row(b, tc, 1, lane), rc = load_row(b, tc, 2, lane);
 #pragma unroll 1
-            for (int row = 0; row < MAX_ROWS; row += 2) {
-                reduce_row<NEG>(s, tc, ra, row, lane, cl, n_all, n_own);
-                nrows = row + 1;
-                if (row + 2 <= OWN_ROWS) ra = load_row(b, tc, row + 2, lane);
-                if (row == OWN_ROWS) {
-                    if (!settle(row + 1)) break;
-                    rb = load_row(b, tc, row + 1, lane);
-                }
-                reduce_row<NEG>(s, tc, rb, row + 1, lane, cl, n_all, n_own);
+            for (int row = 0; row < MAX_ROWS; row += 3) {
+                const uint32_t nl0 = reduce_row<NEG>(s, tc, ra, row, lane, cl, cnl);
+                if (row + 3 <= OWN_ROWS) ra = load_row(b, tc, row + 3, lane);
+                const uint32_t nl1 = reduce_row<NEG>(s, tc, rb, row + 1, lane, cl, cnl);
                 nrows = row + 2;
-                if (row + 3 <= OWN_ROWS) rb = load_row(b, tc, row + 3, lane);
+                if (row + 4 <= OWN_ROWS) rb = load_row(b, tc, row + 4, lane);
+                if (row + 1 == OWN_ROWS) {          // the last two mandatory rows: rank them, settle the phase
+                    rank_rows(s, tc, nl0, nl1, 0u, row, true, lane, n_all, n_own);
+                    if (!settle(row + 2)) break;
+                    rc = load_row(b, tc, row + 2, lane);
+                    const uint32_t nl2 = reduce_row<NEG>(s, tc, rc, row + 2, lane, cl, cnl);
+                    nrows = row + 3;
+                    rank_rows(s, tc, 0u, 0u, nl2, row, true, lane, n_all, n_own);
+                    break;
+                }
+                const uint32_t nl2 = reduce_row<NEG>(s, tc, rc, row + 2, lane, cl, cnl);
+                nrows = row + 3;
+                if (row + 5 <= OWN_ROWS) rc = load_row(b, tc, row + 5, lane);
+                rank_rows(s, tc, nl0, nl1, nl2, row, false, lane, n_all, n_own);
             }
         }
 #endif
@@ -1143,7 +1239,7 @@ kvq_scan_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         for (int k0 = 0; k0 < nown; k0 += 32) {
             const int base = k0 > 0 ? 4 * k0 + off - 1 : 0;
             __syncwarp();
-            if (k0 > 0) scatter_newlines(s, b, tc, nrows, base, lane);
+            if (k0 > 0) scatter_newlines(s, b, tc, nrows, base, lane, cnl);
             __syncwarp();
             run_round<BIG>(s, sh, c, k0, nown, base, (int) n_all, off, at_seg_end, lane, ts);
         }
