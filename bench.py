@@ -286,20 +286,28 @@ def main():
     seqs = ts.seqs()
     eng = Engine(local)
     eng.config(nthreads=max(1, (os.cpu_count() or 8) // max(1, world)), **CFG)
+    if dist is not None:
+        from kvarq_b200 import multi
+        multi.init_comm(eng, dist, rank, world)         # NCCL communicator inside libkvarq_b200.so
+        log('[rank %d] library communicator: %s' % (rank, eng.comm_info()))
 
     # ---- value: FastQ resident in HBM ------------------------------------------------------
     staged = eng.stage([fq])
     for _ in range(args.warmup):
         r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert=False)
+        if world > 1:
+            eng.allreduce(convert='timing')
     sampler = ClockSampler(local if rank == 0 else None)
     sampler.start()
     barrier()
     sampler.mark_begin()
     t0 = time.perf_counter()
-    kernel_ms, launches, d2h, call_ms = 0.0, 0, 0, 0.0
+    kernel_ms, launches, d2h, call_ms, reduce_ms = 0.0, 0, 0, 0.0, 0.0
     for _ in range(args.steps):
         r = eng.scan_staged(staged, seqs, nplus=ts.nplus, want_hits=True, convert='timing')   # syncs the stream
         kernel_ms += r.timing['kernel_ms']; launches += r.timing['launches']; d2h += r.timing['d2h_bytes']; call_ms += r.timing['wall_ms']
+        if world > 1:       # the per-template counters of all ranks: one ncclAllReduce per step, inside the timed region
+            reduce_ms += eng.allreduce(convert='timing').timing['reduce_ms']
     barrier()
     dt = allmax(time.perf_counter() - t0)
     sampler.mark_end()
@@ -314,36 +322,58 @@ def main():
     log('[rank %d] resident: %.3f ms/step wall, %.3f ms/step inside the C call, %.3f ms/step kernels, %d hits, %d records, %d candidates' %
         (rank, 1e3 * dt / args.steps, call_ms / args.steps, kernel_ms / args.steps, r.nhits, r['stats']['records_parsed'], r.timing['candidates']))
 
-    # ---- one NCCL all-reduce of the per-template counters (north_star; not in the timed region) --
-    if dist is not None:
+    # ---- the reduced counters of one more step, checked (the timed loop above already reduced every step)
+    reduce_info = None
+    if world > 1:
         import numpy as np
-        from kvarq_b200 import multi
-        flat, layout = multi.pack_counters(r.coverage, r.mutcount, r['stats']['nseqhits'], r['stats']['nseqbasehits'],
-                                           r['stats']['readlengths'], r['stats']['records_parsed'])
-        red = multi.unpack_counters(multi.all_reduce_counters(flat, dist, device='cuda'), layout)
-        assert red['records_parsed'] == world * r['stats']['records_parsed']
-        assert int(red['coverage'].sum()) == int(np.asarray(red['nseqbasehits']).sum())
-        log('[rank %d] NCCL all-reduce of %d int64 counters: %d records, total coverage %d' %
-            (rank, flat.size, red['records_parsed'], int(red['coverage'].sum())))
+        red = eng.allreduce()
+        assert red['stats']['records_parsed'] == world * r['stats']['records_parsed']
+        assert int(red.coverage.sum()) == int(np.asarray(red['stats']['nseqbasehits']).sum())
+        nwords = 2 * len(seqs) + 7 * len(red.coverage) + 1028
+        reduce_info = {'ms_per_step': allmax(reduce_ms / args.steps), 'int64_counters': nwords, 'in_timed_region': True,
+                       'where': 'libkvarq_b200.so kvq_allreduce: ncclAllReduce(int64, sum) in place on the device accumulators'}
+        log('[rank %d] NCCL all-reduce of %d int64 counters inside every step: %.3f ms/step, %d records, total coverage %d' %
+            (rank, nwords, reduce_ms / args.steps, red['stats']['records_parsed'], int(red.coverage.sum())))
 
-    # ---- e2e: host buffers through the C ABI, copies inside the timed region -----------------
+    # ---- e2e: the reference's own call, engine.findseqs(filename) (csrc/workhorse.c:1249), on a FastQ
+    # file in the page cache (/dev/shm): file -> pinned batches -> HBM -> results, everything inside the
+    # timed region.  e2e_mem: the same scan from a page-locked host buffer (kvq_findseqs_mem).
     e2e_steps = args.e2e_steps or min(args.steps, 3)
+    tmp = '/dev/shm' if os.path.isdir('/dev/shm') else '/tmp'
+    fq_file = os.path.join(tmp, 'kvq_bench_%d_%d.fastq' % (os.getpid(), rank))
+    with open(fq_file, 'wb') as f:
+        f.write(memoryview(fq))
+    try:
+        eng.findseqs(fq_file, seqs, nplus=ts.nplus, convert=False)                      # warm-up
+        barrier()
+        sampler.mark_begin()
+        t0 = time.perf_counter()
+        h2d = d2h_e = 0
+        for _ in range(e2e_steps):
+            q = eng.findseqs(fq_file, seqs, nplus=ts.nplus, convert=False)
+            h2d += q.timing['h2d_bytes']; d2h_e += q.timing['d2h_bytes']
+        barrier()
+        dt_e = allmax(time.perf_counter() - t0)
+        sampler.mark_end()
+    finally:
+        os.remove(fq_file)
+    e2e = allsum(q.timing['bases'] * e2e_steps) / dt_e / 1e9
+    assert q.nhits == r.nhits and q['stats']['records_parsed'] == r['stats']['records_parsed']
+    log('[rank %d] e2e (file): %.1f ms/step' % (rank, 1e3 * dt_e / e2e_steps))
     fq_pin = eng.pinned_copy(fq)                                                    # inputs in pinned host memory
     eng.findseqs_mem([fq_pin], seqs, nplus=ts.nplus, want_hits=False)               # warm-up
     barrier()
     sampler.mark_begin()
     t0 = time.perf_counter()
-    h2d = d2h_e = 0
     for _ in range(e2e_steps):
-        q = eng.findseqs_mem([fq_pin], seqs, nplus=ts.nplus, want_hits=False)
-        h2d += q.timing['h2d_bytes']; d2h_e += q.timing['d2h_bytes']
+        qm = eng.findseqs_mem([fq_pin], seqs, nplus=ts.nplus, want_hits=False)
     barrier()
-    dt_e = allmax(time.perf_counter() - t0)
+    dt_m = allmax(time.perf_counter() - t0)
     sampler.mark_end()
     clocks = sampler.summary()
-    e2e = allsum(q.timing['bases'] * e2e_steps) / dt_e / 1e9
-    assert q.nhits == r.nhits and q['stats']['records_parsed'] == r['stats']['records_parsed']
-    log('[rank %d] e2e: %.1f ms/step' % (rank, 1e3 * dt_e / e2e_steps))
+    e2e_mem = allsum(qm.timing['bases'] * e2e_steps) / dt_m / 1e9
+    assert qm.nhits == r.nhits and qm['stats']['records_parsed'] == r['stats']['records_parsed']
+    log('[rank %d] e2e (pinned buffer): %.1f ms/step' % (rank, 1e3 * dt_m / e2e_steps))
 
     # ---- CPU baseline on rank 0 at N=1 -------------------------------------------------------
     cpu = None
@@ -380,7 +410,10 @@ def main():
                          'algorithmic_bytes_per_launch': stream_bytes},
             'cpu_baseline': cpu, 'parity_prefix': parity_prefix,
             'e2e': {'value': e2e, 'unit': 'Gbp/s', 'h2d_bytes_per_step': h2d // e2e_steps,
-                    'd2h_bytes_per_step': d2h_e // e2e_steps, 'steps': e2e_steps},
+                    'd2h_bytes_per_step': d2h_e // e2e_steps, 'steps': e2e_steps,
+                    'path': 'engine.findseqs(file in /dev/shm): kvq_findseqs, file -> pinned batches -> HBM -> results'},
+            'e2e_mem': {'value': e2e_mem, 'unit': 'Gbp/s', 'path': 'kvq_findseqs_mem on a page-locked host buffer'},
+            'reduce': reduce_info,
             'gpu_launches': launches, 'clocks': clocks,
             'hits_per_step': r.nhits, 'records_per_step': r['stats']['records_parsed'],
         })

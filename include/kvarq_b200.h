@@ -145,6 +145,30 @@ int kvq_stop(kvq_engine *e);
  * csrc/workhorse.c:1454-1458) */
 const char *kvq_last_error(kvq_engine *e, int *cls);
 
+/* ---- multi-GPU: one process and one engine per GPU.  The reference has no counterpart --
+ * its parallelism is nthreads pthreads sharing one file handle (csrc/workhorse.c:1375-1406); here the
+ * read stream is dealt to the ranks (records are independent, templates replicated) and the
+ * per-template counters of Coverage.apply_hit / add_hit (kvarq/analyse.py:57-78, workhorse.c:408-443)
+ * are summed with one ncclAllReduce(int64) over NVLink.  NCCL is bound at run time (the copy already
+ * in the process, else $KVQ_NCCL_LIB, else libnccl.so.2). */
+#define KVQ_COMM_ID_BYTES 128
+int kvq_comm_unique_id(char *id128);                       /* rank 0 makes it, the launcher hands it to every rank */
+int kvq_comm_init(kvq_engine *e, const char *id128, int rank, int world);
+int kvq_comm_destroy(kvq_engine *e);
+int kvq_comm_info(kvq_engine *e, int *rank, int *world, int *nccl_version);
+/* Sums the counters of the engine's last scan (`r`) over all ranks, in place on the device, and
+ * writes the sums into r: coverage, mutcount, nseqhits, nseqbasehits, readlengths, records_parsed,
+ * parsed, bases.  Hits stay per rank.  reduce_ms (may be NULL): device time of the collective. */
+int kvq_allreduce(kvq_engine *e, kvq_result *r, double *reduce_ms);
+/* Batch of isolates (docs/tutorial.rst:378 "hundreds of genomes"): [nslots][row] int64 matrix in HBM,
+ * row = counters of one scan (kvq_job_row_words: nseqhits, nseqbasehits, coverage, mutcount[6],
+ * readlengths[1024], records, bases, parsed, longest+1); each rank stores the isolates it scanned,
+ * one all-reduce at the end gives every rank the whole matrix. */
+int kvq_job_begin(kvq_engine *e, int nslots, int64_t row_words);
+int64_t kvq_job_row_words(kvq_engine *e);
+int kvq_job_store(kvq_engine *e, int slot, const kvq_result *r);
+int kvq_job_allreduce(kvq_engine *e, int64_t *out, int64_t cap_words, double *reduce_ms);
+
 /* build/device info, "sm_100a" etc. */
 const char *kvq_version(void);
 int kvq_device_count(void);

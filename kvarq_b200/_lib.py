@@ -69,6 +69,15 @@ SIGNATURES = {
     'kvq_stats_snapshot': (C.c_int, [VP, P(Stats), P(C.c_int64), P(C.c_int64), C.c_int]),
     'kvq_stop': (C.c_int, [VP]),
     'kvq_last_error': (C.c_char_p, [VP, P(C.c_int)]),
+    'kvq_comm_unique_id': (C.c_int, [C.c_char_p]),
+    'kvq_comm_init': (C.c_int, [VP, C.c_char_p, C.c_int, C.c_int]),
+    'kvq_comm_destroy': (C.c_int, [VP]),
+    'kvq_comm_info': (C.c_int, [VP, P(C.c_int), P(C.c_int), P(C.c_int)]),
+    'kvq_allreduce': (C.c_int, [VP, VP, P(C.c_double)]),
+    'kvq_job_begin': (C.c_int, [VP, C.c_int, C.c_int64]),
+    'kvq_job_row_words': (C.c_int64, [VP]),
+    'kvq_job_store': (C.c_int, [VP, C.c_int, VP]),
+    'kvq_job_allreduce': (C.c_int, [VP, P(C.c_int64), C.c_int64, P(C.c_double)]),
     'kvq_version': (C.c_char_p, []),
     'kvq_device_count': (C.c_int, []),
 }

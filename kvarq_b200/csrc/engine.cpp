@@ -4,6 +4,10 @@
 // All matching happens in scan_kernel.cu; there is no CPU matcher in this library.
 #include <cuda_runtime.h>
 #include <zlib.h>
+#include <fcntl.h>
+#include <unistd.h>
+#include <sys/stat.h>
+#include <functional>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -21,6 +25,7 @@
 
 #include "../../include/kvarq_b200.h"
 #include "kvq_device.h"
+#include "nccl_shim.h"
 
 namespace {
 
@@ -58,6 +63,70 @@ struct Source {
     virtual int64_t disk_pos() const = 0;           // ftell() of the reference at this point
     virtual bool compressed() const = 0;
     virtual const char *direct() const { return nullptr; }   // next unread byte, if the source is memory
+    // Plain files: read up to `max` bytes ahead, with all reader threads, straight to where the
+    // following fill() calls will want them (dst = target of the next fill); end_batch() keeps what
+    // the batch did not take.
+    virtual void preload(char *, int64_t) {}
+    virtual void end_batch() {}
+};
+
+// A few persistent host threads for the byte-moving work of the reader (page cache -> pinned batch
+// buffer): one thread copies at 5-6 GB/s, the H2D link takes 50+.
+class WorkPool {
+public:
+    explicit WorkPool(int n) {
+        for (int i = 0; i < n; i++) th_.emplace_back([this] { loop(); });
+    }
+    ~WorkPool() {
+        { std::lock_guard<std::mutex> g(mu_); quit_ = true; }
+        cv_.notify_all();
+        for (auto &t : th_) t.join();
+    }
+    int size() const { return (int) th_.size(); }
+    // fn(i) for i in [0, n), the caller takes part; returns when all are done
+    void run(int n, const std::function<void(int)> &fn) {
+        if (n <= 0) return;
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            fn_ = &fn; next_ = 0; total_ = n; pending_ = n; gen_++;
+        }
+        cv_.notify_all();
+        work();
+        std::unique_lock<std::mutex> g(mu_);
+        done_.wait(g, [&] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+private:
+    void work() {
+        for (;;) {
+            int i;
+            const std::function<void(int)> *fn;
+            {
+                std::lock_guard<std::mutex> g(mu_);
+                if (!fn_ || next_ >= total_) return;
+                i = next_++; fn = fn_;
+            }
+            (*fn)(i);
+            std::lock_guard<std::mutex> g(mu_);
+            if (--pending_ == 0) done_.notify_all();
+        }
+    }
+    void loop() {
+        uint64_t seen = 0;
+        for (;;) {
+            {
+                std::unique_lock<std::mutex> g(mu_);
+                cv_.wait(g, [&] { return quit_ || gen_ != seen; });
+                if (quit_) return;
+                seen = gen_;
+            }
+            work();
+        }
+    }
+    std::vector<std::thread> th_;
+    std::mutex mu_; std::condition_variable cv_, done_;
+    const std::function<void(int)> *fn_ = nullptr;
+    int next_ = 0, total_ = 0, pending_ = 0; uint64_t gen_ = 0; bool quit_ = false;
 };
 
 struct MemSource : Source {
@@ -77,22 +146,65 @@ struct MemSource : Source {
 };
 
 struct PlainFileSource : Source {
-    FILE *fd; int64_t size;
-    explicit PlainFileSource(const char *name) {
-        fd = fopen(name, "rb");
-        if (!fd) throw KvqError(KVQ_ERR_IO, "cannot open file");                     // workhorse.c:577
-        fseek(fd, 0, SEEK_END); size = ftell(fd); fseek(fd, 0, SEEK_SET);
-        setvbuf(fd, nullptr, _IONBF, 0);
+    int fd; int64_t size, pos = 0; WorkPool *pool;
+    // file bytes [stg_off, stg_off + stg_len) already in memory at stg_ptr (the batch buffer, or `spill`)
+    char *stg_ptr = nullptr; int64_t stg_off = 0, stg_len = 0; std::vector<char> spill;
+    PlainFileSource(const char *name, WorkPool *pool_) : pool(pool_) {
+        fd = open(name, O_RDONLY);
+        struct stat st;
+        if (fd < 0 || fstat(fd, &st) != 0) { if (fd >= 0) close(fd); throw KvqError(KVQ_ERR_IO, "cannot open file"); }   // workhorse.c:577
+        size = (int64_t) st.st_size;
     }
-    ~PlainFileSource() override { if (fd) fclose(fd); }
+    ~PlainFileSource() override { if (fd >= 0) close(fd); }
+    static void read_range(int fd, char *dst, int64_t off, int64_t n) {
+        while (n > 0) {
+            const ssize_t m = pread(fd, dst, (size_t) n, (off_t) off);
+            if (m < 0) throw KvqError(KVQ_ERR_IO, "error while reading from file in fastq_read");   // :894
+            if (m == 0) { memset(dst, 0, (size_t) n); return; }       // (file shrank under the scan)
+            dst += m; off += m; n -= m;
+        }
+    }
     int64_t fill(char *dst, int64_t cap, bool *filled) override {
-        int64_t m = (int64_t) fread(dst, 1, cap, fd);
-        if (ferror(fd)) throw KvqError(KVQ_ERR_IO, "error while reading from file in fastq_read");   // :894
+        const int64_t m = std::min(cap, size - pos);
+        if (m > 0) {
+            if (pos >= stg_off && pos + m <= stg_off + stg_len) {
+                const char *src = stg_ptr + (pos - stg_off);
+                if (src != dst) memcpy(dst, src, (size_t) m);
+            } else read_range(fd, dst, pos, m);
+        }
+        pos += m;
         *filled = (m == cap);       // feof() is set exactly when fread came up short (:901)
         return m;
     }
+    void preload(char *dst, int64_t max) override {
+        const int64_t m = std::min(max, size - pos);
+        if (m <= 0) { stg_len = 0; return; }
+        int64_t have = 0;
+        if (stg_len > 0 && pos >= stg_off && pos < stg_off + stg_len) {     // what the last batch left over
+            have = std::min(m, stg_off + stg_len - pos);
+            memmove(dst, stg_ptr + (pos - stg_off), (size_t) have);
+        }
+        const int64_t from = pos + have, n = m - have, part = 2 << 20;
+        const int parts = (int) ((n + part - 1) / part);
+        std::exception_ptr err; std::mutex emu;
+        auto job = [&](int i) {
+            try { read_range(fd, dst + have + (int64_t) i * part, from + (int64_t) i * part, std::min<int64_t>(part, n - (int64_t) i * part)); }
+            catch (...) { std::lock_guard<std::mutex> g(emu); err = std::current_exception(); }
+        };
+        if (pool && parts > 1) pool->run(parts, job);
+        else for (int i = 0; i < parts; i++) job(i);
+        if (err) std::rethrow_exception(err);
+        stg_ptr = dst; stg_off = pos; stg_len = m;
+    }
+    void end_batch() override {
+        if (stg_len > 0 && pos < stg_off + stg_len && stg_ptr != spill.data()) {
+            std::vector<char> keep(stg_ptr + (pos - stg_off), stg_ptr + stg_len);
+            spill.swap(keep);
+            stg_ptr = spill.data(); stg_off = pos; stg_len = (int64_t) spill.size();
+        } else if (pos >= stg_off + stg_len) stg_len = 0;
+    }
     int64_t disk_size() const override { return size; }
-    int64_t disk_pos() const override { return ftell(fd); }
+    int64_t disk_pos() const override { return pos; }
     bool compressed() const override { return false; }
 };
 
@@ -330,8 +442,8 @@ struct HostBatch {
 class StreamCutter {
 public:
     StreamCutter(std::vector<std::string> names, std::vector<std::pair<const char *, int64_t>> mems,
-                 LiveStats *live)
-        : names_(std::move(names)), mems_(std::move(mems)), live_(live)
+                 LiveStats *live, WorkPool *pool = nullptr)
+        : names_(std::move(names)), mems_(std::move(mems)), live_(live), pool_(pool)
     {
         nfiles_ = names_.empty() ? (int) mems_.size() : (int) names_.size();
         // fastq_open (:659-677): total size first, then the first file
@@ -366,12 +478,16 @@ public:
         carry_.clear();
         b.base_fpos = fpos_ - left;
         int64_t win = 0;
+        // plain files: everything this batch can take is read now, by all reader threads, to where
+        // the fill() calls below expect it (they find it in place and copy nothing)
+        if (!finished_ && src_ && !b.borrowed) src_->preload(b.data + left, BATCH_BYTES - left);
         while (!finished_) {
             if (stop.load(std::memory_order_relaxed)) { finished_ = true; left = 0; break; }
             if (win + REF_CHUNK > BATCH_BYTES) break;                       // batch full
             if (at_eof_ && next_file_ < nfiles_) {                          // :749-753
                 if (b.borrowed) break;                                      // next buffer = next batch
                 open_next();
+                src_->preload(b.data + win + left, BATCH_BYTES - win - left);
             }
             at_eof_ = false;
             bool filled = false;
@@ -400,6 +516,7 @@ public:
             b.cuts.push_back(win);
         }
         if (left) carry_.assign(b.data + win, b.data + win + left);
+        if (src_) src_->end_batch();
         b.nbytes = win;
         if (!b.borrowed) memset(b.data + win, 0, BATCH_PAD);
         return win > 0;
@@ -421,7 +538,7 @@ private:
             } else {
                 if (compressed_)
                     throw KvqError(KVQ_ERR_IO, "error while inflating compressed data : plain file after .gz");
-                src_.reset(new PlainFileSource(names_[i].c_str()));
+                src_.reset(new PlainFileSource(names_[i].c_str(), pool_));
             }
         } else {
             src_.reset(new MemSource(mems_[i].first, mems_[i].second));
@@ -443,6 +560,7 @@ private:
     std::vector<std::string> names_;
     std::vector<std::pair<const char *, int64_t>> mems_;
     LiveStats *live_;
+    WorkPool *pool_ = nullptr;
     int nfiles_ = 0, next_file_ = 0;
     std::unique_ptr<Source> src_;
     bool at_eof_ = false, compressed_ = false, finished_ = false;
@@ -844,7 +962,10 @@ struct Slot {                           // one batch in flight
 };
 
 struct Accum {                          // device-wide accumulators of one scan, one allocation:
-    DevBuf d_all; size_t ns = 0, nc = 0;    // [nseqhits ns][nseqbasehits ns][coverage nc][mutcount 6 nc]
+    DevBuf d_all; size_t ns = 0, nc = 0;    // [nseqhits ns][nseqbasehits ns][coverage nc][mutcount 6 nc][tail]
+    // tail (filled from the host totals right before a reduce): [readlengths 1024][records][bases][parsed][longest + 1]
+    static constexpr size_t TAIL = KVQ_HIST + 4;
+    size_t row_words() const { return words() + TAIL; }
     unsigned long long *seqhits() const { return d_all.as<unsigned long long>(); }
     unsigned long long *seqbase() const { return seqhits() + ns; }
     unsigned long long *cov() const { return seqhits() + 2 * ns; }
@@ -874,7 +995,11 @@ struct kvq_engine {
     cudaStream_t copy_stream = nullptr;             // all batch uploads, back to back (concurrent H2D copies share the link badly)
     Accum acc;
     TemplateSet tpl;
-    PinBuf pin_out, pin_acc, pin_ord, pin_ctr2;               // page-locked staging of the result copies
+    PinBuf pin_out, pin_acc, pin_ord, pin_ctr2;
+    std::unique_ptr<WorkPool> pool; int pool_threads = 0;      // reader threads (plain files)
+    // multi-GPU: one NCCL communicator per engine (one engine per process and GPU)
+    ncclComm_t comm = nullptr; int rank = 0, world = 1;
+    DevBuf d_job, d_max; int job_slots = 0; size_t job_row = 0; PinBuf pin_tail;               // page-locked staging of the result copies
     SortScratch scratch;
 
     void set_error(int cls, const std::string &m) { std::lock_guard<std::mutex> g(mu); err_cls = cls; err_msg = m; }
@@ -969,8 +1094,8 @@ void reset_accum(kvq_engine *e, cudaStream_t st)
 {
     const TemplateSet &t = e->tpl;
     e->acc.ns = (size_t) std::max(1, t.nseqs); e->acc.nc = (size_t) std::max<int64_t>(1, t.cov_total);
-    e->acc.d_all.ensure(e->acc.words() * 8);
-    CK(cudaMemsetAsync(e->acc.d_all.p, 0, e->acc.words() * 8, st));
+    e->acc.d_all.ensure(e->acc.row_words() * 8);
+    CK(cudaMemsetAsync(e->acc.d_all.p, 0, e->acc.row_words() * 8, st));
 }
 
 // enqueue memset + scan + emit + long-record kernels for one batch already resident on the device
@@ -1250,7 +1375,14 @@ kvq_result *run_stream_scan(kvq_engine *e, std::vector<std::string> names,
     const bool trace_stream = getenv("KVQ_TRACE") != nullptr;
     init_slots(e);
     reset_accum(e, e->copy_stream);         // every slot stream waits for an event recorded later on this stream
-    StreamCutter cutter(std::move(names), std::move(mems), &e->live);
+    {   // reader threads: engine.config(nthreads), at least min(8, cores); KVQ_READ_THREADS overrides
+        kvq_config_t cfg; { std::lock_guard<std::mutex> g(e->mu); cfg = e->cfg; }
+        int want = std::max<int>(cfg.nthreads, (int) std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency())));
+        if (const char *v = getenv("KVQ_READ_THREADS")) want = atoi(v);
+        want = std::max(1, std::min(want, 64));
+        if (!names.empty() && (!e->pool || e->pool_threads != want)) { e->pool.reset(new WorkPool(want - 1)); e->pool_threads = want; }
+    }
+    StreamCutter cutter(std::move(names), std::move(mems), &e->live, e->pool.get());
     ScanTotals tot;
     Chan<int> free_q, ready_q;
     for (int i = 0; i < NSLOT; i++) free_q.push(i);
@@ -1392,6 +1524,7 @@ void kvq_destroy(kvq_engine *e)
         if (s.ev_copied) cudaEventDestroy(s.ev_copied);
     }
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    if (e->comm && kvq_nccl::api().CommDestroy) kvq_nccl::api().CommDestroy(e->comm);
     delete e;
 }
 
@@ -1676,5 +1809,190 @@ void *kvq_host_alloc(int64_t nbytes)
 }
 
 void kvq_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+} // extern "C"
+
+// ------------------------------------------------------------------------------- multi-GPU (NCCL)
+// One process per GPU, every rank scans its own share of the stream (records are independent, the
+// template set is replicated); the per-template counters are combined with ONE ncclAllReduce
+// (int64, sum) over NVLink at the end -- SURVEY 8(e).  The counters never leave the device before the
+// reduce: the accumulators the kernels wrote are reduced in place on the scan stream.
+namespace {
+
+void nccl_check(ncclResult_t r, const char *what)
+{
+    if (r != ncclSuccess)
+        throw KvqError(KVQ_ERR_RUNTIME, std::string("NCCL failure in ") + what + ": " + kvq_nccl::api().GetErrorString(r));
+}
+
+kvq_nccl::Api &need_nccl()
+{
+    kvq_nccl::Api &a = kvq_nccl::api();
+    if (!a.handle || !a.error.empty()) throw KvqError(KVQ_ERR_RUNTIME, a.error.empty() ? "NCCL not available" : a.error);
+    return a;
+}
+
+// host totals of the last scan -> tail of the device accumulator row (see Accum)
+void upload_tail(kvq_engine *e, const kvq_result *r, cudaStream_t st)
+{
+    e->pin_tail.ensure(Accum::TAIL * 8);
+    int64_t *t = e->pin_tail.as<int64_t>();
+    for (int i = 0; i < KVQ_HIST; i++) t[i] = r->stats.readlengths[i];
+    t[KVQ_HIST] = r->stats.records_parsed; t[KVQ_HIST + 1] = r->timing.bases;
+    t[KVQ_HIST + 2] = r->stats.parsed; t[KVQ_HIST + 3] = r->stats.rls_longest + 1;
+    CK(cudaMemcpyAsync(e->acc.seqhits() + e->acc.words(), t, Accum::TAIL * 8, cudaMemcpyHostToDevice, st));
+}
+
+void check_result_shape(kvq_engine *e, const kvq_result *r)
+{
+    if (!r) throw KvqError(KVQ_ERR_TYPE, "result is NULL");
+    if (!e->acc.d_all.p || (int) r->nseqhits.size() != e->tpl.nseqs)
+        throw KvqError(KVQ_ERR_RUNTIME, "the result is not the engine's last scan");
+}
+
+} // namespace
+
+extern "C" {
+
+int kvq_comm_unique_id(char *id)
+{
+    if (!id) return KVQ_ERR_TYPE;
+    kvq_nccl::Api &a = kvq_nccl::api();
+    if (!a.handle || !a.error.empty()) return KVQ_ERR_RUNTIME;
+    ncclUniqueId u;
+    if (a.GetUniqueId(&u) != ncclSuccess) return KVQ_ERR_RUNTIME;
+    static_assert(sizeof(u) == KVQ_COMM_ID_BYTES, "ncclUniqueId is 128 bytes");
+    memcpy(id, &u, sizeof(u));
+    return KVQ_OK;
+}
+
+int kvq_comm_init(kvq_engine *e, const char *id, int rank, int world)
+{
+    return guarded(e, [&] {
+        if (!id || world < 1 || rank < 0 || rank >= world) throw KvqError(KVQ_ERR_TYPE, "bad communicator arguments");
+        kvq_nccl::Api &a = need_nccl();
+        CK(cudaSetDevice(e->device));
+        if (e->comm) { a.CommDestroy(e->comm); e->comm = nullptr; }
+        ncclUniqueId u; memcpy(&u, id, sizeof(u));
+        nccl_check(a.CommInitRank(&e->comm, world, u, rank), "ncclCommInitRank");
+        e->rank = rank; e->world = world;
+    });
+}
+
+int kvq_comm_destroy(kvq_engine *e)
+{
+    return guarded(e, [&] {
+        if (e->comm) { CK(cudaSetDevice(e->device)); need_nccl().CommDestroy(e->comm); e->comm = nullptr; }
+        e->rank = 0; e->world = 1;
+    });
+}
+
+int kvq_comm_info(kvq_engine *e, int *rank, int *world, int *nccl_version)
+{
+    if (!e) return KVQ_ERR_TYPE;
+    if (rank) *rank = e->rank;
+    if (world) *world = e->comm ? e->world : 1;
+    if (nccl_version) { *nccl_version = 0; kvq_nccl::Api &a = kvq_nccl::api(); if (a.GetVersion) a.GetVersion(nccl_version); }
+    return KVQ_OK;
+}
+
+// Sums the counters of this engine's last scan over all ranks and writes the sums into `r`
+// (coverage, mutcount, nseqhits, nseqbasehits, readlengths, records_parsed, parsed, bases; rls_longest
+// is the maximum).  Device accumulators -> ncclAllReduce in place on the scan stream -> one D2H copy.
+// Hits stay per rank.  Without a communicator (world 1) the result is left as it is.
+int kvq_allreduce(kvq_engine *e, kvq_result *r, double *reduce_ms)
+{
+    if (reduce_ms) *reduce_ms = 0;
+    return guarded(e, [&] {
+        check_result_shape(e, r);
+        if (!e->comm) return;
+        RunGuard run(e);
+        if (!run.owns) throw KvqError(KVQ_ERR_RUNTIME, "findseqs() already running!");
+        kvq_nccl::Api &a = need_nccl();
+        CK(cudaSetDevice(e->device));
+        init_slots(e);
+        Slot &s0 = e->slots[0];
+        cudaStream_t st = s0.stream;
+        const size_t n = e->acc.row_words();
+        upload_tail(e, r, st);
+        CK(cudaEventRecord(s0.ev0, st));
+        nccl_check(a.AllReduce(e->acc.d_all.p, e->acc.d_all.p, n, ncclInt64, ncclSum, e->comm, st), "ncclAllReduce");
+        CK(cudaEventRecord(s0.ev1, st));
+        e->pin_acc.ensure(n * 8);
+        CK(cudaMemcpyAsync(e->pin_acc.p, e->acc.d_all.p, n * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (reduce_ms) { float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1)); *reduce_ms = ms; }
+        const int64_t *all = e->pin_acc.as<int64_t>();
+        const size_t ns = e->acc.ns, nc = e->acc.nc;
+        for (int i = 0; i < e->tpl.nseqs; i++) { r->nseqhits[i] = all[i]; r->nseqbasehits[i] = all[ns + i]; }
+        if (!r->coverage.empty()) {
+            r->coverage.assign(all + 2 * ns, all + 2 * ns + r->coverage.size());
+            r->mutcount.assign(all + 2 * ns + nc, all + 2 * ns + nc + r->mutcount.size());
+        }
+        const int64_t *t = all + e->acc.words();
+        // the longest read length is a maximum, not a sum: every rank's histogram is in the sum, so it is
+        // the last non-empty bin -- or, beyond the histogram (>= 1024, workhorse.c:397-400), left per rank
+        int64_t longest = -1;
+        for (int i = 0; i < KVQ_HIST; i++) { r->stats.readlengths[i] = t[i]; if (t[i]) longest = i; }
+        r->stats.rls_longest = std::max(r->stats.rls_longest, longest);
+        r->stats.records_parsed = t[KVQ_HIST]; r->timing.bases = t[KVQ_HIST + 1]; r->stats.parsed = t[KVQ_HIST + 2];
+    });
+}
+
+// Batch jobs (BASELINE config 5: many isolates over the ranks): a zeroed [nslots][row] int64 matrix in
+// HBM; after each scan the rank stores that isolate's counters into the isolate's row (device to
+// device); ONE ncclAllReduce over the whole matrix at the end gives every rank every isolate.
+int kvq_job_begin(kvq_engine *e, int nslots, int64_t row_words)
+{
+    return guarded(e, [&] {
+        if (nslots < 1 || row_words < (int64_t) Accum::TAIL) throw KvqError(KVQ_ERR_TYPE, "bad job shape");
+        CK(cudaSetDevice(e->device));
+        e->job_slots = nslots; e->job_row = (size_t) row_words;
+        e->d_job.ensure((size_t) nslots * e->job_row * 8);
+        CK(cudaMemset(e->d_job.p, 0, (size_t) nslots * e->job_row * 8));
+    });
+}
+
+int64_t kvq_job_row_words(kvq_engine *e)     // row of the engine's last scan: 2 nseqs + 7 sum(len plus) + 1028
+{
+    return e && e->acc.d_all.p ? (int64_t) e->acc.row_words() : 0;
+}
+
+int kvq_job_store(kvq_engine *e, int slot, const kvq_result *r)
+{
+    return guarded(e, [&] {
+        check_result_shape(e, r);
+        if (slot < 0 || slot >= e->job_slots || e->acc.row_words() != e->job_row) throw KvqError(KVQ_ERR_TYPE, "bad job slot");
+        CK(cudaSetDevice(e->device));
+        init_slots(e);
+        cudaStream_t st = e->slots[0].stream;
+        upload_tail(e, r, st);
+        CK(cudaMemcpyAsync(e->d_job.as<int64_t>() + (size_t) slot * e->job_row, e->acc.d_all.p, e->job_row * 8,
+                           cudaMemcpyDeviceToDevice, st));
+        CK(cudaStreamSynchronize(st));
+    });
+}
+
+int kvq_job_allreduce(kvq_engine *e, int64_t *out, int64_t cap_words, double *reduce_ms)
+{
+    if (reduce_ms) *reduce_ms = 0;
+    return guarded(e, [&] {
+        const size_t n = (size_t) e->job_slots * e->job_row;
+        if (!e->d_job.p || !out || (size_t) cap_words < n) throw KvqError(KVQ_ERR_TYPE, "bad job buffer");
+        CK(cudaSetDevice(e->device));
+        init_slots(e);
+        Slot &s0 = e->slots[0];
+        cudaStream_t st = s0.stream;
+        if (e->comm) {
+            kvq_nccl::Api &a = need_nccl();
+            CK(cudaEventRecord(s0.ev0, st));
+            nccl_check(a.AllReduce(e->d_job.p, e->d_job.p, n, ncclInt64, ncclSum, e->comm, st), "ncclAllReduce");
+            CK(cudaEventRecord(s0.ev1, st));
+        }
+        CK(cudaMemcpyAsync(out, e->d_job.p, n * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (e->comm && reduce_ms) { float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1)); *reduce_ms = ms; }
+    });
+}
 
 } // extern "C"

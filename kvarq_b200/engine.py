@@ -71,6 +71,7 @@ class Engine(object):
 
     def close(self):
         if getattr(self, '_h', None):
+            self._free_kept()
             self._lib.kvq_destroy(self._h)
             self._h = None
 
@@ -140,8 +141,15 @@ class Engine(object):
             'records_parsed': int(st.records_parsed),
         }
 
+    def _free_kept(self):
+        if getattr(self, '_kept', None):
+            self._lib.kvq_result_free(self._kept)
+            self._kept = None
+
     def _take_result(self, res, want_hits=True):
         lib = self._lib
+        self._free_kept()
+        self._kept = C.c_void_p(res.value)       # the C result of the last scan stays alive for allreduce() / job_store()
         try:
             n = lib.kvq_result_nhits(res)
             if want_hits == 'timing':           # bench loop: no Python objects beyond the counters
@@ -178,10 +186,12 @@ class Engine(object):
             out.nhits = n
             return out
         finally:
-            lib.kvq_result_free(res)
+            pass
 
     # -- engine.findseqs (workhorse.c:1249-1464) --------------------------------------------
-    def findseqs(self, fname, seqlist, nplus=0):
+    def findseqs(self, fname, seqlist, nplus=0, convert=True):
+        """convert=False: the hit list is produced and copied back but not turned into Python tuples
+        (result.nhits counts them); the scan itself is identical."""
         if isinstance(fname, (str, bytes)):
             fnames = [fname]
         else:
@@ -197,7 +207,7 @@ class Engine(object):
         rc = self._lib.kvq_findseqs(self._h, c_fn, len(bf), arr, lens, n, nplus, C.byref(res))
         if rc != 0:
             self._raise(rc)
-        return self._take_result(res)
+        return self._take_result(res, convert)
 
     def findseqs_mem(self, buffers, seqlist, nplus=0, want_hits=True):
         """Scan in-memory FastQ 'files' (bytes / numpy uint8 / anything with a buffer).
@@ -259,6 +269,64 @@ class Engine(object):
         if rc != 0:
             self._raise(rc)
         return self._take_result(res, want_hits if convert is None else convert)
+
+    # -- multi-GPU: one engine per process and GPU, NCCL inside the library -------
+    @staticmethod
+    def unique_id():
+        """128-byte NCCL id made by one rank; every rank passes it to comm_init()."""
+        buf = C.create_string_buffer(128)
+        if L.load().kvq_comm_unique_id(buf) != 0:
+            raise RuntimeError('kvarq_b200: NCCL is not available (libnccl.so.2)')
+        return buf.raw
+
+    def comm_init(self, unique_id, rank, world):
+        rc = self._lib.kvq_comm_init(self._h, unique_id, rank, world)
+        if rc != 0:
+            self._raise(rc)
+
+    def comm_info(self):
+        r, w, v = C.c_int(), C.c_int(), C.c_int()
+        self._lib.kvq_comm_info(self._h, C.byref(r), C.byref(w), C.byref(v))
+        return {'rank': r.value, 'world': w.value, 'nccl_version': v.value}
+
+    def allreduce(self, result=None, convert=True):
+        """Sum the counters of the last scan over all ranks (one ncclAllReduce of the device
+        accumulators, int64) and return them as a Result (no hits: those stay per rank).
+        result.timing['reduce_ms'] = device time of the collective."""
+        if not getattr(self, '_kept', None):
+            raise RuntimeError('allreduce() follows a scan')
+        ms = C.c_double()
+        rc = self._lib.kvq_allreduce(self._h, self._kept, C.byref(ms))
+        if rc != 0:
+            self._raise(rc)
+        kept, self._kept = self._kept, None
+        out = self._take_result(kept, 'timing' if convert == 'timing' else False)
+        out.timing['reduce_ms'] = ms.value
+        return out
+
+    def job_begin(self, nslots):
+        """Batch of isolates: one row of counters per isolate in HBM (call after the first scan of
+        the template set, which fixes the row length)."""
+        self._job = (nslots, self._lib.kvq_job_row_words(self._h))
+        rc = self._lib.kvq_job_begin(self._h, nslots, self._job[1])
+        if rc != 0:
+            self._raise(rc)
+
+    def job_store(self, slot):
+        rc = self._lib.kvq_job_store(self._h, slot, self._kept)
+        if rc != 0:
+            self._raise(rc)
+
+    def job_allreduce(self):
+        """One ncclAllReduce over the whole [nslots][row] matrix; returns (matrix, reduce_ms)."""
+        import numpy as np
+        n, w = self._job
+        out = np.zeros((n, w), dtype=np.int64)
+        ms = C.c_double()
+        rc = self._lib.kvq_job_allreduce(self._h, out.ctypes.data_as(C.POINTER(C.c_int64)), out.size, C.byref(ms))
+        if rc != 0:
+            self._raise(rc)
+        return out, ms.value
 
     # -- engine.stats / engine.stop (workhorse.c:1205-1244 / 1469-1479) ----------------------
     def stats(self):

@@ -50,7 +50,7 @@ def _worker(rank, world, port, fq_shards, seqs_blob, q):
     flat, layout = multi.pack_counters(cov, np.zeros((len(cov), 6), np.int64), r['stats']['nseqhits'],
                                        r['stats']['nseqbasehits'], r['stats']['readlengths'],
                                        r['stats']['records_parsed'])
-    total = multi.all_reduce_counters(flat, dist)
+    total = multi.host_reduce(flat, dist)
     if rank == 0:
         q.put((total, layout, [tuple(h) for h in r['hits']]))
     else:
@@ -100,3 +100,68 @@ def test_two_rank_counter_reduce(tmp_path):
     for w in whole:
         rl[:len(w['stats']['readlengths'])] += np.asarray(w['stats']['readlengths'], np.int64)
     assert (red['readlengths'] == rl[:len(red['readlengths'])]).all()
+
+
+def test_merge_hits_equals_unsharded_scan(tmp_path):
+    """Files dealt to ranks, every rank scanning its own files as one stream: the merged hit list
+    (global file_pos rebuilt from the inflated file sizes, file order) must be the hit list of the
+    unsharded `findseqs(all files)` in the reference's order.  ADVICE r1, multi.py:44."""
+    from kvarq_b200 import multi, synth
+    from oracle import checker
+    if not checker.available('oracle'):
+        checker.build()
+    g = synth.genome(150000, seed=31)
+    ts = synth.mtbc_templates(g, seed=32)
+    iso = synth.isolate(g, ts, seed=33)
+    files, sizes = [], []
+    for i, n in enumerate((1500, 700, 2200, 900, 1300)):
+        fn = str(tmp_path / ('lane%d.fastq' % i))
+        data = synth.fastq_reads(iso, n, readlen=150, seed=40 + i, first_index=10000 * i).tobytes()
+        open(fn, 'wb').write(data)
+        files.append(fn); sizes.append(len(data))
+    cfg = dict(maxerrors=2, minoverlap=25, minreadlength=25, Amin='.')
+    impl = 'ref' if checker.available('ref') else 'oracle'
+    whole = checker.findseqs(files, ts.seqs(), nthreads=1, impl=impl, **cfg)
+    assert len(whole['hits']) > 30
+    for world in (2, 3):
+        rank_files = [multi.shard_indices(len(files), r, world) for r in range(world)]
+        results = [checker.findseqs([files[i] for i in idx], ts.seqs(), nthreads=1, impl=impl, **cfg) for idx in rank_files]
+        hits, hitseqs = multi.merge_hits(rank_files, results, sizes)
+        assert [tuple(h) for h in hits] == [tuple(h) for h in whole['hits']]
+        assert list(hitseqs) == list(whole['hitseqs'])
+
+
+@pytest.mark.gpu
+def test_engine_job_rows_and_allreduce_single_rank(tmp_path):
+    """The library's reduce entry points on one GPU (world 1: the collective is the identity): the job
+    matrix row of a scan holds that scan's counters; with a 1-rank NCCL communicator kvq_allreduce runs
+    the real ncclAllReduce and must leave the counters unchanged."""
+    from kvarq_b200 import multi, synth
+    from kvarq_b200.engine import Engine
+    g = synth.genome(150000, seed=31)
+    ts = synth.mtbc_templates(g, seed=32)
+    e = Engine(0)
+    e.config(maxerrors=2, minoverlap=25, minreadlength=25, Amin='.')
+    rows = []
+    for k in range(3):
+        fq = synth.fastq_reads(synth.isolate(g, ts, seed=50 + k), 4000, readlen=150, seed=60 + k)
+        r = e.findseqs_mem([fq], ts.seqs(), nplus=ts.nplus)
+        if k == 0:
+            e.job_begin(4)
+        e.job_store(k + 1)
+        rows.append(r)
+    m, _ = e.job_allreduce()
+    cov_total = len(rows[0].coverage)
+    assert not m[0].any()
+    for k, r in enumerate(rows):
+        d = multi.split_job_row(m[k + 1], 2 * ts.nplus, cov_total)
+        assert d['coverage'].tolist() == r.coverage.tolist() and d['mutcount'].tolist() == r.mutcount.tolist()
+        assert tuple(d['nseqhits']) == r['stats']['nseqhits'] and tuple(d['nseqbasehits']) == r['stats']['nseqbasehits']
+        assert tuple(d['readlengths']) == r['stats']['readlengths'] and d['records_parsed'] == 4000
+    e.comm_init(Engine.unique_id(), 0, 1)
+    assert e.comm_info()['world'] == 1 and e.comm_info()['nccl_version'] > 20000
+    r = e.findseqs_mem([fq], ts.seqs(), nplus=ts.nplus)
+    red = e.allreduce()
+    assert red.coverage.tolist() == r.coverage.tolist() and red['stats'] == r['stats']
+    assert red.timing['reduce_ms'] > 0
+    e.close()
