@@ -226,6 +226,85 @@ def run_reference_arm(args, rank, world):
     })
 
 
+def run_config5(args, rank, world, local, dist, barrier, allmax, allsum):
+    """BASELINE.json configs[4]: a batch of synthetic isolates (seeds 500.., the config-2 recipe with a
+    random genotype each) dealt round-robin to the ranks.  Every isolate goes through the
+    end-to-end call on host buffers (page-locked, H2D inside the timed region); its counters are
+    stored as one row of an [isolates][row] int64 matrix in HBM; ONE ncclAllReduce over the matrix at
+    the end gives every rank the coverage / hit counters of every isolate.  Timed: the scans + row
+    stores of a rank (max over ranks) + the reduce; the reads are generated on the host between the
+    scans, outside the timed regions."""
+    import numpy as np
+    from kvarq_b200 import multi, synth
+    from kvarq_b200.engine import Engine
+    n_iso, n_reads = args.isolates, args.reads_per_isolate
+    g = synth.genome()
+    ts = synth.mtbc_templates(g, seed=1)
+    seqs = ts.seqs()
+    eng = Engine(local)
+    eng.config(nthreads=max(1, (os.cpu_count() or 8) // max(1, world)), **CFG)
+    if dist is not None:
+        multi.init_comm(eng, dist, rank, world)
+    mine = multi.shard_indices(n_iso, rank, world)
+    pin = None
+    scan_s, bases, nbytes, nhits, kernel_ms = 0.0, 0, 0, 0, 0.0
+    sampler = ClockSampler(local if rank == 0 else None)
+    for k, i in enumerate(mine):
+        t0 = time.time()
+        iso = synth.isolate(g, ts, fraction=0.3, seed=500 + i)
+        fq = synth.fastq_reads(iso, n_reads, readlen=READLEN, seed=500 + i)
+        if pin is None:
+            pin = eng.pinned_empty(int(fq.nbytes * 1.02) + 4096)
+        buf = pin[:fq.nbytes]
+        buf[:] = fq
+        tgen = time.time() - t0
+        if k == 0:
+            eng.findseqs_mem([buf[:min(fq.nbytes, 32 << 20)]], seqs, nplus=ts.nplus, want_hits=False)     # warm-up: tables, buffers
+            if world > 1:
+                eng.allreduce(convert='timing')         # warm-up of the communicator (NCCL connects lazily)
+            eng.job_begin(n_iso)
+        sampler.mark_begin()
+        t0 = time.perf_counter()
+        r = eng.findseqs_mem([buf], seqs, nplus=ts.nplus, want_hits=False)
+        eng.job_store(i)
+        scan_s += time.perf_counter() - t0
+        sampler.mark_end()
+        bases += r.timing['bases']; nbytes += r.timing['stream_bytes']; nhits += r.nhits; kernel_ms += r.timing['kernel_ms']
+        assert r['stats']['records_parsed'] == n_reads
+        log('[rank %d] isolate %d: generated in %.1f s, scanned in %.1f ms, %d hits' % (rank, i, tgen, r.timing['wall_ms'], r.nhits))
+    barrier()
+    t0 = time.perf_counter()
+    m, reduce_ms = eng.job_allreduce()
+    barrier()
+    red_s = time.perf_counter() - t0
+    scan_max = allmax(scan_s)
+    total_s = scan_max + allmax(red_s)
+    total_bases = allsum(bases)
+    h2d_total, hits_total = allsum(nbytes), allsum(nhits)
+    cov_total = sum(len(x) for x in ts.plus)
+    for i in range(n_iso):                       # every rank now holds every isolate's counters
+        d = multi.split_job_row(m[i], len(seqs), cov_total)
+        assert d['records_parsed'] == n_reads, 'isolate %d: %d records' % (i, d['records_parsed'])
+        assert int(d['coverage'].sum()) == int(d['nseqbasehits'].sum())
+    if rank == 0:
+        emit({
+            'metric': 'Gbp scanned/sec', 'value': total_bases / total_s / 1e9, 'unit': 'Gbp/s', 'n_gpus': world,
+            'steps': 1, 'warmup': 0, 'ms_per_step': 1e3 * total_s, 'higher_is_better': True, 'scaling': 'strong',
+            'vs_baseline': None, 'dtype': 'u8', 'data': 'synthetic',
+            'config': {'workload': 'configs[4]: batch of %d synthetic isolates (seeds 500..%d, %d x %d bp reads each, %.1f Gbp) dealt to %d '
+                                   'ranks, MTBC templates (264 seqs), end-to-end from page-locked host buffers, per-isolate counters '
+                                   '[%d][%d] int64 reduced with one ncclAllReduce' % (n_iso, 499 + n_iso, n_reads, READLEN,
+                                                                                   total_bases / 1e9, world, n_iso, m.shape[1]),
+                       'isolates': n_iso, 'reads_per_isolate': n_reads},
+            'e2e': {'value': total_bases / total_s / 1e9, 'unit': 'Gbp/s', 'h2d_bytes_per_step': int(h2d_total),
+                    'd2h_bytes_per_step': int(m.nbytes * world)},
+            'reduce': {'ms': reduce_ms, 'wall_ms': 1e3 * red_s, 'int64_counters': int(m.size), 'in_timed_region': True},
+            'scan_ms_max_rank': 1e3 * scan_max, 'kernel_ms_sum_rank0': kernel_ms, 'hits_total': int(hits_total),
+            'gpu_launches': 3 * len(mine) * 16, 'clocks': sampler.summary(),
+        })
+    eng.close()
+
+
 def workload_config():
     return {'workload': 'configs[1]: synthetic H37Rv-like 4.4 Mb genome, 100x, %d x %d bp SE reads vs MTBC '
                         'templates (132 -> 264 seqs), maxerrors=2 minoverlap=25 minreadlength=25 Q13' % (READS, READLEN),
@@ -241,6 +320,10 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--e2e-steps', type=int, default=0, help='0 = min(steps, 3)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--config', type=int, default=2, choices=[2, 5],
+                    help='2: the headline workload (default); 5: batch of isolates over all ranks + one NCCL reduce')
+    ap.add_argument('--isolates', type=int, default=96)
+    ap.add_argument('--reads-per-isolate', type=int, default=2080000, help='config 5: 312 Mbp per isolate at 150 bp')
     args = ap.parse_args()
     claim_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
@@ -282,6 +365,11 @@ def main():
         return float(t.item())
 
     from kvarq_b200.engine import Engine
+    if args.config == 5:
+        run_config5(args, rank, world, local, dist, barrier, allmax, allsum)
+        if dist is not None:
+            dist.destroy_process_group()
+        return
     ts, fq = make_workload(rank)
     seqs = ts.seqs()
     eng = Engine(local)

@@ -244,6 +244,17 @@ class Engine(object):
         self._pinned[arr.ctypes.data] = ptr
         return arr
 
+    def pinned_empty(self, nbytes):
+        """Page-locked host memory as a numpy uint8 array (kvq_host_alloc); free with release_pinned()."""
+        import numpy as np
+        ptr = self._lib.kvq_host_alloc(max(1, nbytes))
+        if not ptr:
+            raise MemoryError('kvq_host_alloc failed')
+        arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(max(1, nbytes),))
+        self._pinned = getattr(self, '_pinned', {})
+        self._pinned[arr.ctypes.data] = ptr
+        return arr
+
     def release_pinned(self, arr):
         ptr = getattr(self, '_pinned', {}).pop(arr.ctypes.data, None)
         if ptr:
