@@ -263,6 +263,8 @@ def run_config5(args, rank, world, local, dist, barrier, allmax, allsum):
             if world > 1:
                 eng.allreduce(convert='timing')         # warm-up of the communicator (NCCL connects lazily)
             eng.job_begin(n_iso)
+            if world > 1:
+                eng.job_allreduce()                     # same for a collective of the matrix's size (all zeros still)
         sampler.mark_begin()
         t0 = time.perf_counter()
         r = eng.findseqs_mem([buf], seqs, nplus=ts.nplus, want_hits=False)

@@ -26,6 +26,7 @@
 #include "../../include/kvarq_b200.h"
 #include "kvq_device.h"
 #include "nccl_shim.h"
+#include "gz_parallel.h"
 
 namespace {
 
@@ -303,10 +304,12 @@ struct GzFileSource : Source {
 // side instead of one after the other, and inflate overlaps the cutting of the batches.  What the
 // scan sees is byte for byte what GzFileSource delivers, including the reference's file position
 // after every fill (GzEvent), which feeds the size estimate of engine.stats().
+// With more than one inflate thread per file the stream is decoded chunk-parallel (gz_parallel.h):
+// same bytes, same read positions, several times the rate of one zlib stream.
 class GzAhead : public Source {
 public:
     static constexpr int64_t BLOCK = 4ll << 20, LIMIT = 1ll << 30;      // read-ahead per file
-    explicit GzAhead(const std::string &name) : name_(name) { th_ = std::thread([this] { run(); }); }
+    GzAhead(const std::string &name, int threads) : name_(name), threads_(threads) { th_ = std::thread([this] { run(); }); }
     ~GzAhead() override {
         { std::lock_guard<std::mutex> g(mu_); cancel_ = true; }
         cv_.notify_all();
@@ -326,13 +329,16 @@ public:
                 if (err_) std::rethrow_exception(err_);
                 break;
             }
-            std::vector<char> &bk = blocks_.front();
+            std::vector<uint8_t> &bk = blocks_.front();
             const int64_t m = std::min<int64_t>(cap - got, (int64_t) bk.size() - front_off_);
             g.unlock();
             memcpy(dst + got, bk.data() + front_off_, (size_t) m);
             g.lock();
             got += m; front_off_ += m; buffered_ -= m;
-            if (front_off_ == (int64_t) bk.size()) { blocks_.pop_front(); front_off_ = 0; cv_.notify_all(); }
+            if (front_off_ == (int64_t) bk.size()) {
+                if (spares_.size() < 32) spares_.push_back(std::move(bk));      // its pages are used again by the decoder
+                blocks_.pop_front(); front_off_ = 0; cv_.notify_all();
+            }
         }
         consumed_ += got;
         while (ev_at_ < events_.size() &&
@@ -345,8 +351,52 @@ public:
     int64_t disk_pos() const override { return pos_; }
     bool compressed() const override { return true; }
 private:
+    void run_parallel() {
+        // the whole compressed file in memory (readable 64 bytes past its end), then round after round
+        int fd = open(name_.c_str(), O_RDONLY);
+        struct stat sb;
+        if (fd < 0 || fstat(fd, &sb) != 0) { if (fd >= 0) close(fd); throw KvqError(KVQ_ERR_IO, "cannot open file"); }
+        std::vector<uint8_t> file((size_t) sb.st_size + 64, 0);
+        for (int64_t at = 0; at < (int64_t) sb.st_size;) {
+            const ssize_t m = pread(fd, file.data() + at, (size_t) std::min<int64_t>(8 << 20, (int64_t) sb.st_size - at), (off_t) at);
+            if (m <= 0) { close(fd); throw KvqError(KVQ_ERR_IO, "could not read enough bytes from .fastq.gz"); }
+            at += m;
+        }
+        close(fd);
+        try {
+            kvq_gz::FileDecoder dec(file.data(), (int64_t) sb.st_size, threads_);
+            {
+                std::lock_guard<std::mutex> g(mu_);
+                size_ = (int64_t) sb.st_size; pos_ = dec.disk_pos(); opened_ = true;
+            }
+            cv_.notify_all();
+            std::vector<std::vector<uint8_t>> outs, spares;
+            std::vector<kvq_gz::Event> ev;
+            for (;;) {
+                {
+                    std::unique_lock<std::mutex> g(mu_);
+                    cv_.wait(g, [&] { return buffered_ < LIMIT || cancel_; });
+                    if (cancel_) break;
+                    spares.swap(spares_);
+                }
+                outs.clear(); ev.clear();
+                const bool more = dec.next(outs, ev, &spares);
+                {
+                    std::lock_guard<std::mutex> g(mu_);
+                    for (const kvq_gz::Event &x : ev) events_.push_back(GzEvent{x.out, x.pos, x.at_end});
+                    for (auto &o : outs) if (!o.empty()) { buffered_ += (int64_t) o.size(); blocks_.push_back(std::move(o)); }
+                    if (!more) done_ = true;
+                }
+                cv_.notify_all();
+                if (!more) break;
+            }
+        } catch (const kvq_gz::Error &err) {
+            throw KvqError(err.io ? KVQ_ERR_IO : KVQ_ERR_RUNTIME, err.what());
+        }
+    }
     void run() {
         try {
+            if (threads_ > 1) { run_parallel(); return; }
             GzFileSource src(name_.c_str());
             {
                 std::lock_guard<std::mutex> g(mu_);
@@ -360,9 +410,9 @@ private:
                     cv_.wait(g, [&] { return buffered_ < LIMIT || cancel_; });
                     if (cancel_) break;
                 }
-                std::vector<char> bk((size_t) BLOCK);
+                std::vector<uint8_t> bk((size_t) BLOCK);
                 bool filled = false;
-                const int64_t got = src.fill(bk.data(), BLOCK, &filled);
+                const int64_t got = src.fill((char *) bk.data(), BLOCK, &filled);
                 bk.resize((size_t) got);
                 {
                     std::lock_guard<std::mutex> g(mu_);
@@ -380,10 +430,11 @@ private:
             cv_.notify_all();
         }
     }
-    std::string name_;
+    std::string name_; int threads_ = 1;
     std::thread th_;
     std::mutex mu_; std::condition_variable cv_;
-    std::deque<std::vector<char>> blocks_; int64_t front_off_ = 0, buffered_ = 0, consumed_ = 0;
+    std::deque<std::vector<uint8_t>> blocks_; std::vector<std::vector<uint8_t>> spares_;
+    int64_t front_off_ = 0, buffered_ = 0, consumed_ = 0;
     std::vector<GzEvent> events_; size_t ev_at_ = 0;
     int64_t size_ = 0, pos_ = 0;
     bool opened_ = false, open_failed_ = false, done_ = false, cancel_ = false;
@@ -442,9 +493,14 @@ struct HostBatch {
 class StreamCutter {
 public:
     StreamCutter(std::vector<std::string> names, std::vector<std::pair<const char *, int64_t>> mems,
-                 LiveStats *live, WorkPool *pool = nullptr)
+                 LiveStats *live, WorkPool *pool = nullptr, int inflate_threads = 1)
         : names_(std::move(names)), mems_(std::move(mems)), live_(live), pool_(pool)
     {
+        {   // inflate threads per .gz file: the files of a scan inflate side by side (start_ahead)
+            int ngz = 0;
+            for (auto &nm : names_) ngz += has_gz_suffix(nm);
+            gz_threads_ = std::max(1, inflate_threads / std::max(1, std::min(ngz, (int) AHEAD)));
+        }
         nfiles_ = names_.empty() ? (int) mems_.size() : (int) names_.size();
         // fastq_open (:659-677): total size first, then the first file
         for (int i = 0; i < nfiles_; i++) {
@@ -529,7 +585,7 @@ private:
         const int i = next_file_++;
         if (!names_.empty()) {
             if (has_gz_suffix(names_[i])) {
-                if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i]));
+                if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i], gz_threads_));
                 ahead_[i]->wait_opened();
                 src_ = std::move(ahead_[i]);
                 start_ahead();
@@ -551,7 +607,7 @@ private:
         int running = 0;
         for (size_t i = (size_t) next_file_; i < names_.size() && running < AHEAD; i++) {
             if (!has_gz_suffix(names_[i])) break;                           // (a plain file after .gz is an error anyway)
-            if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i]));
+            if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i], gz_threads_));
             running++;
         }
     }
@@ -560,7 +616,7 @@ private:
     std::vector<std::string> names_;
     std::vector<std::pair<const char *, int64_t>> mems_;
     LiveStats *live_;
-    WorkPool *pool_ = nullptr;
+    WorkPool *pool_ = nullptr; int gz_threads_ = 1;
     int nfiles_ = 0, next_file_ = 0;
     std::unique_ptr<Source> src_;
     bool at_eof_ = false, compressed_ = false, finished_ = false;
@@ -1382,7 +1438,14 @@ kvq_result *run_stream_scan(kvq_engine *e, std::vector<std::string> names,
         want = std::max(1, std::min(want, 64));
         if (!names.empty() && (!e->pool || e->pool_threads != want)) { e->pool.reset(new WorkPool(want - 1)); e->pool_threads = want; }
     }
-    StreamCutter cutter(std::move(names), std::move(mems), &e->live, e->pool.get());
+    int inflate_threads;
+    {   // inflate threads: engine.config(nthreads) when set (> 1), else the machine's cores; KVQ_GZ_THREADS overrides (1: one zlib stream per file)
+        kvq_config_t cfg; { std::lock_guard<std::mutex> g(e->mu); cfg = e->cfg; }
+        inflate_threads = cfg.nthreads > 1 ? cfg.nthreads : (int) std::max(1u, std::thread::hardware_concurrency());
+        if (const char *v = getenv("KVQ_GZ_THREADS")) inflate_threads = atoi(v);
+        inflate_threads = std::max(1, std::min(inflate_threads, 128));
+    }
+    StreamCutter cutter(std::move(names), std::move(mems), &e->live, e->pool.get(), inflate_threads);
     ScanTotals tot;
     Chan<int> free_q, ready_q;
     for (int i = 0; i < NSLOT; i++) free_q.push(i);

@@ -1,0 +1,747 @@
+// Chunk-parallel inflate of one gzip file held in memory (N4: the step in front of the scan).
+//
+// The reference inflates a .gz FastQ with one miniz stream under the reader mutex
+// (csrc/workhorse.c:781-885); round 1 of this engine used one zlib stream per file: 0.26 GB/s of
+// FastQ, two orders of magnitude below what the GPU scans.  A deflate stream has no index, but it
+// can still be decoded by many threads (the idea of pugz / rapidgzip):
+//
+//   1. the compressed bytes are cut into chunks; every thread looks for the first deflate block that
+//      starts in its chunk (bit by bit: a dynamic-Huffman header whose code-length code, literal and
+//      distance codes are all complete, whose block decodes to its end-of-block and is followed by
+//      another valid block header);
+//   2. it decodes from there WITHOUT the 32 KiB of history in front of it: output goes to 16-bit
+//      cells, a back-reference into the unknown history becomes a marker (0x8000 | window offset).
+//      At the first block boundary with 32 KiB of marker-free output behind it the thread hands the
+//      stream to zlib (inflatePrime to the bit position, inflateSetDictionary with those 32 KiB) and
+//      decodes plain bytes at zlib's speed until it lands exactly on the start another thread found;
+//   3. the chunks are chained in stream order (a chunk start nobody lands on was a false positive and
+//      its output is dropped), markers are replaced from the tail of the chunk in front.
+//
+// Nothing is trusted: a chain that does not close, a candidate that fails, any zlib error -> the
+// member is decoded by the sequential reader below, which is the round-1 code on a memory buffer
+// and reproduces the reference byte for byte, including the positions of its 1 MiB compressed
+// reads (GzEvent: they feed the size estimate of engine.stats(), workhorse.c:883-884).
+#pragma once
+#include <stdint.h>
+#include <string.h>
+#include <zlib.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <chrono>
+#include <algorithm>
+#include <atomic>
+#include <functional>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <vector>
+
+namespace kvq_gz {
+
+// File position of the reference's reader as a function of the inflated bytes delivered: `pos`
+// holds from output offset `out` on (at_end: the reposition behind a member's end, which happens in
+// the call that delivers the member's last byte).
+struct Event { int64_t out, pos; bool at_end; };
+
+struct Error : std::runtime_error {
+    bool io;        // IOError of the reference (else RuntimeError)
+    Error(bool io_, const std::string &m) : std::runtime_error(m), io(io_) {}
+};
+
+constexpr int64_t PIECE = 1024 * 1024;      // compressed bytes per read of the reference (SCANBUFSIZE, workhorse.c:15)
+constexpr int WSIZE = 32768;
+
+// ---------------------------------------------------------------------------------- bit access
+struct Bits {
+    const uint8_t *d; int64_t nbits;        // readable bits; d is readable 8 bytes past the end (callers pad)
+    inline uint64_t peek(int64_t pos) const {       // >= 57 valid bits from bit position pos
+        uint64_t v;
+        memcpy(&v, d + (pos >> 3), 8);
+        return v >> (pos & 7);
+    }
+};
+
+// ---------------------------------------------------------------------------------- Huffman codes
+// Canonical decoder: 11-bit direct table for the short codes, count/offset search for longer ones.
+struct Huff {
+    static constexpr int FAST = 11;
+    uint16_t fast[1 << FAST];               // sym << 4 | len, 0 = not a short code
+    uint16_t count[16], symbol[288];
+    int maxlen = 0;
+
+    // returns 0 complete, 1 incomplete, -1 over-subscribed
+    int build(const uint8_t *len, int n)
+    {
+        memset(count, 0, sizeof(count));
+        for (int i = 0; i < n; i++) count[len[i]]++;
+        maxlen = 0;
+        for (int l = 15; l > 0; l--) if (count[l]) { maxlen = l; break; }
+        int left = 1;
+        for (int l = 1; l <= 15; l++) {
+            left <<= 1; left -= count[l];
+            if (left < 0) return -1;
+        }
+        uint16_t offs[16]; offs[1] = 0;
+        for (int l = 1; l < 15; l++) offs[l + 1] = offs[l] + count[l];
+        for (int i = 0; i < n; i++) if (len[i]) symbol[offs[len[i]]++] = (uint16_t) i;
+        memset(fast, 0, sizeof(fast));
+        // canonical codes, bit-reversed into the table
+        int code = 0, idx = 0;
+        for (int l = 1; l <= FAST && l <= maxlen; l++) {
+            for (int k = 0; k < count[l]; k++, idx++, code++) {
+                int rev = 0;
+                for (int b = 0; b < l; b++) rev |= ((code >> b) & 1) << (l - 1 - b);
+                const uint16_t e = (uint16_t) (symbol[idx] << 4 | l);
+                for (int f = rev; f < (1 << FAST); f += 1 << l) fast[f] = e;
+            }
+            code <<= 1;
+        }
+        count[0] = 0;
+        return left > 0 ? 1 : 0;
+    }
+
+    // decodes one symbol from the low bits of v; returns the symbol and its length in `len`, -1 = invalid
+    inline int decode(uint64_t v, int &len) const
+    {
+        const uint16_t e = fast[v & ((1 << FAST) - 1)];
+        if (e) { len = e & 15; return e >> 4; }
+        int code = 0, first = 0, index = 0;
+        for (int l = 1; l <= maxlen; l++) {
+            code |= (int) (v & 1); v >>= 1;
+            const int c = count[l];
+            if (code - c < first) { len = l; return symbol[index + (code - first)]; }
+            index += c; first += c; first <<= 1; code <<= 1;
+        }
+        return -1;
+    }
+};
+
+static const uint16_t LEN_BASE[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
+static const uint8_t LEN_EXTRA[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
+static const uint16_t DIST_BASE[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
+static const uint8_t DIST_EXTRA[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
+
+struct BlockCodes { Huff lit, dist; };
+
+// Header of a dynamic block at bit position pos (behind BFINAL / BTYPE): code lengths -> codes.
+// Strict: every code must be complete (a lone distance code excepted, as zlib allows), 256 must
+// have a code.  Returns the bit position behind the header, -1 if invalid.
+inline int64_t read_dynamic_header(const Bits &b, int64_t pos, BlockCodes &bc)
+{
+    static const uint8_t order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+    if (pos + 14 > b.nbits) return -1;
+    uint64_t v = b.peek(pos);
+    const int nlen = (int) (v & 31) + 257, ndist = (int) ((v >> 5) & 31) + 1, ncode = (int) ((v >> 10) & 15) + 4;
+    pos += 14;
+    if (nlen > 286 || ndist > 30) return -1;
+    if (pos + 3 * ncode > b.nbits) return -1;
+    uint8_t cl[19] = {0};
+    v = b.peek(pos);
+    for (int i = 0; i < ncode; i++) { cl[order[i]] = (uint8_t) (v & 7); v >>= 3; }      // <= 57 bits
+    pos += 3 * ncode;
+    {   // complete code-length code?  (cheap: rejects nearly every wrong bit position of the block search)
+        int kraft = 0;
+        for (int i = 0; i < 19; i++) if (cl[i]) kraft += 128 >> cl[i];
+        if (kraft != 128) return -1;
+    }
+    Huff lencode;
+    if (lencode.build(cl, 19) != 0) return -1;
+    uint8_t lens[320];
+    int idx = 0;
+    while (idx < nlen + ndist) {
+        if (pos + 16 > b.nbits) return -1;
+        v = b.peek(pos);
+        int l;
+        const int sym = lencode.decode(v, l);
+        if (sym < 0) return -1;
+        pos += l; v >>= l;
+        if (sym < 16) lens[idx++] = (uint8_t) sym;
+        else {
+            int prev = 0, rep;
+            if (sym == 16) {
+                if (idx == 0) return -1;
+                prev = lens[idx - 1]; rep = 3 + (int) (v & 3); pos += 2;
+            } else if (sym == 17) { rep = 3 + (int) (v & 7); pos += 3; }
+            else { rep = 11 + (int) (v & 127); pos += 7; }
+            if (idx + rep > nlen + ndist) return -1;
+            while (rep--) lens[idx++] = (uint8_t) prev;
+        }
+    }
+    if (lens[256] == 0) return -1;
+    if (bc.lit.build(lens, nlen) != 0) return -1;
+    const int dr = bc.dist.build(lens + nlen, ndist);
+    if (dr < 0 || (dr > 0 && bc.dist.count[1] + bc.dist.count[2] + bc.dist.count[3] + bc.dist.count[4] + bc.dist.count[5]
+                   + bc.dist.count[6] + bc.dist.count[7] + bc.dist.count[8] + bc.dist.count[9] + bc.dist.count[10]
+                   + bc.dist.count[11] + bc.dist.count[12] + bc.dist.count[13] + bc.dist.count[14] + bc.dist.count[15] > 1))
+        return -1;
+    return pos;
+}
+
+inline void fixed_codes(BlockCodes &bc)
+{
+    uint8_t l[288];
+    for (int i = 0; i < 144; i++) l[i] = 8;
+    for (int i = 144; i < 256; i++) l[i] = 9;
+    for (int i = 256; i < 280; i++) l[i] = 7;
+    for (int i = 280; i < 288; i++) l[i] = 8;
+    bc.lit.build(l, 288);
+    uint8_t d[30];
+    for (int i = 0; i < 30; i++) d[i] = 5;
+    bc.dist.build(d, 30);
+}
+
+// ------------------------------------------------------------------------ decoding without history
+// Output cells: 0..255 a byte, 0x8000 | k the byte at offset k of the (unknown) 32 KiB in front of the chunk.
+struct MarkerOut {
+    std::vector<uint16_t> cells;            // capacity; `n` cells are valid
+    int64_t n = 0;
+    inline void room(int64_t more) { if (n + more > (int64_t) cells.size()) cells.resize((size_t) std::max<int64_t>(2 * (int64_t) cells.size(), n + more + (1 << 20))); }
+};
+
+// crossings of the reference's 1 MiB input pieces: (piece boundary as file byte offset, output produced by then)
+struct Crossing { int64_t boundary, out; };
+
+constexpr int64_t NO_BOUNDARY = INT64_MAX / 16;
+
+struct CrossTracker {
+    int64_t next;                           // next piece boundary (file byte offset) not yet crossed; NO_BOUNDARY: none
+    int64_t step_base;                      // boundaries are step_base + k * PIECE
+    std::vector<Crossing> list;
+    void init(int64_t base, int64_t from_bit, int64_t file_size)
+    {
+        step_base = base;
+        // first boundary b with 8 b >= from_bit (a symbol that ends behind 8 b crosses it)
+        int64_t k = (std::max<int64_t>(0, (from_bit + 7) / 8 - base) + PIECE - 1) / PIECE;
+        if (k == 0) k = 1;                  // the piece that starts at `base` is read before anything is decoded
+        next = base + k * PIECE;
+        if (next >= file_size) next = NO_BOUNDARY;
+        fsize = file_size;
+    }
+    inline void symbol_end(int64_t end_bit, int64_t out_before)
+    {
+        while (end_bit > 8 * next) {
+            list.push_back(Crossing{next, out_before});
+            next += PIECE;
+            if (next >= fsize) next = NO_BOUNDARY;
+        }
+    }
+    int64_t fsize = 0;
+};
+
+// One deflate block at bit position pos (its BFINAL bit) into marker cells.  Returns the bit
+// position behind the block, -1 on invalid data; *final = BFINAL.  max_out bounds the output.
+inline int64_t marker_block(const Bits &b, int64_t pos, MarkerOut &o, CrossTracker &ct, bool *final, int64_t max_out)
+{
+    if (pos + 3 > b.nbits) return -1;
+    uint64_t v = b.peek(pos);
+    *final = v & 1;
+    const int type = (int) ((v >> 1) & 3);
+    pos += 3;
+    if (type == 3) return -1;
+    if (type == 0) {                        // stored
+        pos = (pos + 7) & ~(int64_t) 7;
+        if (pos + 32 > b.nbits) return -1;
+        v = b.peek(pos);
+        const uint32_t len = (uint32_t) (v & 0xFFFF), nlen = (uint32_t) ((v >> 16) & 0xFFFF);
+        if ((len ^ 0xFFFF) != nlen) return -1;
+        pos += 32;
+        if (pos + 8 * (int64_t) len > b.nbits || o.n + len > max_out) return -1;
+        const uint8_t *src = b.d + (pos >> 3);
+        o.room(len);
+        for (uint32_t i = 0; i < len; i++) {
+            ct.symbol_end(pos + 8 * (int64_t) (i + 1), o.n);
+            o.cells[(size_t) o.n++] = src[i];
+        }
+        return pos + 8 * (int64_t) len;
+    }
+    BlockCodes bc;
+    if (type == 1) fixed_codes(bc);
+    else { pos = read_dynamic_header(b, pos, bc); if (pos < 0) return -1; }
+    const int64_t limit_bits = b.nbits - 48;            // (a symbol needs at most 15 + 5 + 15 + 13 bits)
+    for (;;) {
+        o.room(4096);
+        uint16_t *c = o.cells.data();
+        int64_t n = o.n;
+        const int64_t n_stop = std::min<int64_t>((int64_t) o.cells.size() - 300, max_out);
+        const int64_t cross_bit = ct.next >= NO_BOUNDARY ? INT64_MAX : 8 * ct.next;
+        // inner loop: until the output room or the next piece boundary needs attention
+        while (n < n_stop) {
+            if (pos > limit_bits) { o.n = n; return -1; }
+            v = b.peek(pos);
+            int l;
+            int sym = bc.lit.decode(v, l);
+            if (sym < 0) { o.n = n; return -1; }
+            int64_t p = pos + l; v >>= l;
+            if (sym < 256) {
+                if (p > cross_bit) { o.n = n; ct.symbol_end(p, n); pos = p; c[n++] = (uint16_t) sym; break; }
+                c[n++] = (uint16_t) sym;
+                pos = p;
+                // a second literal from the same 57 bits
+                sym = bc.lit.decode(v, l);
+                if (sym >= 0 && sym < 256 && p + l <= cross_bit) { c[n++] = (uint16_t) sym; pos = p + l; }
+                continue;
+            }
+            if (sym == 256) { o.n = n; ct.symbol_end(p, n); return p; }
+            sym -= 257;
+            if (sym >= 29) { o.n = n; return -1; }
+            const int len = LEN_BASE[sym] + (int) (v & ((1u << LEN_EXTRA[sym]) - 1));
+            p += LEN_EXTRA[sym]; v >>= LEN_EXTRA[sym];
+            int dl;
+            const int ds = bc.dist.decode(v, dl);
+            if (ds < 0 || ds >= 30) { o.n = n; return -1; }
+            p += dl; v >>= dl;
+            const int dist = DIST_BASE[ds] + (int) (v & ((1u << DIST_EXTRA[ds]) - 1));
+            p += DIST_EXTRA[ds];
+            if (p > cross_bit) { o.n = n; ct.symbol_end(p, n); }
+            pos = p;
+            int64_t from = n - dist;
+            if (from >= 0) {
+                const uint16_t *src = c + from; uint16_t *dst = c + n;
+                if (dist >= len) memcpy(dst, src, 2 * (size_t) len);
+                else for (int i = 0; i < len; i++) dst[i] = src[i];
+                n += len;
+            } else {
+                if (from < -WSIZE) { o.n = n; return -1; }
+                for (int i = 0; i < len; i++, from++) c[n++] = from < 0 ? (uint16_t) (0x8000 | (WSIZE + from)) : c[from];
+            }
+            if (p > cross_bit) break;
+        }
+        o.n = n;
+        if (n >= max_out) return -1;
+    }
+}
+
+// Is there a block start at bit position pos?  A non-final dynamic block that decodes to its end
+// and is followed by a plausible block header.
+inline bool plausible_block_start(const Bits &b, int64_t pos)
+{
+    if (pos + 17 > b.nbits) return false;
+    const uint64_t v = b.peek(pos);
+    if ((v & 7) != 4) return false;                     // BFINAL = 0, BTYPE = 10b (dynamic)
+    if (((v >> 3) & 31) > 29 || ((v >> 8) & 31) > 29) return false;
+    BlockCodes bc;
+    if (read_dynamic_header(b, pos + 3, bc) < 0) return false;
+    MarkerOut o; CrossTracker ct; ct.next = NO_BOUNDARY; ct.fsize = 0;
+    bool fin;
+    const int64_t end = marker_block(b, pos, o, ct, &fin, 4 << 20);
+    if (end < 0 || o.n < 1024) return false;     // (real blocks of a FastQ hold tens of KB)
+    if (end + 3 > b.nbits) return true;
+    const uint64_t w = b.peek(end);
+    const int type = (int) ((w >> 1) & 3);
+    if (type == 3) return false;
+    if (type == 2) { BlockCodes nb; return read_dynamic_header(b, end + 3, nb) >= 0; }
+    if (type == 0) {
+        const int64_t q = (end + 3 + 7) & ~(int64_t) 7;
+        if (q + 32 > b.nbits) return false;
+        const uint64_t x = b.peek(q);
+        return ((x & 0xFFFF) ^ 0xFFFF) == ((x >> 16) & 0xFFFF);
+    }
+    return true;
+}
+
+inline int64_t find_block_start(const Bits &b, int64_t from_bit, int64_t to_bit)
+{
+    for (int64_t pos = from_bit; pos < to_bit; pos++)
+        if (plausible_block_start(b, pos)) return pos;
+    return -1;
+}
+
+// ------------------------------------------------------------------------------- one chunk
+struct Chunk {
+    int64_t start_bit = -1;                 // where decoding starts (chunk 0: known; others: the block start found)
+    bool ok = false;                        // decoded without an error up to `end_bit`
+    int64_t end_bit = -1;                   // block boundary where it stopped
+    int landed = -1;                        // index of the chunk whose start it stopped on, -1: none
+    bool at_final = false, at_limit = false; // stopped in front of a final block / at the end of the round
+    MarkerOut head;                         // output decoded without history (empty for chunk 0)
+    std::vector<uint8_t> body;              // output decoded by zlib behind it
+    std::vector<Crossing> cross;            // 1 MiB input piece boundaries crossed, `out` counted from the chunk's start
+    int64_t out_size() const { return head.n + (int64_t) body.size(); }
+};
+
+struct RoundCtx {
+    Bits bits; const uint8_t *file; int64_t fsize;
+    int64_t piece_base;                     // file offset where the member's 1 MiB input pieces start
+    int64_t stop_bit;                       // chunks stop at the first block boundary at or behind this
+    const std::vector<Chunk> *chunks;       // (start_bit of every chunk: landing targets)
+};
+
+// stop test at a block boundary; returns true if the chunk ends here
+inline bool chunk_stops_here(const RoundCtx &rc, Chunk &c, int self, int64_t pos)
+{
+    if (pos != c.start_bit)
+        for (size_t j = (size_t) self + 1; j < rc.chunks->size(); j++)
+            if ((*rc.chunks)[j].start_bit == pos) { c.landed = (int) j; return true; }
+    if (pos + 1 > rc.bits.nbits) { c.at_limit = true; return true; }
+    if (rc.bits.peek(pos) & 1) { c.at_final = true; return true; }         // the final block belongs to the sequential reader
+    if (pos >= rc.stop_bit) { c.at_limit = true; return true; }
+    return false;
+}
+
+// known: the history in front of start_bit is `window` (wlen <= 32 KiB bytes; chunk 0); else it is decoded into marker cells
+inline void decode_chunk(const RoundCtx &rc, Chunk &c, int self, bool known, const uint8_t *window, int wlen)
+{
+    c.ok = false;
+    c.body.clear();                         // (keeps the capacity of a recycled buffer)
+    c.head.n = 0;
+    if (c.start_bit < 0) return;
+    CrossTracker ct;
+    ct.init(rc.piece_base, c.start_bit, rc.fsize);
+    int64_t pos = c.start_bit;
+    if (!known) {
+        // ---- without history: the whole chunk into marker cells (in a FastQ the markers never die out --
+        // every header line copies from the one before it -- so there is no point in looking for a clean window)
+        for (;;) {
+            if (chunk_stops_here(rc, c, self, pos)) { c.end_bit = pos; c.cross.swap(ct.list); c.ok = true; return; }
+            bool fin;
+            const int64_t e = marker_block(rc.bits, pos, c.head, ct, &fin, (int64_t) 1 << 31);
+            if (e < 0) return;
+            pos = e;
+        }
+    }
+    std::vector<uint8_t> dict;
+    if (wlen > 0) dict.assign(window, window + wlen);
+    // ---- zlib from the block boundary `pos` with the history in `dict`
+    z_stream zs;
+    memset(&zs, 0, sizeof(zs));
+    if (inflateInit2(&zs, -15) != Z_OK) return;
+    struct Guard { z_stream *z; ~Guard() { inflateEnd(z); } } guard{&zs};
+    int64_t in_at = pos >> 3;                                       // file offset of next_in
+    if (pos & 7) {
+        if (inflatePrime(&zs, 8 - (int) (pos & 7), rc.file[in_at] >> (pos & 7)) != Z_OK) return;
+        in_at++;
+    }
+    if (!dict.empty() && inflateSetDictionary(&zs, dict.data(), (uInt) dict.size()) != Z_OK) return;
+    if (chunk_stops_here(rc, c, self, pos)) { c.end_bit = pos; c.cross.swap(ct.list); c.ok = true; return; }
+    // (ct.next was advanced by the marker phase; a boundary at or in front of in_at cannot be pending:
+    //  the symbol that took the last bits in front of `pos` crossed it)
+    const int64_t head_n = c.head.n;
+    size_t used = 0;
+    c.body.resize(std::max<size_t>(c.body.capacity(), 8u << 20));
+    zs.next_in = const_cast<Bytef *>(rc.file + in_at);
+    for (;;) {
+        const int64_t lim = std::min<int64_t>(ct.next == NO_BOUNDARY ? rc.fsize : ct.next, rc.fsize);
+        zs.avail_in = (uInt) std::min<int64_t>(lim - in_at, 1 << 30);
+        if (c.body.size() - used < (1u << 20)) c.body.resize(c.body.size() * 2);
+        zs.next_out = c.body.data() + used;
+        zs.avail_out = (uInt) std::min<size_t>(c.body.size() - used, 1u << 30);
+        const uInt in0 = zs.avail_in, out0 = zs.avail_out;
+        const int st = inflate(&zs, Z_BLOCK);
+        in_at += in0 - zs.avail_in; used += out0 - zs.avail_out;
+        if (st != Z_OK && st != Z_BUF_ERROR) { c.body.clear(); return; }    // (Z_STREAM_END cannot happen: final blocks are not entered)
+        if ((zs.data_type & 128) && !(zs.data_type & 64)) {         // at a block boundary
+            pos = 8 * in_at - (zs.data_type & 63);
+            if (chunk_stops_here(rc, c, self, pos)) break;
+        }
+        if (zs.avail_in == 0 && in_at == lim) {
+            if (ct.next != NO_BOUNDARY && in_at == ct.next) {         // the input piece is used up: everything it can give is out
+                ct.list.push_back(Crossing{ct.next, head_n + (int64_t) used});
+                ct.next += PIECE;
+                if (ct.next >= rc.fsize) ct.next = NO_BOUNDARY;
+            } else if (in_at >= rc.fsize) { c.body.clear(); return; }      // ran off the file without reaching a stop
+        } else if (st == Z_BUF_ERROR && zs.avail_out != 0 && zs.avail_in != 0) { c.body.clear(); return; }
+    }
+    c.body.resize(used);
+    c.end_bit = pos;
+    c.cross.swap(ct.list);
+    c.ok = true;
+}
+
+// ------------------------------------------------------------------------------- the file reader
+// One .gz file in memory -> its inflated bytes and the reference's read positions, in order.
+// The sequential part restates the round-1 GzFileSource (engine.cpp) on a memory buffer; parallel
+// rounds run inside a member between block boundaries and leave the sequential state exactly where
+// the reference's reader would be.
+class FileDecoder {
+public:
+    // `file` must stay valid and be readable 16 bytes past `size`
+    FileDecoder(const uint8_t *file, int64_t size, int nthreads)
+        : f_(file), size_(size), threads_(std::max(1, nthreads))
+    {
+        memset(&zs_, 0, sizeof(zs_));
+        if (inflateInit2(&zs_, -15) != Z_OK) throw Error(false, "cannot mz_inflateInit()");
+        live_ = true;
+        remaining_ = size_;
+        const char *msg = skip_header(rd_, 0);
+        if (msg) throw Error(true, std::string("no valid gzip header found at beginning of file : ") + msg);
+        remaining_ -= rd_;
+        member_start(rd_);
+    }
+    ~FileDecoder() { if (live_) inflateEnd(&zs_); }
+    FileDecoder(const FileDecoder &) = delete;
+    FileDecoder &operator=(const FileDecoder &) = delete;
+
+    int64_t disk_pos() const { return rd_; }
+    int64_t produced() const { return produced_; }
+    int64_t parallel_bytes() const { return par_bytes_; }      // inflated bytes that came out of parallel rounds
+
+    // Appends the next stretch of output (one or more buffers) and the read events that fall into it.
+    // Returns false when the stream has ended (nothing appended).
+    // `spares`: buffers handed out earlier that the caller is done with (their pages are reused:
+    // fresh pages cost more than the decoding).
+    bool next(std::vector<std::vector<uint8_t>> &outs, std::vector<Event> &ev, std::vector<std::vector<uint8_t>> *spares = nullptr)
+    {
+        if (spares) { for (auto &b : *spares) if (spare_.size() < 64) spare_.push_back(std::move(b)); spares->clear(); }
+        if (done_) return false;
+        if (par_ok_ && threads_ > 1) {
+            if (parallel_round(outs, ev)) return true;
+            par_ok_ = false;
+            handover(par_bit_);                     // the sequential reader takes the member from here
+        }
+        std::vector<uint8_t> buf = take_spare((size_t) 4 << 20);
+        bool filled = false;
+        const int64_t got = fill(buf.data(), (int64_t) buf.size(), &filled, ev);
+        buf.resize((size_t) got);
+        if (got) outs.push_back(std::move(buf));
+        if (!filled) done_ = true;
+        return got > 0 || !done_;
+    }
+
+private:
+    // ---- gzip member header on memory (skip_gz_header, workhorse.c:482-541; fgetc at EOF does not advance)
+    const char *skip_header(int64_t &p, int dist) const
+    {
+        auto get = [&]() -> int { return p < size_ ? (int) f_[p++] : -1; };
+        int state = 0, junk = 0, c = get();
+        while (state != 2 && junk <= dist && c != -1) {
+            if (state == 0 && c == 0x1F) state = 1;
+            else if (state == 1 && c == 0x8B) state = 2;
+            else { state = 0; junk++; }
+            c = get();
+        }
+        if (state != 2) return "magic bytes not found";
+        if (c != 8) return "expected method==DEFLATED";
+        const int flags = get();
+        if (flags & (0x02 | 0x20 | 0xC0)) return "unsupported flags (CONTINUATION or ENCRYPTED or RESERVED)";
+        for (int i = 0; i < 6; i++) (void) get();
+        if (flags & 0x04) { int n = get(); n |= get() << 8; while (n-- > 0) (void) get(); }
+        if (flags & 0x08) { do c = get(); while (c > 0); }
+        if (flags & 0x10) { do c = get(); while (c > 0); }
+        return nullptr;
+    }
+
+    void member_start(int64_t data_at)
+    {
+        piece_base_ = data_at;
+        member_out0_ = produced_;
+        par_ok_ = true; par_bit_ = 8 * data_at; window_.clear();
+    }
+
+    // ---- the reference's reader (workhorse.c:781-885), zlib instead of miniz
+    int64_t fill(uint8_t *dst, int64_t cap, bool *filled, std::vector<Event> &ev)
+    {
+        int64_t got = 0;
+        bool at_member = false;
+        zs_.next_out = dst; zs_.avail_out = (uInt) cap;
+        do {
+            if (zs_.avail_in == 0) {
+                const int64_t m = std::min<int64_t>(PIECE, remaining_);
+                if (rd_ + m > size_) throw Error(true, "could not read enough bytes from .fastq.gz");
+                zs_.next_in = const_cast<Bytef *>(f_ + rd_); zs_.avail_in = (uInt) m;
+                rd_ += m; remaining_ -= m;
+                ev.push_back(Event{produced_ + got, rd_, false});
+            }
+            const uInt before = zs_.avail_out;
+            int st = inflate(&zs_, Z_SYNC_FLUSH);
+            if (st == Z_BUF_ERROR && zs_.avail_out == 0) st = Z_OK;
+            if (st != Z_OK && st != Z_STREAM_END)
+                throw Error(true, "error while inflating compressed data : status=" + std::to_string(st));
+            got += before - zs_.avail_out;
+            if (st == Z_STREAM_END && remaining_ + zs_.avail_in > 10) {
+                // another member may follow after <= 10 junk bytes (:842-866)
+                rd_ -= zs_.avail_in; remaining_ += zs_.avail_in;
+                const int64_t pos = rd_;
+                if (skip_header(rd_, 10) != nullptr) {
+                    remaining_ = 0; zs_.avail_in = 0;
+                    ev.push_back(Event{produced_ + got, rd_, true});
+                    par_ok_ = false;
+                    break;
+                }
+                remaining_ -= rd_ - pos;
+                inflateReset2(&zs_, -15);
+                zs_.avail_in = 0;
+                ev.push_back(Event{produced_ + got, rd_, true});
+                produced_ += got;               // (member_start reads produced_)
+                member_start(rd_);
+                produced_ -= got;
+                at_member = true;               // hand the new member to a parallel round: nothing of it is read yet
+                break;
+            } else if (st == Z_STREAM_END) {
+                break;
+            }
+        } while (remaining_ + zs_.avail_in > 10 && zs_.avail_out > 0);
+        *filled = at_member || (zs_.avail_out == 0);
+        produced_ += got;
+        return got;
+    }
+
+    // sequential reader := "at block boundary `bit` with the history window_, input pieces read up to rd_"
+    void handover(int64_t bit)
+    {
+        inflateReset2(&zs_, -15);
+        int64_t nb = bit >> 3;
+        if (bit & 7) { inflatePrime(&zs_, 8 - (int) (bit & 7), f_[nb] >> (bit & 7)); nb++; }
+        if (!window_.empty()) inflateSetDictionary(&zs_, window_.data(), (uInt) window_.size());
+        if (rd_ < nb) rd_ = nb;                 // (cannot happen: every byte taken lies in a piece already read)
+        zs_.next_in = const_cast<Bytef *>(f_ + nb);
+        zs_.avail_in = (uInt) (rd_ - nb);
+        remaining_ = size_ - rd_;
+    }
+
+    bool parallel_round(std::vector<std::vector<uint8_t>> &outs, std::vector<Event> &ev);
+
+    std::vector<uint8_t> take_spare(size_t n)       // a buffer of n bytes, from the spares when one is large enough
+    {
+        size_t best = spare_.size();
+        for (size_t i = 0; i < spare_.size(); i++)
+            if (spare_[i].capacity() >= n && (best == spare_.size() || spare_[i].capacity() < spare_[best].capacity())) best = i;
+        std::vector<uint8_t> b;
+        if (best < spare_.size()) { b.swap(spare_[best]); spare_.erase(spare_.begin() + (long) best); }
+        b.resize(n);
+        return b;
+    }
+    std::vector<std::vector<uint8_t>> spare_;
+    std::vector<std::vector<uint16_t>> cells_pool_;
+
+    const uint8_t *f_; int64_t size_; int threads_;
+    z_stream zs_; bool live_ = false;
+    int64_t rd_ = 0, remaining_ = 0, produced_ = 0, piece_base_ = 0, member_out0_ = 0, par_bytes_ = 0;
+    bool done_ = false, par_ok_ = false;
+    int64_t par_bit_ = 0; std::vector<uint8_t> window_;
+};
+
+inline bool FileDecoder::parallel_round(std::vector<std::vector<uint8_t>> &outs, std::vector<Event> &ev)
+{
+    constexpr int64_t CHUNK = 2 << 20;              // compressed bytes per chunk
+    const int64_t sb = par_bit_ >> 3;
+    if (size_ - sb < 3 * CHUNK) return false;       // not worth a round: the sequential reader finishes the file
+    const int T = (int) std::min<int64_t>(threads_, (size_ - sb) / CHUNK);
+    std::vector<Chunk> chunks((size_t) T);
+    RoundCtx rc;
+    rc.bits = Bits{f_, 8 * size_}; rc.file = f_; rc.fsize = size_; rc.piece_base = piece_base_;
+    rc.stop_bit = 8 * std::min<int64_t>(size_, sb + (int64_t) T * CHUNK);
+    rc.chunks = &chunks;
+    chunks[0].start_bit = par_bit_;
+    if ((int) cells_pool_.size() < T) cells_pool_.resize((size_t) T);
+    for (int i = 1; i < T; i++) chunks[(size_t) i].head.cells.swap(cells_pool_[(size_t) i]);
+    chunks[0].body = take_spare((size_t) 10 << 20);
+    struct GiveBack {                               // the cell buffers go back to the pool whatever happens
+        std::vector<Chunk> &ch; std::vector<std::vector<uint16_t>> &pool; int T;
+        ~GiveBack() { for (int i = 1; i < T; i++) if (ch[(size_t) i].head.cells.capacity() > pool[(size_t) i].capacity()) ch[(size_t) i].head.cells.swap(pool[(size_t) i]); }
+    } give_back{chunks, cells_pool_, T};
+    auto in_threads = [&](int n, const std::function<void(int)> &fn) {
+        std::vector<std::thread> th;
+        std::atomic<int> failed{0};
+        for (int i = 1; i < n; i++) th.emplace_back([&, i] { try { fn(i); } catch (...) { failed++; } });
+        try { fn(0); } catch (...) { failed++; }
+        for (auto &t : th) t.join();
+        return failed.load() == 0;
+    };
+    const bool trace = getenv("KVQ_GZ_TRACE") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
+    // phase 0: the first block that starts in every chunk (looked for in the chunk's first quarter: deflate
+    // blocks of text are tens of KB; data without such blocks -- stored, incompressible -- is not worth a round)
+    in_threads(T, [&](int i) {
+        if (i > 0) chunks[(size_t) i].start_bit = find_block_start(rc.bits, 8 * (sb + (int64_t) i * CHUNK),
+                                                                   std::min<int64_t>(8 * (sb + (int64_t) i * CHUNK + CHUNK / 4), 8 * size_ - 64));
+    });
+    int found = 0;
+    for (int i = 1; i < T; i++) found += chunks[(size_t) i].start_bit >= 0;
+    if (2 * found < T - 1) return false;
+    const double t1 = now();
+    // phase 1: every chunk from its start to the next start it lands on
+    const bool known0 = true;                       // chunk 0 starts at a known boundary with the history in window_ (empty at a member's start)
+    in_threads(T, [&](int i) {
+        try { decode_chunk(rc, chunks[(size_t) i], i, i == 0 && known0, window_.data(), (int) window_.size()); }
+        catch (...) { chunks[(size_t) i].ok = false; }
+    });
+    const double t2 = now();
+    // phase 2a: chain the chunks in stream order (a start nobody lands on was a false positive); the 32 KiB in
+    // front of every chunk of the chain from the resolved tail of the one before it
+    std::vector<int> order;
+    bool broken = false;
+    for (int i = 0; i >= 0; i = chunks[(size_t) i].landed) {
+        if (!chunks[(size_t) i].ok) { broken = true; break; }
+        order.push_back(i);
+    }
+    std::vector<std::vector<uint8_t>> wins(order.size() + 1);
+    wins[0] = window_;
+    for (size_t k = 0; k < order.size(); k++) {
+        Chunk &c = chunks[(size_t) order[k]];
+        const std::vector<uint8_t> &w = wins[k];
+        std::vector<uint8_t> &t = wins[k + 1];
+        const int64_t need_head = std::min<int64_t>(c.head.n, std::max<int64_t>(0, WSIZE - (int64_t) c.body.size()));
+        const int64_t need_prev = std::max<int64_t>(0, WSIZE - (int64_t) c.body.size() - c.head.n);
+        if (need_prev > 0) t.assign(w.end() - std::min<int64_t>(need_prev, (int64_t) w.size()), w.end());
+        const int64_t have = (int64_t) w.size();
+        for (int64_t q = c.head.n - need_head; q < c.head.n && !broken; q++) {
+            const uint16_t x = c.head.cells[(size_t) q];
+            if (x & 0x8000) {
+                const int64_t wi = (int64_t) (x & 0x7FFF) - (WSIZE - have);
+                if (wi < 0) broken = true; else t.push_back(w[(size_t) wi]);
+            } else t.push_back((uint8_t) x);
+        }
+        if (broken) { order.resize(k); break; }      // (reaches in front of the member: not a valid stream; zlib will say so)
+        const size_t nb = std::min<size_t>(c.body.size(), (size_t) WSIZE);
+        t.insert(t.end(), c.body.end() - nb, c.body.end());
+    }
+    // phase 2b: markers -> bytes, every chunk of the chain on its own thread
+    std::vector<std::vector<uint8_t>> heads(order.size());
+    for (size_t k = 0; k < order.size(); k++)
+        if (chunks[(size_t) order[k]].head.n) heads[k] = take_spare((size_t) chunks[(size_t) order[k]].head.n);
+    std::atomic<int> bad{0};
+    in_threads((int) order.size(), [&](int k) {
+        Chunk &c = chunks[(size_t) order[(size_t) k]];
+        if (c.head.n == 0) return;
+        const std::vector<uint8_t> &w = wins[(size_t) k];
+        const int64_t have = (int64_t) w.size();
+        std::vector<uint8_t> &hb = heads[(size_t) k];
+        const uint16_t *cells = c.head.cells.data();
+        for (int64_t q = 0; q < c.head.n; q++) {
+            const uint16_t x = cells[q];
+            if (x & 0x8000) {
+                const int64_t wi = (int64_t) (x & 0x7FFF) - (WSIZE - have);
+                if (wi < 0) { bad++; return; }
+                hb[(size_t) q] = w[(size_t) wi];
+            } else hb[(size_t) q] = (uint8_t) x;
+        }
+    });
+    const double t3 = now();
+    if (trace) {
+        fprintf(stderr, "[gz] round at byte %ld: search %.1f ms, decode %.1f ms, resolve %.1f ms, chain %zu of %d;", (long) sb, t1 - t0, t2 - t1, t3 - t2, order.size(), T);
+        for (int i = 0; i < T; i++)
+            fprintf(stderr, " [%d: +%ld ok=%d head=%ld body=%zu land=%d]", i, (long) (chunks[(size_t) i].start_bit / 8 - sb - (int64_t) i * CHUNK),
+                    chunks[(size_t) i].ok, (long) chunks[(size_t) i].head.n, chunks[(size_t) i].body.size(), chunks[(size_t) i].landed);
+        fprintf(stderr, "\n");
+    }
+    if (bad.load() || order.empty()) return false;
+    int64_t round_out = 0;
+    for (int i : order) round_out += chunks[(size_t) i].out_size();
+    if (round_out == 0) return false;               // (a final block right at the start)
+    // phase 2c: hand the buffers out in stream order, with the reads of input pieces they stand for
+    if (par_bit_ == 8 * piece_base_ && rd_ == piece_base_) {        // the member's first input piece is read before anything comes out
+        rd_ = std::min(size_, piece_base_ + PIECE);
+        ev.push_back(Event{produced_, rd_, false});
+    }
+    int64_t at = 0;
+    for (size_t k = 0; k < order.size(); k++) {
+        Chunk &c = chunks[(size_t) order[k]];
+        for (const Crossing &x : c.cross) {
+            rd_ = std::min(size_, x.boundary + PIECE);
+            ev.push_back(Event{produced_ + at + x.out, rd_, false});
+        }
+        at += c.out_size();
+        if (!heads[k].empty()) outs.push_back(std::move(heads[k]));
+        if (!c.body.empty()) outs.push_back(std::move(c.body));
+    }
+    // the sequential state follows: block boundary end_bit, history = tail of the chain
+    produced_ += round_out; par_bytes_ += round_out;
+    par_bit_ = chunks[(size_t) order.back()].end_bit;
+    window_.swap(wins[order.size()]);
+    if (broken) par_ok_ = false;                    // what the chain has is good; the rest of the member goes sequentially
+    if (!par_ok_) handover(par_bit_);
+    return true;
+}
+
+} // namespace kvq_gz

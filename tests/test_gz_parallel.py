@@ -1,0 +1,82 @@
+"""Chunk-parallel inflate (kvarq_b200/csrc/gz_parallel.h, N4) on the CPU: the bytes and the read
+positions (GzEvent: they feed the reference's size estimate, csrc/workhorse.c:883-884) of a parallel
+decode must equal those of the sequential reader -- the round-1 code path, which the GPU tests pin
+to the reference -- and the bytes must equal zlib's, for single- and multi-member files, every
+compression level, stored blocks, incompressible stretches, truncated and tiny files."""
+import gzip
+import os
+import subprocess
+import zlib
+
+import numpy as np
+import pytest
+
+from kvarq_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope='module')
+def harness(tmp_path_factory):
+    d = tmp_path_factory.mktemp('gzh')
+    exe = str(d / 'gz_harness')
+    subprocess.run(['g++', '-O2', '-std=c++17', '-o', exe, os.path.join(ROOT, 'tests', 'gz_harness.cpp'), '-lz', '-lpthread'],
+                   check=True)
+    return exe
+
+
+def run(exe, threads, fn, out):
+    p = subprocess.run([exe, str(threads), fn, out], capture_output=True, text=True, check=True)
+    par = int(p.stderr.strip().split()[-1])
+    return open(out, 'rb').read(), p.stdout, par
+
+
+def inflate_members(blob):
+    """All members of a gzip file, trailing junk ignored (what the reference reads)."""
+    out = []
+    while blob:
+        d = zlib.decompressobj(31)
+        try:
+            out.append(d.decompress(blob))
+        except zlib.error:
+            break
+        if not d.eof:
+            break
+        blob = d.unused_data
+        k = blob.find(b'\x1f\x8b')
+        if k < 0 or k > 10:
+            break
+        blob = blob[k:]
+    return b''.join(out)
+
+
+def test_parallel_equals_sequential(harness, tmp_path):
+    g = synth.genome(500000, seed=3)
+    fq = synth.fastq_reads(g, 90000, readlen=250, seed=5, qmean0=37.0, qdrop=20.0).tobytes()    # ~47 MB
+    rnd = np.random.default_rng(1).integers(0, 256, 9000000, dtype=np.uint8).tobytes()
+    cut = fq.index(b'\n@SYN', len(fq) // 3) + 1
+    cases = {
+        'level6': gzip.compress(fq, 6),
+        'level1': gzip.compress(fq, 1),
+        'level9': gzip.compress(fq[:len(fq) // 2], 9),
+        'members': gzip.compress(fq[:cut], 6) + gzip.compress(b'', 6) + gzip.compress(fq[cut:], 6) + b'junk',
+        'stored': gzip.compress(fq[:20000000], 0),
+        'mixed': gzip.compress(rnd + fq[:30000000] + rnd[:3000000], 6),
+        'truncated': gzip.compress(fq, 6)[:-2000000],
+        'small': gzip.compress(fq[:2000000], 6),
+        'empty': gzip.compress(b'', 6),
+    }
+    used_parallel = 0
+    for name, blob in cases.items():
+        fn = str(tmp_path / (name + '.fastq.gz'))
+        open(fn, 'wb').write(blob)
+        seq, ev_seq, _ = run(harness, 1, fn, str(tmp_path / 'seq.bin'))
+        par, ev_par, nb = run(harness, 4, fn, str(tmp_path / 'par.bin'))
+        assert par == seq, name + ': bytes differ'
+        assert ev_par == ev_seq, name + ': read events differ'
+        assert 'ERROR' not in ev_seq, name       # (a truncated stream just ends, as in the reference: workhorse.c:885)
+        assert seq == inflate_members(blob), name + ': sequential reader differs from zlib'
+        used_parallel += nb > 0
+        if name in ('level6', 'level1', 'level9', 'members'):
+            assert nb > 0.4 * len(seq), name + ': the parallel path was not taken'
+    assert used_parallel >= 5

@@ -158,3 +158,41 @@ def test_config2_shape_200k_reads(checker, tmp_path):
         want2 = oracle(checker, fn2, seqs, DEFAULT, impl='ref', nthreads=1)
         assert_same_result(got2, want2, what='config 2, 20k-read prefix vs the reference C')
     e.close()
+
+
+# ------------------------------------------------------------- chunk-parallel inflate (N4) ------
+def test_large_gz_parallel_inflate(checker, tmp_path, monkeypatch):
+    """.gz inputs large enough for parallel inflate rounds (kvarq_b200/csrc/gz_parallel.h): single
+    member and three members + trailing junk, two files side by side.  Hits, hitseqs and stats -- the
+    single-precision size estimate included, which follows the reference's 1 MiB compressed reads
+    (csrc/workhorse.c:883-884) -- against the CPU checker; and identical with one zlib stream per file."""
+    import gzip
+    from kvarq_b200.engine import Engine
+    g = synth.genome(300000, seed=81)
+    ts = synth.mtbc_templates(g, seed=82, n_phylo=6, n_res=10, regions=(3, 81), n_spacers=5)
+    iso = synth.isolate(g, ts, seed=83)
+    seqs = ts.seqs()
+    fq1 = synth.fastq_reads(iso, 110000, readlen=250, seed=84, qmean0=37.0, qdrop=20.0).tobytes()
+    fq2 = synth.fastq_reads(iso, 70000, readlen=150, seed=85, mate=2).tobytes()
+    f1 = str(tmp_path / 'big_1.fastq.gz')
+    open(f1, 'wb').write(gzip.compress(fq1, 6))
+    cut = [fq2.index(b'\n@SYN', int(len(fq2) * x)) + 1 for x in (0.3, 0.31)]
+    f2 = str(tmp_path / 'big_2.fastq.gz')
+    open(f2, 'wb').write(gzip.compress(fq2[:cut[0]], 6) + gzip.compress(fq2[cut[0]:cut[1]], 1) + gzip.compress(fq2[cut[1]:], 9) + b'tail')
+    assert os.path.getsize(f1) > (12 << 20)
+    e = Engine(0)
+    e.config(nthreads=8, **DEFAULT)
+    want = oracle(checker, [f1, f2], seqs, DEFAULT, impl='oracle', nthreads=os.cpu_count() or 8)
+    assert want['stats']['records_parsed'] == 180000 and len(want['hits']) > 300
+    got = e.findseqs([f1, f2], seqs, nplus=ts.nplus)
+    assert_same_result(got, want, what='parallel inflate')
+    monkeypatch.setenv('KVQ_GZ_THREADS', '1')
+    one = e.findseqs([f1, f2], seqs, nplus=ts.nplus)
+    assert_same_result(one, want, what='one zlib stream per file')
+    if checker.available('ref'):
+        small = str(tmp_path / 'ref_1.fastq.gz')
+        open(small, 'wb').write(gzip.compress(fq1[:fq1.index(b'\n@SYN', 30 << 20) + 1], 6))
+        monkeypatch.delenv('KVQ_GZ_THREADS')
+        got = e.findseqs(small, seqs[:8])
+        assert_same_result(got, oracle(checker, small, seqs[:8], DEFAULT, impl='ref'), what='parallel inflate vs the reference C')
+    e.close()
