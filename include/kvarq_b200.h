@@ -169,6 +169,21 @@ int64_t kvq_job_row_words(kvq_engine *e);
 int kvq_job_store(kvq_engine *e, int slot, const kvq_result *r);
 int kvq_job_allreduce(kvq_engine *e, int64_t *out, int64_t cap_words, double *reduce_ms);
 
+/* ---- ordering hits without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops).  Puts `nhits` hits (device memory, any order) into the reference's nthreads=1 emission order
+ * (file order, template, rules (a) (b) shifts descending, (c)/(d) ascending): d_sorted[r] = the hit of
+ * rank r, d_order[r] (may be NULL) = its index in d_hits -- use it to gather the hitseqs.  d_seqlens[nseqs]
+ * = template lengths (device memory).  One kernel on `stream` (a cudaStream_t, NULL = default stream),
+ * not synchronised; a single-block variant of the kernels behind kvq_scan_staged whose scratch is a
+ * file-scope device array of 2 MiB that every GPU loading the library holds until exit.  At most
+ * KVQ_ORDER_STATIC_MAX hits (more: KVQ_ERR_TYPE, message via kvq_static_last_error).  Calls no
+ * cudaMalloc / cudaFree.  All calls share the scratch: calls that overlap on the GPU race. */
+#define KVQ_ORDER_STATIC_MAX 65536
+int kvq_order_hits_static(int device, const kvq_hit_t *d_hits, int64_t nhits, const int32_t *d_seqlens,
+                          int32_t nseqs, kvq_hit_t *d_sorted, uint32_t *d_order, void *stream);
+const char *kvq_static_last_error(void);
+
 /* build/device info, "sm_100a" etc. */
 const char *kvq_version(void);
 int kvq_device_count(void);

@@ -78,11 +78,31 @@ SIGNATURES = {
     'kvq_job_row_words': (C.c_int64, [VP]),
     'kvq_job_store': (C.c_int, [VP, C.c_int, VP]),
     'kvq_job_allreduce': (C.c_int, [VP, P(C.c_int64), C.c_int64, P(C.c_double)]),
+    'kvq_order_hits_static': (C.c_int, [C.c_int, VP, C.c_int64, VP, C.c_int32, VP, VP, VP]),
+    'kvq_static_last_error': (C.c_char_p, []),
     'kvq_version': (C.c_char_p, []),
     'kvq_device_count': (C.c_int, []),
 }
 
 _lib = None
+
+
+def _pick_nccl():
+    """The library binds NCCL at run time (csrc/nccl_shim.h).  A process can only hold one libnccl.so.2
+    (the loader matches by SONAME), so when PyTorch's bundled copy is installed that is the one to load
+    -- whichever of the two libraries comes first -- unless $KVQ_NCCL_LIB says otherwise."""
+    if os.environ.get('KVQ_NCCL_LIB'):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec('nvidia.nccl')
+        for d in (spec.submodule_search_locations if spec else []):
+            path = os.path.join(d, 'lib', 'libnccl.so.2')
+            if os.path.exists(path):
+                os.environ['KVQ_NCCL_LIB'] = path
+                return
+    except Exception:
+        pass
 
 
 def load():
@@ -92,6 +112,7 @@ def load():
         if not os.path.exists(LIB_PATH):
             raise ImportError('%s is missing: build it with `make -C kvarq_b200/csrc` '
                               '(or __graft_entry__.build()); there is no fallback' % LIB_PATH)
+        _pick_nccl()
         lib = C.CDLL(LIB_PATH)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)     # AttributeError = library does not match the header

@@ -1579,3 +1579,159 @@ int kvq_launch_order(const KvqBatch &b, const KvqOut &o, const KvqOrder &ord, vo
     kvq_order_copy<<<296, 256, 0, st>>>(o, ord);
     return (int) cudaGetLastError();
 }
+
+// ---- hit ordering without any allocation (kvq_order_hits_static, include/kvarq_b200.h) ----------
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc (CUDA graph capture, tight serving loops).  A single-block variant of the
+// kvq_order_* kernels above: same bucket sort over the stream position, same rank-by-full-key
+// inside the (tiny) buckets, but its scratch -- keys, bucket numbers, bucket starts, cursors, member
+// lists -- lives in ONE file-scope device array of fixed size instead of cudaMalloc'ed buffers, and
+// the rule tag of a hit (which the public kvq_hit_t does not carry) is derived from the tuple and the
+// template length.  Every GPU that loads the library holds the array (2 MiB) until exit; all calls
+// share it, so calls that overlap on the GPU race (serialise them on one stream).
+#include <mutex>
+#include <string>
+#include "../../include/kvarq_b200.h"
+
+namespace {
+
+struct OrderScratch {
+    ulonglong2 keys[KVQ_ORDER_STATIC_MAX];
+    uint32_t bkt[KVQ_ORDER_STATIC_MAX];             // bucket | flush-right flag << 31
+    uint32_t start[KVQ_ORDER_STATIC_MAX + 1];
+    uint32_t cursor[KVQ_ORDER_STATIC_MAX + 1];
+    uint32_t members[KVQ_ORDER_STATIC_MAX];
+};
+
+static __device__ __align__(256) unsigned char g_order_scratch[sizeof(OrderScratch)];
+
+__device__ __forceinline__ unsigned long long order_key_y(int seq_nr, int rule, int seq_pos)
+{
+    const int sh = rule == 0 ? seq_pos : rule == 1 ? -seq_pos : (seq_pos < 0 ? -seq_pos : seq_pos);
+    return ((unsigned long long) (uint32_t) seq_nr << 34) | ((unsigned long long) (uint32_t) rule << 32)
+         | (unsigned long long) (uint32_t) (sh + (1 << 30));
+}
+
+// one block of 1024 threads; `sc` is the device address of g_order_scratch
+__global__ void __launch_bounds__(1024)
+kvq_order_static_kernel(OrderScratch *sc, const KvqHitOut *hits, uint32_t n, const int32_t *seqlens, int32_t nseqs,
+                        KvqHitOut *sorted, uint32_t *order)
+{
+    __shared__ unsigned long long lo_s, hi_s;
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) { lo_s = ~0ULL; hi_s = 0ULL; }
+    for (uint32_t i = tid; i <= n; i += 1024) sc->start[i] = 0;      // the scratch keeps the last call's contents
+    __syncthreads();
+    unsigned long long lo = ~0ULL, hi = 0ULL;
+    for (uint32_t i = tid; i < n; i += 1024) {
+        const unsigned long long f = (unsigned long long) hits[i].file_pos;
+        lo = f < lo ? f : lo; hi = f > hi ? f : hi;
+    }
+    if (lo != ~0ULL) { atomicMin(&lo_s, lo); atomicMax(&hi_s, hi); }
+    __syncthreads();
+    lo = lo_s; hi = hi_s;
+    // keys and buckets.  Rule of a hit (workhorse.c:1112-1174) from its tuple: seq_pos < 0: template
+    // inside the read (c) when the whole template matched, else read tail on template head (a);
+    // seq_pos > 0: read inside the template (d) when the whole read matched, else read head on
+    // template tail (b).  A flush-right (d) hit may be one of the reference's two identical copies
+    // (rules b + d): flagged, settled below.
+    for (uint32_t i = tid; i < n; i += 1024) {
+        const KvqHitOut h = hits[i];
+        const int sl = (h.seq_nr >= 0 && h.seq_nr < nseqs) ? seqlens[h.seq_nr] : 0;
+        int rule = 2; uint32_t flag = 0;
+        if (h.seq_pos < 0) rule = h.length == sl ? 2 : 0;
+        else if (h.seq_pos > 0) {
+            rule = h.length == h.readlength ? 2 : 1;
+            flag = (rule == 2 && h.seq_pos + h.readlength == sl) ? 0x80000000u : 0u;
+        }
+        ulonglong2 k; k.x = (unsigned long long) h.file_pos; k.y = order_key_y(h.seq_nr, rule, h.seq_pos);
+        sc->keys[i] = k;
+        unsigned long long bk = (k.x - lo) * n / (hi - lo + 1);
+        if (bk >= n) bk = n - 1;
+        sc->bkt[i] = (uint32_t) bk | flag;
+        atomicAdd(&sc->start[bk + 1], 1u);
+    }
+    __syncthreads();
+    if (n) block_scan(sc->start, sc->cursor, n);
+    __syncthreads();
+    for (uint32_t i = tid; i < n; i += 1024) sc->members[atomicAdd(&sc->cursor[sc->bkt[i] & 0x7FFFFFFFu], 1u)] = i;
+    __syncthreads();
+    // the two copies of a flush-right duplicate: the first is the reference's rule (b) hit, the second its rule (d) hit
+    for (uint32_t i = tid; i < n; i += 1024) {
+        if (!(sc->bkt[i] & 0x80000000u)) continue;
+        const uint32_t bk = sc->bkt[i] & 0x7FFFFFFFu;
+        const KvqHitOut me = hits[i];
+        uint32_t same = 0, before = 0;
+        for (uint32_t m = sc->start[bk]; m < sc->start[bk + 1]; m++) {
+            const uint32_t j = sc->members[m];
+            const KvqHitOut o = hits[j];
+            if (o.file_pos == me.file_pos && o.seq_nr == me.seq_nr && o.seq_pos == me.seq_pos && o.length == me.length) {
+                same++; before += j < i;
+            }
+        }
+        if (same >= 2 && (before & 1u) == 0) sc->keys[i].y = order_key_y(me.seq_nr, 1, me.seq_pos);
+    }
+    __syncthreads();
+    for (uint32_t i = tid; i < n; i += 1024) {
+        const uint32_t bk = sc->bkt[i] & 0x7FFFFFFFu;
+        const ulonglong2 me = sc->keys[i];
+        uint32_t r = sc->start[bk];
+        for (uint32_t m = sc->start[bk]; m < sc->start[bk + 1]; m++) {
+            const uint32_t j = sc->members[m];
+            if (j != i && key_before(sc->keys[j], j, me, i)) r++;
+        }
+        sorted[r] = hits[i];
+        if (order) order[r] = i;
+    }
+}
+
+std::mutex g_static_mu;
+OrderScratch *g_static_ptr[64];                     // device address of g_order_scratch, per device
+thread_local std::string g_static_err;
+
+} // namespace
+
+extern "C" const char *kvq_static_last_error(void) { return g_static_err.c_str(); }
+
+extern "C" int kvq_order_hits_static(int device, const kvq_hit_t *d_hits, int64_t nhits, const int32_t *d_seqlens,
+                                     int32_t nseqs, kvq_hit_t *d_sorted, uint32_t *d_order, void *stream)
+{
+    static_assert(sizeof(KvqHitOut) == sizeof(kvq_hit_t), "device hit layout == kvq_hit_t");
+    g_static_err.clear();
+    if (nhits < 0 || nhits > KVQ_ORDER_STATIC_MAX) {
+        g_static_err = "kvq_order_hits_static: " + std::to_string((long long) nhits) + " hits, the static scratch takes at most "
+                     + std::to_string(KVQ_ORDER_STATIC_MAX) + " (KVQ_ORDER_STATIC_MAX)";
+        return KVQ_ERR_TYPE;
+    }
+    if (device < 0 || device >= 64 || (nhits > 0 && (!d_hits || !d_sorted || !d_seqlens)) || nseqs < 0) {
+        g_static_err = "kvq_order_hits_static: bad arguments";
+        return KVQ_ERR_TYPE;
+    }
+    if (nhits == 0) return KVQ_OK;
+    int prev = -1;
+    cudaError_t e = cudaGetDevice(&prev);
+    if (e == cudaSuccess && prev != device) e = cudaSetDevice(device);
+    OrderScratch *sc = nullptr;
+    if (e == cudaSuccess) {
+        // the array's name is a host-side stand-in, not a device address: ask for the address once per
+        // device, with that device current
+        std::lock_guard<std::mutex> g(g_static_mu);
+        if (!g_static_ptr[device]) {
+            void *p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_order_scratch);
+            if (e == cudaSuccess) g_static_ptr[device] = static_cast<OrderScratch *>(p);
+        }
+        sc = g_static_ptr[device];
+    }
+    if (e == cudaSuccess) {
+        kvq_order_static_kernel<<<1, 1024, 0, (cudaStream_t) stream>>>(sc, reinterpret_cast<const KvqHitOut *>(d_hits), (uint32_t) nhits,
+                                                                      d_seqlens, nseqs, reinterpret_cast<KvqHitOut *>(d_sorted), d_order);
+        e = cudaGetLastError();
+    }
+    if (prev >= 0 && prev != device) cudaSetDevice(prev);
+    if (e != cudaSuccess) {
+        g_static_err = std::string("kvq_order_hits_static: CUDA failure: ") + cudaGetErrorString(e);
+        return KVQ_ERR_RUNTIME;
+    }
+    return KVQ_OK;
+}
