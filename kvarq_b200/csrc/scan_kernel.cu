@@ -58,7 +58,7 @@ constexpr int SEEDQ = 2 * DRAIN;
 struct WarpSmem {
     uint32_t ge[NWORDS + 1];                // quality plane, bit j of word w <=> byte 32 w + j is >= Amin
     alignas(16) uint32_t pk[2 * NWORDS + 4]; // code plane: 2 bits per byte, contiguous stream (read as uint2)
-    uint16_t nlpos[NLCAP];                  // positions of the newlines ranked [base, base + NLCAP)
+    uint16_t nlpos[NLCAP + 2];              // positions of the newlines ranked [base, base + NLCAP); [NLCAP]: spare slot (store_two)
     uint32_t rd[32];                        // reads of the round: start | length << 16 (0 = none)
     uint32_t seedq[SEEDQ];
     uint32_t qn;                            // seeds reserved on the stack (may exceed SEEDQ until drained)
@@ -252,10 +252,14 @@ __device__ __forceinline__ uint32_t reduce_row(WarpSmem &s, const TileCtx &t, co
 // none or one, "\n+\n" gives two); what is left stays in `nl`
 __device__ __forceinline__ void store_two(WarpSmem &s, uint32_t &nl, uint32_t rank, int wb)
 {
-    if (nl && rank < NLCAP) s.nlpos[rank] = (uint16_t) (wb + 31 - __clz(nl & (0u - nl)));
-    nl &= nl - 1;
-    if (nl && rank + 1 < NLCAP) s.nlpos[rank + 1] = (uint16_t) (wb + 31 - __clz(nl & (0u - nl)));
-    nl &= nl - 1;
+    // unconditional stores (no divergent branches): what has no newline, or no room, lands in the
+    // spare slot behind the list
+    const uint32_t l0 = nl & (0u - nl);
+    s.nlpos[(nl != 0u && rank < NLCAP) ? rank : NLCAP] = (uint16_t) (wb + 31 - __clz(l0));
+    nl ^= l0;
+    const uint32_t l1 = nl & (0u - nl);
+    s.nlpos[(nl != 0u && rank + 1 < NLCAP) ? rank + 1 : NLCAP] = (uint16_t) (wb + 31 - __clz(l1));
+    nl ^= l1;
 }
 
 // Newline masks of three rows (one word per lane and row) -> ranks and positions.  One shuffle
