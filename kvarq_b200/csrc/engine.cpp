@@ -991,6 +991,9 @@ struct kvq_result {
     kvq_stats_t stats{};
     std::vector<int64_t> nseqhits, nseqbasehits, coverage, mutcount;
     kvq_timing_t timing{};
+    // HBM-resident scans hand the ordered hits out where the DMA put them: page-locked memory the result owns
+    // (v_n >= 0: the accessors return these views instead of the vectors above)
+    PinBuf pin; const kvq_hit_t *v_hits = nullptr; const int64_t *v_off = nullptr; const char *v_blob = nullptr; int64_t v_n = -1;
 };
 
 namespace {
@@ -1066,7 +1069,6 @@ struct kvq_staged {
     DevBuf d_data, d_seg, d_ctr, d_hits, d_blob, d_longs, d_surv; size_t surv_cap = 0;
     TileBufs tiles;
     size_t hit_cap = 0, blob_cap = 0, long_cap = 0;
-    size_t last_hits = 0, last_blob = 0;            // result sizes of the previous scan of this stream
     // hits put into the reference's order on the device (KvqOrder)
     DevBuf o_keys, o_bkt, o_start, o_cursor, o_members, o_lens, o_src, o_hits, o_offsets, o_blob, o_status;
     int64_t nbytes = 0, base_fpos = 0, parsed = 0, total = 0; int nseg = 0;
@@ -1114,6 +1116,8 @@ struct ScanTotals {
     size_t spec_hits = 0, spec_blob = 0; // hit records / hitseq bytes already in e->pin_out (copied behind the kernels)
     // hits already in the reference's order (ordered on the device): page-locked staging, see kvq_scan_staged
     const KvqHitOut *s_hits = nullptr; const long long *s_off = nullptr; const char *s_blob = nullptr; size_t s_n = 0, s_nb = 0;
+    kvq_result *pre = nullptr;          // result taken before the scan: its page-locked buffer is the target of the ordered-hit copies
+    ~ScanTotals() { if (pre) kvq_result_free(pre); }
     ScanTotals() { memset(rls, 0, sizeof(rls)); }
 };
 
@@ -1332,7 +1336,8 @@ void fill_stats(kvq_engine *e, kvq_stats_t &st, const int64_t *rls, int64_t long
 kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
 {
     const double t_fin = now_ms();
-    std::unique_ptr<kvq_result> r(take_result());
+    std::unique_ptr<kvq_result> r(tot.pre ? tot.pre : take_result());
+    tot.pre = nullptr;
     // reference emission order: sort 24-byte keys, not the records
     const size_t nh = tot.hits.size();
     typedef HitKey Key;
@@ -1372,7 +1377,11 @@ kvq_result *finish_result(kvq_engine *e, ScanTotals &tot, double wall_ms)
     }
     const double t_sorted = now_ms();
     static_assert(sizeof(KvqHitOut) == sizeof(kvq_hit_t) && sizeof(kvq_hit_t) == 24, "device hit layout == kvq_hit_t");
-    if (tot.s_hits) {                   // ordered on the device: three plain copies
+    if (tot.s_hits && r->pin.p && (const char *) tot.s_hits >= r->pin.as<char>() && (const char *) tot.s_hits < r->pin.as<char>() + r->pin.cap) {
+        // ordered on the device and copied into the result's own page-locked buffer: nothing to move
+        r->v_hits = reinterpret_cast<const kvq_hit_t *>(tot.s_hits); r->v_off = reinterpret_cast<const int64_t *>(tot.s_off);
+        r->v_blob = tot.s_blob; r->v_n = (int64_t) tot.s_n;
+    } else if (tot.s_hits) {            // ordered on the device: three plain copies
         r->hits.resize(tot.s_n); r->offsets.resize(tot.s_n + 1); r->blob.resize(tot.s_nb);
         if (tot.s_n) memcpy(r->hits.data(), tot.s_hits, tot.s_n * sizeof(kvq_hit_t));
         memcpy(r->offsets.data(), tot.s_off, (tot.s_n + 1) * sizeof(int64_t));
@@ -1628,10 +1637,10 @@ int kvq_findseqs_mem(kvq_engine *e, const char *const *bufs, const int64_t *bufl
     return scan_entry(e, {}, std::move(mems), seqs, seqlens, nseqs, nplus, out);
 }
 
-int64_t kvq_result_nhits(const kvq_result *r) { return r ? (int64_t) r->hits.size() : 0; }
-const kvq_hit_t *kvq_result_hits(const kvq_result *r) { return r ? r->hits.data() : nullptr; }
-const char *kvq_result_hitseq_blob(const kvq_result *r) { return r ? r->blob.data() : nullptr; }
-const int64_t *kvq_result_hitseq_offsets(const kvq_result *r) { return r ? r->offsets.data() : nullptr; }
+int64_t kvq_result_nhits(const kvq_result *r) { return !r ? 0 : r->v_n >= 0 ? r->v_n : (int64_t) r->hits.size(); }
+const kvq_hit_t *kvq_result_hits(const kvq_result *r) { return !r ? nullptr : r->v_n >= 0 ? r->v_hits : r->hits.data(); }
+const char *kvq_result_hitseq_blob(const kvq_result *r) { return !r ? nullptr : r->v_n >= 0 ? r->v_blob : r->blob.data(); }
+const int64_t *kvq_result_hitseq_offsets(const kvq_result *r) { return !r ? nullptr : r->v_n >= 0 ? r->v_off : r->offsets.data(); }
 const kvq_stats_t *kvq_result_stats(const kvq_result *r) { return r ? &r->stats : nullptr; }
 const int64_t *kvq_result_nseqhits(const kvq_result *r) { return r ? r->nseqhits.data() : nullptr; }
 const int64_t *kvq_result_nseqbasehits(const kvq_result *r) { return r ? r->nseqbasehits.data() : nullptr; }
@@ -1655,6 +1664,7 @@ void kvq_result_free(kvq_result *r)
             r->hits.clear(); r->blob.clear(); r->offsets.clear();
             r->nseqhits.clear(); r->nseqbasehits.clear(); r->coverage.clear(); r->mutcount.clear();
             r->stats = kvq_stats_t{}; r->timing = kvq_timing_t{};
+            r->v_n = -1; r->v_hits = nullptr; r->v_off = nullptr; r->v_blob = nullptr;
             g_spare = r;
             return;
         }
@@ -1782,45 +1792,33 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
             e->pin_acc.ensure(words * 8);
             CK(cudaMemcpyAsync(e->pin_acc.p, e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost, s0.stream));
         }
-        // the hits are put into the reference's order on the device (KvqOrder) and ride behind the
-        // kernels too: as many as the previous scan of this stream had (+25 %)
+        // the hits are put into the reference's order on the device (KvqOrder); a last kernel exports the
+        // ordered records, the hitseq offsets and the hitseq bytes into the result's page-locked host buffer
+        // (mapped into the device's address space under unified addressing) with wide coalesced stores:
+        // exactly the bytes of this scan cross PCIe, no staging copy, nothing sized by an earlier scan
         static const bool host_order = getenv("KVQ_HOST_ORDER") != nullptr;
         const bool dev_order = want_hits && !host_order && st->nbytes > 0;
         KvqOrder ord{};
-        size_t oh = 0, oo = 0, ob = 0;          // staging layout: hits | offsets | blob
-        auto fetch_ordered = [&](size_t nh, size_t nb) {
-            oh = 0; oo = (nh * sizeof(KvqHitOut) + 255) & ~(size_t) 255; ob = oo + (((nh + 1) * 8 + 255) & ~(size_t) 255);
-            e->pin_out.ensure(ob + nb + 256);
-            char *pin = e->pin_out.as<char>();
-            if (nh) CK(cudaMemcpyAsync(pin + oh, ord.hits, nh * sizeof(KvqHitOut), cudaMemcpyDeviceToHost, s0.stream));
-            CK(cudaMemcpyAsync(pin + oo, ord.offsets, (nh + 1) * 8, cudaMemcpyDeviceToHost, s0.stream));
-            if (nb) CK(cudaMemcpyAsync(pin + ob, ord.blob, nb, cudaMemcpyDeviceToHost, s0.stream));
-        };
+        size_t oh = 0, oo = 0, ob = 0;          // layout of the result's buffer: hits | offsets | blob
         if (dev_order) {
+            tot.pre = take_result();
             const size_t cap = std::min<size_t>(st->hit_cap, KVQ_ORDER_MAX);
+            oh = 0; oo = (cap * sizeof(KvqHitOut) + 255) & ~(size_t) 255; ob = oo + (((cap + 1) * 8 + 255) & ~(size_t) 255);
+            tot.pre->pin.ensure(ob + st->blob_cap + 256);
+            char *pin = tot.pre->pin.as<char>();
             st->o_keys.ensure(cap * 16); st->o_bkt.ensure(cap * 4); st->o_start.ensure((cap + 1) * 4); st->o_cursor.ensure((cap + 1) * 4);
-            st->o_members.ensure(cap * 4); st->o_lens.ensure((cap + 1) * 4); st->o_src.ensure(cap * 8); st->o_hits.ensure(cap * sizeof(KvqHitOut));
-            st->o_offsets.ensure((cap + 1) * 8); st->o_blob.ensure(st->blob_cap); st->o_status.ensure(16);
+            st->o_members.ensure(cap * 4); st->o_lens.ensure((cap + 1) * 4); st->o_src.ensure(cap * 8); st->o_status.ensure(16);
+            st->o_hits.ensure(cap * sizeof(KvqHitOut) + 16); st->o_offsets.ensure((cap + 1) * 8 + 16); st->o_blob.ensure(st->blob_cap + 16);
             ord.keys = st->o_keys.as<ulonglong2>(); ord.bkt = st->o_bkt.as<uint32_t>(); ord.start = st->o_start.as<uint32_t>();
             ord.cursor = st->o_cursor.as<uint32_t>(); ord.members = st->o_members.as<uint32_t>(); ord.lens = st->o_lens.as<uint32_t>();
-            ord.src = st->o_src.as<unsigned long long>(); ord.hits = st->o_hits.as<KvqHitOut>(); ord.offsets = st->o_offsets.as<long long>();
-            ord.blob = st->o_blob.as<uint8_t>(); ord.status = st->o_status.as<uint32_t>();
+            ord.src = st->o_src.as<unsigned long long>(); ord.status = st->o_status.as<uint32_t>();
+            ord.hits = st->o_hits.as<KvqHitOut>(); ord.offsets = st->o_offsets.as<long long>(); ord.blob = st->o_blob.as<uint8_t>();
+            ord.out_hits = reinterpret_cast<KvqHitOut *>(pin + oh); ord.out_offsets = reinterpret_cast<long long *>(pin + oo);
+            ord.out_blob = reinterpret_cast<uint8_t *>(pin + ob);
             ord.cap = (uint32_t) cap; ord.blob_cap = st->blob_cap; ord.span = st->nbytes;
             cuda_check((cudaError_t) kvq_launch_order(b, o, ord, s0.stream), "order kernels launch");
             e->pin_ord.ensure(16);
             CK(cudaMemcpyAsync(e->pin_ord.p, ord.status, 4, cudaMemcpyDeviceToHost, s0.stream));
-            if (st->last_hits) {
-                tot.spec_hits = std::min(cap, st->last_hits + st->last_hits / 4 + 64);
-                tot.spec_blob = std::min(st->blob_cap, st->last_blob + st->last_blob / 4 + 4096);
-                fetch_ordered(tot.spec_hits, tot.spec_blob);
-            }
-        } else if (want_hits && st->last_hits) {
-            tot.spec_hits = std::min(st->hit_cap, st->last_hits + st->last_hits / 4 + 64);
-            tot.spec_blob = std::min(st->blob_cap, st->last_blob + st->last_blob / 4 + 4096);
-            const size_t hb = (tot.spec_hits * sizeof(KvqHitRec) + 255) & ~(size_t) 255;
-            e->pin_out.ensure(hb + tot.spec_blob + 256);
-            CK(cudaMemcpyAsync(e->pin_out.p, st->d_hits.p, tot.spec_hits * sizeof(KvqHitRec), cudaMemcpyDeviceToHost, s0.stream));
-            CK(cudaMemcpyAsync(e->pin_out.as<char>() + hb, st->d_blob.p, tot.spec_blob, cudaMemcpyDeviceToHost, s0.stream));
         }
         mark();
         CK(cudaStreamSynchronize(s0.stream));
@@ -1837,19 +1835,13 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
                               && *e->pin_ord.as<uint32_t>() == (uint32_t) c.hit_count && c.hit_count <= ord.cap && c.hit_count > 0;
             if (ordered) {
                 const size_t nh = (size_t) c.hit_count, nb = (size_t) c.blob_used;
-                if (!(nh <= tot.spec_hits && nb <= tot.spec_blob && st->last_hits)) {
-                    fetch_ordered(nh, nb);
-                    CK(cudaStreamSynchronize(s0.stream));
-                }
-                const char *pin = e->pin_out.as<char>();
+                const char *pin = tot.pre->pin.as<char>();
                 tot.s_hits = reinterpret_cast<const KvqHitOut *>(pin + oh); tot.s_off = reinterpret_cast<const long long *>(pin + oo);
                 tot.s_blob = pin + ob; tot.s_n = nh; tot.s_nb = nb;
-                tot.launches += 6; tot.d2h += (int64_t) (nh * sizeof(KvqHitOut) + (nh + 1) * 8 + nb + 4);
+                tot.launches += 7; tot.d2h += (int64_t) (nh * sizeof(KvqHitOut) + (nh + 1) * 8 + nb + 4);
             } else {
-                if (dev_order) tot.spec_hits = tot.spec_blob = 0;       // the staging holds ordered arrays, not raw records
                 collect_hits(e, b, bufs_of(*st), used, c, s0.stream, tot);
             }
-            st->last_hits = (size_t) c.hit_count; st->last_blob = (size_t) c.blob_used;
         }
         mark();
         if (tot.err_key != ~0ULL) throw KvqError(KVQ_ERR_FASTQ_FORMAT, format_error_message(tot.err_key));

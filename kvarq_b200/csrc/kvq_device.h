@@ -182,6 +182,9 @@ struct KvqOrder {
     KvqHitOut *hits;                    // [cap] by rank
     long long *offsets;                 // [cap + 1] by rank
     uint8_t *blob;                      // [blob_cap] hitseqs by rank
+    // page-locked host memory (mapped under unified addressing): the three arrays above are exported there by one
+    // kernel with wide coalesced stores -- exactly the bytes of this scan, no copy sized on the host
+    KvqHitOut *out_hits; long long *out_offsets; uint8_t *out_blob;
     uint32_t *status;                   // [0] number of ordered hits, 0xFFFFFFFF = not ordered (overflow, re-run pending, too many)
     uint32_t cap; uint32_t pad;
     unsigned long long blob_cap;

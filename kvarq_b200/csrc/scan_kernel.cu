@@ -1471,40 +1471,41 @@ kvq_order_count(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqO
 }
 
 // one block of 1024 threads: x[0 .. n] -> inclusive prefix sums in place (x[0] stays), copy to y
-// when given.  Tiles of 1024 elements, coalesced; warp scans by shuffles, one carry between tiles.
+// when given.  Every thread takes a contiguous run of ceil((n + 1) / 1024) elements (sum, one block
+// scan over the 1024 run totals, prefix written back): three barriers whatever n is.
 __device__ __forceinline__ void block_scan(uint32_t *x, uint32_t *y, uint32_t n)
 {
     __shared__ uint32_t wsum[32];
-    __shared__ uint32_t carry_s;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    uint32_t carry = 0;
-    for (uint32_t base = 0; base <= n; base += 1024) {
-        const uint32_t i = base + threadIdx.x;
-        const uint32_t v = i <= n ? x[i] : 0u;
-        uint32_t inc = v;
+    const uint32_t per = (n + 1 + 1023) / 1024;
+    const uint32_t lo = threadIdx.x * per, hi = min(lo + per, n + 1);
+    uint32_t sum = 0;
+    for (uint32_t i = lo; i < hi; i++) sum += x[i];
+    uint32_t inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += u;
+    }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t w = wsum[lane], winc = w;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t u = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += u;
+            const uint32_t u = __shfl_up_sync(0xffffffffu, winc, d);
+            if (lane >= d) winc += u;
         }
-        if (lane == 31) wsum[wid] = inc;
-        __syncthreads();
-        if (wid == 0) {
-            uint32_t w = wsum[lane], winc = w;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t u = __shfl_up_sync(0xffffffffu, winc, d);
-                if (lane >= d) winc += u;
-            }
-            wsum[lane] = winc - w;                  // exclusive prefix of the warp totals
-            if (lane == 31) carry_s = winc;         // tile total
-        }
-        __syncthreads();
-        const uint32_t r = carry + wsum[wid] + inc;
-        if (i <= n) { x[i] = r; if (y) y[i] = r; }
-        carry += carry_s;
-        __syncthreads();
+        wsum[lane] = winc - w;                      // exclusive prefix of the warp totals
     }
+    __syncthreads();
+    uint32_t run = wsum[wid] + inc - sum;           // everything in front of this thread's run
+    for (uint32_t i = lo; i < hi; i++) {
+        run += x[i];
+        x[i] = run;
+        if (y) y[i] = run;
+    }
+    __syncthreads();
 }
 
 __global__ void __launch_bounds__(1024)
@@ -1569,6 +1570,28 @@ kvq_order_copy(const __grid_constant__ KvqOut o, const __grid_constant__ KvqOrde
 
 } // namespace
 
+namespace {
+
+__device__ __forceinline__ void export16(void *dst, const void *src, size_t nbytes, size_t tid, size_t nthreads)
+{
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst);
+    for (size_t i = tid; i < (nbytes + 15) / 16; i += nthreads) d4[i] = s4[i];       // (both buffers are padded to 16 bytes)
+}
+
+__global__ void __launch_bounds__(256)
+kvq_order_export(const __grid_constant__ KvqOut o, const __grid_constant__ KvqOrder ord)
+{
+    const uint32_t n = order_n(o, ord);
+    if (!n) return;
+    const size_t tid = (size_t) blockIdx.x * blockDim.x + threadIdx.x, nt = (size_t) gridDim.x * blockDim.x;
+    export16(ord.out_hits, ord.hits, (size_t) n * sizeof(KvqHitOut), tid, nt);
+    export16(ord.out_offsets, ord.offsets, ((size_t) n + 1) * 8, tid, nt);
+    export16(ord.out_blob, ord.blob, (size_t) ord.lens[n], tid, nt);
+}
+
+} // namespace
+
 int kvq_launch_order(const KvqBatch &b, const KvqOut &o, const KvqOrder &ord, void *stream)
 {
     cudaStream_t st = (cudaStream_t) stream;
@@ -1581,6 +1604,7 @@ int kvq_launch_order(const KvqBatch &b, const KvqOut &o, const KvqOrder &ord, vo
     kvq_order_rank<<<g, 256, 0, st>>>(o, ord);
     kvq_order_scan_lens<<<1, 1024, 0, st>>>(o, ord);
     kvq_order_copy<<<296, 256, 0, st>>>(o, ord);
+    if (ord.out_hits) kvq_order_export<<<148, 256, 0, st>>>(o, ord);
     return (int) cudaGetLastError();
 }
 
