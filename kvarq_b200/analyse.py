@@ -318,14 +318,24 @@ class Analyser(object):
     def __len__(self):
         return len(self.coverages)
 
-    def __getitem__(self, thing):
-        return self.coverage_at(thing) if type(thing) == int else self.coverages[str(thing)]
+    def __getitem__(self, thing):                                       # :310-323: int, Test, or name
+        if type(thing) == int:
+            return self.coverage_at(thing)
+        if hasattr(thing, 'template'):
+            return self.coverages[str(thing.template)]
+        return self.coverages[str(thing)]
 
     def scan(self, fastq, templates, do_reverse=True, engine=None, fused=True):        # :325-364
         import time
         if engine is None:
             from . import engine as _e
             engine = _e._engine()
+        if templates and all(hasattr(v, 'tests') for v in templates.values()):
+            # testsuites instead of bare templates (the reference's signature): load_coverages, :260-282
+            from . import genes
+            self.testsuites = templates
+            self.testsuite_versions = dict((name, ts.version) for name, ts in templates.items())
+            templates = genes.template_sequences(templates, self.spacing)
         self.fastq = fastq
         self.fastq_filenames = fastq.filenames()
         self.fastq_sizes = fastq.filesizes()
@@ -349,6 +359,14 @@ class Analyser(object):
                 self.coverages[name] = c
         else:
             self.update_coverages()
+
+    def update_testsuites(self):                                        # :384-395
+        self.results = {}
+        for name, testsuite in (getattr(self, 'testsuites', None) or {}).items():
+            try:
+                self.results[name] = testsuite.analyse(self)
+            except Exception as e:
+                self.results[name] = 'ERROR : ' + str(e)
 
     def update_coverages(self):                                         # :367-381
         assert self.hits is not None, 'cannot update coverages without .hits'

@@ -156,3 +156,41 @@ def count_bases(fastq):
     n = (len(nl) // 4) * 4
     nl = nl[:n].reshape(-1, 4)
     return int((nl[:, 1] - nl[:, 0] - 1).sum())
+
+
+# ------------------------------------------------------ the MTBC suites at their real positions
+def mtbc_genome(seed=GENOME_SEED):
+    """Synthetic stand-in for the MTB ancestor genome the reference does not ship:
+    the i.i.d. genome with the ORIGINAL base forced at every resistance-SNP position
+    (testsuites/MTBC/resistance.py:136-193) and a base other than the mutant at every phylogenetic
+    SNP position (phylo.py:132-162), so that the assertions of SNP.__init__ (kvarq/genes.py:491-495)
+    hold.  Positions are 1-based."""
+    from . import testsuite_data as D
+    g = genome(seed=seed)
+    for pos, orig, _, _ in D.RESISTANCE_SNPS:
+        g[pos - 1] = ord(orig)
+    for pos, base, _ in D.PHYLO_SNPS:
+        if g[pos - 1] == ord(base):
+            g[pos - 1] = [b for b in b'ACGT' if b != ord(base)][pos % 3]
+    return g
+
+
+def plant(g, mutations):
+    """isolate = genome with (1-based position, base) substitutions"""
+    h = g.copy()
+    for pos, base in mutations:
+        h[pos - 1] = ord(base) if isinstance(base, str) else base
+    return h
+
+
+def reads_around(g, sites, per_site=60, readlen=150, seed=3, **kw):
+    """FastQ of reads that overlap the given (1-based start, length) sites of genome g: `per_site` reads per
+    site, starts uniform over every position where the read still touches the site."""
+    rng = np.random.default_rng(seed)
+    starts = []
+    for pos, length in sites:
+        lo, hi = max(0, pos - 1 - readlen + 8), min(len(g) - readlen, pos - 1 + length - 8)
+        starts.append(rng.integers(lo, max(lo + 1, hi), size=per_site))
+    starts = np.concatenate(starts)
+    rng.shuffle(starts)
+    return fastq_reads(g, len(starts), readlen=readlen, seed=seed + 1, starts=starts, **kw)
