@@ -7,6 +7,8 @@
 #include <fcntl.h>
 #include <unistd.h>
 #include <sys/stat.h>
+#include <sys/mman.h>
+#include <set>
 #include <functional>
 #include <stdint.h>
 #include <stdio.h>
@@ -306,10 +308,34 @@ struct GzFileSource : Source {
 // after every fill (GzEvent), which feeds the size estimate of engine.stats().
 // With more than one inflate thread per file the stream is decoded chunk-parallel (gz_parallel.h):
 // same bytes, same read positions, several times the rate of one zlib stream.
+// One chunk-parallel round at a time, the earliest file of the list first: the file being scanned has all the
+// inflate threads, and the next one takes them over as soon as that file is done or has its read-ahead full.
+// (Side by side with half the threads each, the second mate of a pair is finished long before the scan gets to
+// it, and what remains then -- copying it out of the read-ahead -- runs on one thread with the others idle.)
+struct GzGate {
+    std::mutex mu; std::condition_variable cv;
+    std::set<int> wanting; bool busy = false;
+    void want(int idx) { std::lock_guard<std::mutex> g(mu); wanting.insert(idx); }          // (kept from round to round)
+    void unwant(int idx) {
+        { std::lock_guard<std::mutex> g(mu); wanting.erase(idx); }
+        cv.notify_all();
+    }
+    void enter(int idx) {
+        std::unique_lock<std::mutex> g(mu);
+        cv.wait(g, [&] { return !busy && !wanting.empty() && *wanting.begin() == idx; });
+        busy = true;
+    }
+    void leave() {
+        { std::lock_guard<std::mutex> g(mu); busy = false; }
+        cv.notify_all();
+    }
+};
+
 class GzAhead : public Source {
 public:
     static constexpr int64_t BLOCK = 4ll << 20, LIMIT = 1ll << 30;      // read-ahead per file
-    GzAhead(const std::string &name, int threads) : name_(name), threads_(threads) { th_ = std::thread([this] { run(); }); }
+    GzAhead(const std::string &name, int threads, std::shared_ptr<GzGate> gate = nullptr, int index = 0)
+        : name_(name), threads_(threads), gate_(std::move(gate)), index_(index) { th_ = std::thread([this] { run(); }); }
     ~GzAhead() override {
         { std::lock_guard<std::mutex> g(mu_); cancel_ = true; }
         cv_.notify_all();
@@ -329,7 +355,7 @@ public:
                 if (err_) std::rethrow_exception(err_);
                 break;
             }
-            std::vector<uint8_t> &bk = blocks_.front();
+            kvq_gz::Bytes &bk = blocks_.front();
             const int64_t m = std::min<int64_t>(cap - got, (int64_t) bk.size() - front_off_);
             g.unlock();
             memcpy(dst + got, bk.data() + front_off_, (size_t) m);
@@ -352,17 +378,27 @@ public:
     bool compressed() const override { return true; }
 private:
     void run_parallel() {
-        // the whole compressed file in memory (readable 64 bytes past its end), then round after round
+        // the whole compressed file mapped (readable 64 bytes past its end: the mapping of the file lies on top of
+        // a zero-filled reservation one page longer), then round after round
         int fd = open(name_.c_str(), O_RDONLY);
         struct stat sb;
         if (fd < 0 || fstat(fd, &sb) != 0) { if (fd >= 0) close(fd); throw KvqError(KVQ_ERR_IO, "cannot open file"); }
-        std::vector<uint8_t> file((size_t) sb.st_size + 64, 0);
-        for (int64_t at = 0; at < (int64_t) sb.st_size;) {
-            const ssize_t m = pread(fd, file.data() + at, (size_t) std::min<int64_t>(8 << 20, (int64_t) sb.st_size - at), (off_t) at);
-            if (m <= 0) { close(fd); throw KvqError(KVQ_ERR_IO, "could not read enough bytes from .fastq.gz"); }
-            at += m;
+        struct Mapping {
+            uint8_t *p = nullptr; size_t n = 0;
+            ~Mapping() { if (p) munmap(p, n); }
+        } map;
+        const size_t page = (size_t) sysconf(_SC_PAGESIZE);
+        map.n = (((size_t) sb.st_size + 64 + page - 1) / page + 1) * page;
+        void *base = mmap(nullptr, map.n, PROT_READ, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+        if (base == MAP_FAILED) { close(fd); throw KvqError(KVQ_ERR_IO, "cannot map file"); }
+        map.p = (uint8_t *) base;
+        if (sb.st_size > 0 && mmap(base, (size_t) sb.st_size, PROT_READ, MAP_PRIVATE | MAP_FIXED, fd, 0) == MAP_FAILED) {
+            close(fd);
+            throw KvqError(KVQ_ERR_IO, "could not read enough bytes from .fastq.gz");
         }
         close(fd);
+        madvise(map.p, (size_t) sb.st_size, MADV_WILLNEED);
+        struct { const uint8_t *p; const uint8_t *data() const { return p; } } file{map.p};
         try {
             kvq_gz::FileDecoder dec(file.data(), (int64_t) sb.st_size, threads_);
             {
@@ -370,17 +406,24 @@ private:
                 size_ = (int64_t) sb.st_size; pos_ = dec.disk_pos(); opened_ = true;
             }
             cv_.notify_all();
-            std::vector<std::vector<uint8_t>> outs, spares;
+            std::vector<kvq_gz::Bytes> outs, spares;
             std::vector<kvq_gz::Event> ev;
+            struct Unwant { GzGate *g; int idx; ~Unwant() { if (g) g->unwant(idx); } } unwant{gate_.get(), index_};
             for (;;) {
                 {
                     std::unique_lock<std::mutex> g(mu_);
+                    if (gate_ && !(buffered_ < LIMIT || cancel_)) gate_->unwant(index_);       // read-ahead full: the next file's turn
                     cv_.wait(g, [&] { return buffered_ < LIMIT || cancel_; });
                     if (cancel_) break;
                     spares.swap(spares_);
                 }
                 outs.clear(); ev.clear();
+                const bool gated = gate_ && dec.parallel_mode();
+                if (gated) { gate_->want(index_); gate_->enter(index_); }
+                else if (gate_) gate_->unwant(index_);
+                struct Leave { GzGate *g; ~Leave() { if (g) g->leave(); } } leave{gated ? gate_.get() : nullptr};
                 const bool more = dec.next(outs, ev, &spares);
+                if (gated) { gate_->leave(); leave.g = nullptr; }
                 {
                     std::lock_guard<std::mutex> g(mu_);
                     for (const kvq_gz::Event &x : ev) events_.push_back(GzEvent{x.out, x.pos, x.at_end});
@@ -410,7 +453,7 @@ private:
                     cv_.wait(g, [&] { return buffered_ < LIMIT || cancel_; });
                     if (cancel_) break;
                 }
-                std::vector<uint8_t> bk((size_t) BLOCK);
+                kvq_gz::Bytes bk((size_t) BLOCK);
                 bool filled = false;
                 const int64_t got = src.fill((char *) bk.data(), BLOCK, &filled);
                 bk.resize((size_t) got);
@@ -431,9 +474,10 @@ private:
         }
     }
     std::string name_; int threads_ = 1;
+    std::shared_ptr<GzGate> gate_; int index_ = 0;
     std::thread th_;
     std::mutex mu_; std::condition_variable cv_;
-    std::deque<std::vector<uint8_t>> blocks_; std::vector<std::vector<uint8_t>> spares_;
+    std::deque<kvq_gz::Bytes> blocks_; std::vector<kvq_gz::Bytes> spares_;
     int64_t front_off_ = 0, buffered_ = 0, consumed_ = 0;
     std::vector<GzEvent> events_; size_t ev_at_ = 0;
     int64_t size_ = 0, pos_ = 0;
@@ -496,11 +540,10 @@ public:
                  LiveStats *live, WorkPool *pool = nullptr, int inflate_threads = 1)
         : names_(std::move(names)), mems_(std::move(mems)), live_(live), pool_(pool)
     {
-        {   // inflate threads per .gz file: the files of a scan inflate side by side (start_ahead)
-            int ngz = 0;
-            for (auto &nm : names_) ngz += has_gz_suffix(nm);
-            gz_threads_ = std::max(1, inflate_threads / std::max(1, std::min(ngz, (int) AHEAD)));
-        }
+        // every .gz file may use all the inflate threads: the parallel rounds take turns (GzGate); with one thread the
+        // files of a scan inflate side by side, one zlib stream each (start_ahead)
+        gz_threads_ = std::max(1, inflate_threads);
+        if (gz_threads_ > 1) gate_ = std::make_shared<GzGate>();
         nfiles_ = names_.empty() ? (int) mems_.size() : (int) names_.size();
         // fastq_open (:659-677): total size first, then the first file
         for (int i = 0; i < nfiles_; i++) {
@@ -585,7 +628,7 @@ private:
         const int i = next_file_++;
         if (!names_.empty()) {
             if (has_gz_suffix(names_[i])) {
-                if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i], gz_threads_));
+                if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i], gz_threads_, gate_, (int) i));
                 ahead_[i]->wait_opened();
                 src_ = std::move(ahead_[i]);
                 start_ahead();
@@ -607,7 +650,7 @@ private:
         int running = 0;
         for (size_t i = (size_t) next_file_; i < names_.size() && running < AHEAD; i++) {
             if (!has_gz_suffix(names_[i])) break;                           // (a plain file after .gz is an error anyway)
-            if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i], gz_threads_));
+            if (!ahead_[i]) ahead_[i].reset(new GzAhead(names_[i], gz_threads_, gate_, (int) i));
             running++;
         }
     }
@@ -617,6 +660,7 @@ private:
     std::vector<std::pair<const char *, int64_t>> mems_;
     LiveStats *live_;
     WorkPool *pool_ = nullptr; int gz_threads_ = 1;
+    std::shared_ptr<GzGate> gate_;
     int nfiles_ = 0, next_file_ = 0;
     std::unique_ptr<Source> src_;
     bool at_eof_ = false, compressed_ = false, finished_ = false;

@@ -5,19 +5,24 @@
 // FastQ, two orders of magnitude below what the GPU scans.  A deflate stream has no index, but it
 // can still be decoded by many threads (the idea of pugz / rapidgzip):
 //
-//   1. the compressed bytes are cut into chunks; every thread looks for the first deflate block that
-//      starts in its chunk (bit by bit: a dynamic-Huffman header whose code-length code, literal and
-//      distance codes are all complete, whose block decodes to its end-of-block and is followed by
-//      another valid block header);
+//   1. the compressed bytes are cut into chunks of 2 MiB, two per thread; every thread looks for the first
+//      deflate block that starts in its chunks (bit by bit: BFINAL = 0 / dynamic / HLIT, HDIST in range and a
+//      complete code-length code are tested in line -- one position in ~1 500 survives --, then a header
+//      whose literal and distance codes are complete, whose block decodes to its end-of-block and is
+//      followed by another valid block header);
 //   2. it decodes from there WITHOUT the 32 KiB of history in front of it: output goes to 16-bit
-//      cells, a back-reference into the unknown history becomes a marker (0x8000 | window offset).
-//      At the first block boundary with 32 KiB of marker-free output behind it the thread hands the
-//      stream to zlib (inflatePrime to the bit position, inflateSetDictionary with those 32 KiB) and
-//      decodes plain bytes at zlib's speed until it lands exactly on the start another thread found;
+//      cells, a back-reference into the unknown history becomes a marker (0x8000 | window offset) and is
+//      copied along like any other cell (in a FastQ the markers never die out: every header line copies
+//      from the one before it), until the chunk lands exactly on the start another thread found.  The
+//      first chunk of a round knows its history and writes bytes into the same cells.  The symbol loop is
+//      branch-free (hot1 / hot2 below: a literal is a copy of one cell; literal-or-copy is a coin toss in
+//      DNA, and so is every branch on it) and runs over the thread's two chunks together, so that one
+//      chunk's chain of dependent table look-ups overlaps the other's;
 //   3. the chunks are chained in stream order (a chunk start nobody lands on was a false positive and
-//      its output is dropped), markers are replaced from the tail of the chunk in front.
+//      its output is dropped); cells become bytes through a 64 KiB table made of the 32 KiB in front of
+//      the chunk (the tail of the chunk before it, resolved first).
 //
-// Nothing is trusted: a chain that does not close, a candidate that fails, any zlib error -> the
+// Nothing is trusted: a chain that does not close, a candidate that fails, invalid data -> the
 // member is decoded by the sequential reader below, which is the round-1 code on a memory buffer
 // and reproduces the reference byte for byte, including the positions of its 1 MiB compressed
 // reads (GzEvent: they feed the size estimate of engine.stats(), workhorse.c:883-884).
@@ -34,6 +39,10 @@
 #include <stdexcept>
 #include <string>
 #include <thread>
+#if defined(__x86_64__)
+#include <immintrin.h>
+#include <emmintrin.h>
+#endif
 #include <vector>
 
 namespace kvq_gz {
@@ -47,6 +56,22 @@ struct Error : std::runtime_error {
     bool io;        // IOError of the reference (else RuntimeError)
     Error(bool io_, const std::string &m) : std::runtime_error(m), io(io_) {}
 };
+
+// Buffers whose bytes are written before they are read: growing them must not zero-fill (a memset of the
+// whole output, on one thread, costs as much as decoding it on sixteen).
+template <class T> struct NoInit {
+    using value_type = T;
+    NoInit() = default;
+    template <class U> NoInit(const NoInit<U> &) {}
+    T *allocate(size_t n) { return static_cast<T *>(::operator new(n * sizeof(T))); }
+    void deallocate(T *p, size_t) { ::operator delete(p); }
+    template <class U> void construct(U *p) { ::new ((void *) p) U; }
+    template <class U, class A0, class... A> void construct(U *p, A0 &&a0, A &&... a) { ::new ((void *) p) U(std::forward<A0>(a0), std::forward<A>(a)...); }
+    template <class U> bool operator==(const NoInit<U> &) const { return true; }
+    template <class U> bool operator!=(const NoInit<U> &) const { return false; }
+};
+using Bytes = std::vector<uint8_t, NoInit<uint8_t>>;
+using Cells = std::vector<uint16_t, NoInit<uint16_t>>;
 
 constexpr int64_t PIECE = 1024 * 1024;      // compressed bytes per read of the reference (SCANBUFSIZE, workhorse.c:15)
 constexpr int WSIZE = 32768;
@@ -62,9 +87,9 @@ struct Bits {
 };
 
 // ---------------------------------------------------------------------------------- Huffman codes
-// Canonical decoder: 11-bit direct table for the short codes, count/offset search for longer ones.
+// Canonical decoder: 10-bit direct table for the short codes, count/offset search for longer ones.
 struct Huff {
-    static constexpr int FAST = 11;
+    static constexpr int FAST = 10;
     uint16_t fast[1 << FAST];               // sym << 4 | len, 0 = not a short code
     uint16_t count[16], symbol[288];
     int maxlen = 0;
@@ -121,7 +146,15 @@ static const uint8_t LEN_EXTRA[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 
 static const uint16_t DIST_BASE[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
 static const uint8_t DIST_EXTRA[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
 
-struct BlockCodes { Huff lit, dist; };
+// Packed entries for the decoder's hot loop, indexed by the next FAST bits:
+//   bits 0-7 code length + extra bits, 8-11 code length, 14 a length (a copy follows), 15 not for the hot loop
+//   (end of block, a code longer than FAST bits, an invalid code), 16-31 the literal or the base of the length /
+//   distance.  A distance entry of 0 (long or invalid code) yields distance 0, which the hot loop stops at.
+struct BlockCodes {
+    Huff lit, dist;
+    uint32_t lt[1 << Huff::FAST], dt[1 << Huff::FAST];
+    void pack();
+};
 
 // Header of a dynamic block at bit position pos (behind BFINAL / BTYPE): code lengths -> codes.
 // Strict: every code must be complete (a lone distance code excepted, as zlib allows), 256 must
@@ -177,6 +210,23 @@ inline int64_t read_dynamic_header(const Bits &b, int64_t pos, BlockCodes &bc)
     return pos;
 }
 
+inline void BlockCodes::pack()
+{
+    for (int i = 0; i < (1 << Huff::FAST); i++) {
+        uint32_t e = lit.fast[i], x = 0x8000;
+        if (e) {
+            const uint32_t sym = e >> 4, l = e & 15;
+            if (sym < 256) x = sym << 16 | l << 8 | l;
+            else if (sym > 256 && sym < 286)
+                x = (uint32_t) LEN_BASE[sym - 257] << 16 | 0x4000 | l << 8 | (l + LEN_EXTRA[sym - 257]);
+        }
+        lt[i] = x;
+        e = dist.fast[i]; x = 0;
+        if (e && (e >> 4) < 30) x = (uint32_t) DIST_BASE[e >> 4] << 16 | (e & 15) << 8 | ((e & 15) + DIST_EXTRA[e >> 4]);
+        dt[i] = x;
+    }
+}
+
 inline void fixed_codes(BlockCodes &bc)
 {
     uint8_t l[288];
@@ -193,7 +243,7 @@ inline void fixed_codes(BlockCodes &bc)
 // ------------------------------------------------------------------------ decoding without history
 // Output cells: 0..255 a byte, 0x8000 | k the byte at offset k of the (unknown) 32 KiB in front of the chunk.
 struct MarkerOut {
-    std::vector<uint16_t> cells;            // capacity; `n` cells are valid
+    Cells cells;                            // capacity; `n` cells are valid
     int64_t n = 0;
     inline void room(int64_t more) { if (n + more > (int64_t) cells.size()) cells.resize((size_t) std::max<int64_t>(2 * (int64_t) cells.size(), n + more + (1 << 20))); }
 };
@@ -228,87 +278,218 @@ struct CrossTracker {
     int64_t fsize = 0;
 };
 
-// One deflate block at bit position pos (its BFINAL bit) into marker cells.  Returns the bit
-// position behind the block, -1 on invalid data; *final = BFINAL.  max_out bounds the output.
-inline int64_t marker_block(const Bits &b, int64_t pos, MarkerOut &o, CrossTracker &ct, bool *final, int64_t max_out)
-{
-    if (pos + 3 > b.nbits) return -1;
-    uint64_t v = b.peek(pos);
-    *final = v & 1;
-    const int type = (int) ((v >> 1) & 3);
-    pos += 3;
-    if (type == 3) return -1;
-    if (type == 0) {                        // stored
-        pos = (pos + 7) & ~(int64_t) 7;
-        if (pos + 32 > b.nbits) return -1;
-        v = b.peek(pos);
-        const uint32_t len = (uint32_t) (v & 0xFFFF), nlen = (uint32_t) ((v >> 16) & 0xFFFF);
-        if ((len ^ 0xFFFF) != nlen) return -1;
-        pos += 32;
-        if (pos + 8 * (int64_t) len > b.nbits || o.n + len > max_out) return -1;
-        const uint8_t *src = b.d + (pos >> 3);
-        o.room(len);
-        for (uint32_t i = 0; i < len; i++) {
-            ct.symbol_end(pos + 8 * (int64_t) (i + 1), o.n);
-            o.cells[(size_t) o.n++] = src[i];
-        }
-        return pos + 8 * (int64_t) len;
-    }
+struct LitCells { uint16_t cell[256 + 16]; LitCells() { for (int i = 0; i < 256 + 16; i++) cell[i] = (uint16_t) i; } };
+static const LitCells LIT;
+
+// One deflate block of one stream, resumable: begin() reads the header, hot1() / hot2() run the
+// branch-free symbol loop (for one stream, or for two independent streams in the same loop: one
+// symbol costs a chain of ~28 dependent cycles -- table look-up, shift, table look-up, shift --
+// that a second stream's chain overlaps), careful() takes one symbol with every check: the ones the
+// hot loop stops in front of (end of block, a code longer than FAST bits, a copy from closer than
+// 16 cells or out of the window) and those near the end of the data or a 1 MiB input piece.
+// Output: cells, see MarkerOut; win / wlen: the known history in front of cell 0 (the first chunk
+// of a round), nullptr: unknown -> markers.
+struct BlockDec {
+    const Bits *b = nullptr; MarkerOut *o = nullptr; CrossTracker *ct = nullptr;
+    const uint8_t *win = nullptr; int wlen = 0;
+    int64_t max_out = 0;
     BlockCodes bc;
-    if (type == 1) fixed_codes(bc);
-    else { pos = read_dynamic_header(b, pos, bc); if (pos < 0) return -1; }
-    const int64_t limit_bits = b.nbits - 48;            // (a symbol needs at most 15 + 5 + 15 + 13 bits)
-    for (;;) {
-        o.room(4096);
-        uint16_t *c = o.cells.data();
-        int64_t n = o.n;
-        const int64_t n_stop = std::min<int64_t>((int64_t) o.cells.size() - 300, max_out);
-        const int64_t cross_bit = ct.next >= NO_BOUNDARY ? INT64_MAX : 8 * ct.next;
-        // inner loop: until the output room or the next piece boundary needs attention
-        while (n < n_stop) {
-            if (pos > limit_bits) { o.n = n; return -1; }
-            v = b.peek(pos);
-            int l;
-            int sym = bc.lit.decode(v, l);
-            if (sym < 0) { o.n = n; return -1; }
-            int64_t p = pos + l; v >>= l;
-            if (sym < 256) {
-                if (p > cross_bit) { o.n = n; ct.symbol_end(p, n); pos = p; c[n++] = (uint16_t) sym; break; }
-                c[n++] = (uint16_t) sym;
-                pos = p;
-                // a second literal from the same 57 bits
-                sym = bc.lit.decode(v, l);
-                if (sym >= 0 && sym < 256 && p + l <= cross_bit) { c[n++] = (uint16_t) sym; pos = p + l; }
-                continue;
+    int64_t pos = 0;                        // bit position of the next symbol / behind the block
+    bool final = false;
+    // the stretch the hot loop may run over, set by prepare()
+    uint16_t *c = nullptr; int64_t n = 0, n_stop = 0, cross_bit = 0, fast_limit = 0, limit_bits = 0;
+    enum Status { MORE, END, BAD };
+
+    // header at bit position `at` (the BFINAL bit).  A stored block is copied whole: END.
+    Status begin(int64_t at)
+    {
+        pos = at;
+        if (pos + 3 > b->nbits) return BAD;
+        uint64_t v = b->peek(pos);
+        final = v & 1;
+        const int type = (int) ((v >> 1) & 3);
+        pos += 3;
+        if (type == 3) return BAD;
+        if (type == 0) {
+            pos = (pos + 7) & ~(int64_t) 7;
+            if (pos + 32 > b->nbits) return BAD;
+            v = b->peek(pos);
+            const uint32_t len = (uint32_t) (v & 0xFFFF), nlen = (uint32_t) ((v >> 16) & 0xFFFF);
+            if ((len ^ 0xFFFF) != nlen) return BAD;
+            pos += 32;
+            if (pos + 8 * (int64_t) len > b->nbits || o->n + len > max_out) return BAD;
+            const uint8_t *src = b->d + (pos >> 3);
+            o->room(len);
+            for (uint32_t i = 0; i < len; i++) {
+                ct->symbol_end(pos + 8 * (int64_t) (i + 1), o->n);
+                o->cells[(size_t) o->n++] = src[i];
             }
-            if (sym == 256) { o.n = n; ct.symbol_end(p, n); return p; }
-            sym -= 257;
-            if (sym >= 29) { o.n = n; return -1; }
-            const int len = LEN_BASE[sym] + (int) (v & ((1u << LEN_EXTRA[sym]) - 1));
-            p += LEN_EXTRA[sym]; v >>= LEN_EXTRA[sym];
-            int dl;
-            const int ds = bc.dist.decode(v, dl);
-            if (ds < 0 || ds >= 30) { o.n = n; return -1; }
-            p += dl; v >>= dl;
-            const int dist = DIST_BASE[ds] + (int) (v & ((1u << DIST_EXTRA[ds]) - 1));
-            p += DIST_EXTRA[ds];
-            if (p > cross_bit) { o.n = n; ct.symbol_end(p, n); }
-            pos = p;
-            int64_t from = n - dist;
-            if (from >= 0) {
-                const uint16_t *src = c + from; uint16_t *dst = c + n;
-                if (dist >= len) memcpy(dst, src, 2 * (size_t) len);
-                else for (int i = 0; i < len; i++) dst[i] = src[i];
-                n += len;
-            } else {
-                if (from < -WSIZE) { o.n = n; return -1; }
-                for (int i = 0; i < len; i++, from++) c[n++] = from < 0 ? (uint16_t) (0x8000 | (WSIZE + from)) : c[from];
-            }
-            if (p > cross_bit) break;
+            pos += 8 * (int64_t) len;
+            return END;
         }
-        o.n = n;
-        if (n >= max_out) return -1;
+        if (type == 1) fixed_codes(bc);
+        else { pos = read_dynamic_header(*b, pos, bc); if (pos < 0) return BAD; }
+        bc.pack();
+        limit_bits = b->nbits - 48;         // (a symbol needs at most 15 + 5 + 15 + 13 bits)
+        return MORE;
     }
+
+    // room for the next stretch of output, and how far the hot loop may go without looking up
+    inline void prepare()
+    {
+        o->room(4096);
+        c = o->cells.data();
+        n = o->n;
+        n_stop = std::min<int64_t>((int64_t) o->cells.size() - 300, max_out);
+        cross_bit = ct->next >= NO_BOUNDARY ? INT64_MAX : 8 * ct->next;
+        fast_limit = std::min(limit_bits, cross_bit) - 128;
+    }
+    inline bool hot_ready() const { return pos < fast_limit && n < n_stop && n >= 16; }
+
+    // one symbol, every check.  Needs n < n_stop (room for 258 cells).
+    Status careful()
+    {
+        if (pos > limit_bits) return BAD;
+        uint64_t v = b->peek(pos);
+        int l;
+        int sym = bc.lit.decode(v, l);
+        if (sym < 0) return BAD;
+        int64_t p = pos + l; v >>= l;
+        if (sym < 256) {
+            if (p > cross_bit) { ct->symbol_end(p, n); cross_bit = ct->next >= NO_BOUNDARY ? INT64_MAX : 8 * ct->next; }
+            c[n++] = (uint16_t) sym;
+            pos = p; o->n = n;
+            return MORE;
+        }
+        if (sym == 256) { o->n = n; ct->symbol_end(p, n); pos = p; return END; }
+        sym -= 257;
+        if (sym >= 29) return BAD;
+        const int len = LEN_BASE[sym] + (int) (v & ((1u << LEN_EXTRA[sym]) - 1));
+        p += LEN_EXTRA[sym]; v >>= LEN_EXTRA[sym];
+        int dl;
+        const int ds = bc.dist.decode(v, dl);
+        if (ds < 0 || ds >= 30) return BAD;
+        p += dl; v >>= dl;
+        const int dist = DIST_BASE[ds] + (int) (v & ((1u << DIST_EXTRA[ds]) - 1));
+        p += DIST_EXTRA[ds];
+        if (p > cross_bit) { ct->symbol_end(p, n); cross_bit = ct->next >= NO_BOUNDARY ? INT64_MAX : 8 * ct->next; }
+        pos = p;
+        int64_t from = n - dist;
+        if (from >= 0) {
+            const uint16_t *src = c + from; uint16_t *dst = c + n;
+            if (dist >= len) memcpy(dst, src, 2 * (size_t) len);
+            else for (int i = 0; i < len; i++) dst[i] = src[i];
+            n += len;
+        } else {
+            if (from < -WSIZE) return BAD;
+            if (win) {
+                if (wlen + from < 0) return BAD;
+                for (int i = 0; i < len; i++, from++) c[n++] = from < 0 ? (uint16_t) win[wlen + from] : c[from];
+            } else for (int i = 0; i < len; i++, from++) c[n++] = from < 0 ? (uint16_t) (0x8000 | (WSIZE + from)) : c[from];
+        }
+        o->n = n;
+        return MORE;
+    }
+};
+
+// The registers of one stream inside the hot loop.
+#define KVQ_GZ_HOT_OPEN(S, D)                                                                                   \
+    const uint8_t *S##inp = (D).b->d + ((D).pos >> 3);                                                          \
+    uint64_t S##bb = (uint64_t) *S##inp++ >> ((D).pos & 7);                                                     \
+    int S##left = 8 - (int) ((D).pos & 7);                                                                      \
+    { uint64_t w; memcpy(&w, S##inp, 8); S##bb |= w << S##left; S##inp += (63 - S##left) >> 3; S##left |= 56; } \
+    const uint8_t *const S##stop = (D).b->d + ((D).fast_limit >> 3);                                            \
+    const uint32_t *const S##lt = (D).bc.lt, *const S##dt = (D).bc.dt;                                          \
+    uint16_t *const S##c = (D).c;                                                                               \
+    int64_t S##n = (D).n;                                                                                       \
+    const int64_t S##n_stop = (D).n_stop;                                                                       \
+    uint32_t S##e = S##lt[S##bb & M];
+// One symbol: a literal is a copy of one cell out of LIT; the distance look-up is made for every symbol and
+// masked away for literals; `break` in front of anything unusual, with nothing consumed.  Everything is selected
+// with masks (written as ?: the compiler makes a branch of it, and literal-or-copy is a coin toss).
+// BZHI(x, n): the low (n & 255) bits of x.
+#define KVQ_GZ_HOT_SYMBOL(S, BZHI)                                                                              \
+    if (__builtin_expect(S##e & 0x8000, 0)) break;                                                              \
+    const uint64_t S##mm = 0ull - ((S##e >> 14) & 1);                                                           \
+    const uint32_t S##val = (uint32_t) (BZHI(S##bb, S##e) >> ((S##e >> 8) & 63)) + (S##e >> 16);               \
+    const uint64_t S##b1 = S##bb >> (S##e & 63);                                                                \
+    const uint32_t S##d = S##dt[S##b1 & M];                                                                     \
+    const int64_t S##dist = (int64_t) ((BZHI(S##b1, S##d) >> ((S##d >> 8) & 63)) + (S##d >> 16));              \
+    if (__builtin_expect(S##mm & (uint64_t) ((uint64_t) (S##dist - 16) > (uint64_t) (S##n - 16)), 0)) break;    \
+    const int S##tot = (int) ((S##e & 0xFF) + ((S##d & 0xFF) & (uint32_t) S##mm));                              \
+    const uintptr_t S##s_lit = (uintptr_t) (LIT.cell + S##val), S##s_m = (uintptr_t) (S##c + (S##n - S##dist)); \
+    const uint16_t *S##src = (const uint16_t *) (S##s_lit ^ ((S##s_lit ^ S##s_m) & (uintptr_t) S##mm));         \
+    const int S##len = 1 + (int) ((S##val - 1) & (uint32_t) S##mm);                                             \
+    S##e = S##lt[(S##bb >> S##tot) & M];            /* (>= 16 bits are left: enough for the next code) */       \
+    S##bb >>= S##tot; S##left -= S##tot;                                                                        \
+    { uint64_t w; memcpy(&w, S##inp, 8); S##bb |= w << S##left; S##inp += (63 - S##left) >> 3; S##left |= 56; } \
+    {                                                                                                           \
+        uint16_t *dst = S##c + S##n;                                                                            \
+        memcpy(dst, S##src, 16); memcpy(dst + 8, S##src + 8, 16);                                               \
+        if (__builtin_expect(S##len > 16, 0))                                                                   \
+            for (int i = 16; i < S##len; i += 8) memcpy(dst + i, S##src + i, 16);                               \
+    }                                                                                                           \
+    S##n += S##len;
+#define KVQ_GZ_HOT_CLOSE(S, D)                                                                                  \
+    (D).pos = 8 * (int64_t) (S##inp - (D).b->d) - S##left;                                                      \
+    (D).n = S##n; (D).o->n = S##n;
+
+#define KVQ_GZ_BZHI_PLAIN(x, n) ((x) & ~(~0ull << ((n) & 63)))
+#define KVQ_GZ_BZHI_BMI2(x, n) _bzhi_u64((x), (uint32_t) (n))
+#define KVQ_GZ_HOT1_BODY(BZHI)                                                                                  \
+    {                                                                                                           \
+        constexpr uint64_t M = (1u << Huff::FAST) - 1;                                                          \
+        KVQ_GZ_HOT_OPEN(a, A)                                                                                   \
+        while (an < an_stop && ainp < astop) {                                                                  \
+            KVQ_GZ_HOT_SYMBOL(a, BZHI)                                                                          \
+        }                                                                                                       \
+        KVQ_GZ_HOT_CLOSE(a, A)                                                                                  \
+    }
+#define KVQ_GZ_HOT2_BODY(BZHI)                                                                                  \
+    {                                                                                                           \
+        constexpr uint64_t M = (1u << Huff::FAST) - 1;                                                          \
+        KVQ_GZ_HOT_OPEN(a, A)                                                                                   \
+        KVQ_GZ_HOT_OPEN(b, B)                                                                                   \
+        while (an < an_stop && ainp < astop && bn < bn_stop && binp < bstop) {                                  \
+            KVQ_GZ_HOT_SYMBOL(a, BZHI)                                                                          \
+            KVQ_GZ_HOT_SYMBOL(b, BZHI)                                                                          \
+        }                                                                                                       \
+        KVQ_GZ_HOT_CLOSE(a, A)                                                                                  \
+        KVQ_GZ_HOT_CLOSE(b, B)                                                                                  \
+    }
+// Built twice: BMI2 (shrx / shlx / bzhi: a third fewer instructions in a loop that is bound by them) and plain.
+inline void hot1_plain(BlockDec &A) KVQ_GZ_HOT1_BODY(KVQ_GZ_BZHI_PLAIN)
+inline void hot2_plain(BlockDec &A, BlockDec &B) KVQ_GZ_HOT2_BODY(KVQ_GZ_BZHI_PLAIN)
+#if defined(__x86_64__)
+__attribute__((target("bmi2"))) inline void hot1_bmi2(BlockDec &A) KVQ_GZ_HOT1_BODY(KVQ_GZ_BZHI_BMI2)
+__attribute__((target("bmi2"))) inline void hot2_bmi2(BlockDec &A, BlockDec &B) KVQ_GZ_HOT2_BODY(KVQ_GZ_BZHI_BMI2)
+inline bool cpu_has_bmi2() { static const bool yes = __builtin_cpu_supports("bmi2") && !getenv("KVQ_GZ_NO_BMI2"); return yes; }
+#else
+inline void hot1_bmi2(BlockDec &A) { hot1_plain(A); }
+inline void hot2_bmi2(BlockDec &A, BlockDec &B) { hot2_plain(A, B); }
+inline bool cpu_has_bmi2() { return false; }
+#endif
+// (both need hot_ready() of their streams)
+inline void hot1(BlockDec &A) { if (cpu_has_bmi2()) hot1_bmi2(A); else hot1_plain(A); }
+inline void hot2(BlockDec &A, BlockDec &B) { if (cpu_has_bmi2()) hot2_bmi2(A, B); else hot2_plain(A, B); }
+
+// One deflate block at bit position pos (its BFINAL bit) into cells.  Returns the bit position
+// behind the block, -1 on invalid data; *final = BFINAL.  max_out bounds the output.
+inline int64_t marker_block(const Bits &b, int64_t pos, MarkerOut &o, CrossTracker &ct, bool *final, int64_t max_out,
+                            const uint8_t *win = nullptr, int wlen = 0)
+{
+    BlockDec d;
+    d.b = &b; d.o = &o; d.ct = &ct; d.win = win; d.wlen = wlen; d.max_out = max_out;
+    BlockDec::Status st = d.begin(pos);
+    *final = d.final;
+    if (st == BlockDec::BAD) return -1;
+    while (st == BlockDec::MORE) {
+        d.prepare();
+        if (d.n >= max_out) return -1;
+        if (d.hot_ready()) hot1(d);
+        if (d.n < d.n_stop) st = d.careful();
+    }
+    return st == BlockDec::END ? d.pos : -1;
 }
 
 // Is there a block start at bit position pos?  A non-final dynamic block that decodes to its end
@@ -341,8 +522,20 @@ inline bool plausible_block_start(const Bits &b, int64_t pos)
 
 inline int64_t find_block_start(const Bits &b, int64_t from_bit, int64_t to_bit)
 {
-    for (int64_t pos = from_bit; pos < to_bit; pos++)
+    // the cheap tests here, in line (BFINAL = 0, BTYPE = dynamic, HLIT / HDIST in range, code-length code complete):
+    // one position in ~1 500 goes on to the full test
+    static const uint8_t K[8] = {0, 64, 32, 16, 8, 4, 2, 1};
+    to_bit = std::min(to_bit, b.nbits - 17 - 57);
+    for (int64_t pos = from_bit; pos < to_bit; pos++) {
+        const uint64_t v = b.peek(pos);
+        if ((v & 7) != 4 || ((v >> 3) & 31) > 29 || ((v >> 8) & 31) > 29) continue;
+        const int ncode = (int) ((v >> 13) & 15) + 4;
+        uint64_t w = b.peek(pos + 17) & ~(~0ull << (3 * ncode));        // (a fixed trip count: lengths not sent count as 0)
+        int kraft = 0;
+        for (int i = 0; i < 19; i++) { kraft += K[w & 7]; w >>= 3; }
+        if (kraft != 128) continue;
         if (plausible_block_start(b, pos)) return pos;
+    }
     return -1;
 }
 
@@ -353,10 +546,10 @@ struct Chunk {
     int64_t end_bit = -1;                   // block boundary where it stopped
     int landed = -1;                        // index of the chunk whose start it stopped on, -1: none
     bool at_final = false, at_limit = false; // stopped in front of a final block / at the end of the round
-    MarkerOut head;                         // output decoded without history (empty for chunk 0)
-    std::vector<uint8_t> body;              // output decoded by zlib behind it
+    MarkerOut head;                         // the chunk's output, in cells
+    double ms = 0;                          // decoding time, for the trace
     std::vector<Crossing> cross;            // 1 MiB input piece boundaries crossed, `out` counted from the chunk's start
-    int64_t out_size() const { return head.n + (int64_t) body.size(); }
+    int64_t out_size() const { return head.n; }
 };
 
 struct RoundCtx {
@@ -378,73 +571,71 @@ inline bool chunk_stops_here(const RoundCtx &rc, Chunk &c, int self, int64_t pos
     return false;
 }
 
-// known: the history in front of start_bit is `window` (wlen <= 32 KiB bytes; chunk 0); else it is decoded into marker cells
+// One chunk being decoded, resumable so that one thread can take two chunks through hot2() together.
+// known: the history in front of start_bit is `window` (wlen <= 32 KiB bytes: the round's first chunk, which
+// then writes bytes); else the whole chunk goes into marker cells (in a FastQ the markers never die out --
+// every header line copies from the one before it -- so there is no point in looking for a clean window).
+struct ChunkRun {
+    const RoundCtx *rc = nullptr; Chunk *c = nullptr; int self = 0;
+    CrossTracker ct; BlockDec d;
+    bool in_block = false, finished = true, after_hot = false;
+
+    void start(const RoundCtx &rc_, Chunk &c_, int self_, bool known, const uint8_t *window, int wlen)
+    {
+        rc = &rc_; c = &c_; self = self_;
+        c->ok = false; c->head.n = 0;
+        finished = c->start_bit < 0;
+        if (finished) return;
+        ct.init(rc->piece_base, c->start_bit, rc->fsize);
+        d.b = &rc->bits; d.o = &c->head; d.ct = &ct; d.max_out = (int64_t) 1 << 31;
+        d.win = known ? (window ? window : (const uint8_t *) "") : nullptr; d.wlen = known ? wlen : 0;
+        d.pos = c->start_bit;
+        in_block = false; after_hot = false;
+    }
+    // up to the next stretch for the hot loop (returns true), or to the end of the chunk (false)
+    bool advance()
+    {
+        while (!finished) {
+            if (!in_block) {
+                if (chunk_stops_here(*rc, *c, self, d.pos)) { c->end_bit = d.pos; c->cross.swap(ct.list); c->ok = true; finished = true; break; }
+                const BlockDec::Status st = d.begin(d.pos);
+                if (st == BlockDec::BAD) { finished = true; break; }
+                in_block = (st == BlockDec::MORE);
+                after_hot = false;
+                continue;
+            }
+            d.prepare();
+            if (d.n >= d.max_out) { finished = true; break; }
+            if (!after_hot && d.hot_ready()) return true;
+            after_hot = false;
+            if (d.n < d.n_stop) {
+                const BlockDec::Status st = d.careful();
+                if (st == BlockDec::BAD) { finished = true; break; }
+                if (st == BlockDec::END) in_block = false;
+            }
+        }
+        return false;
+    }
+};
+
+// two chunks on one thread (either may be absent: start_bit < 0)
+inline void decode_pair(ChunkRun &x, ChunkRun &y)
+{
+    bool rx = x.advance(), ry = y.advance();
+    while (rx && ry) {
+        hot2(x.d, y.d);
+        x.after_hot = y.after_hot = true;
+        rx = x.advance(); ry = y.advance();
+    }
+    while (rx) { hot1(x.d); x.after_hot = true; rx = x.advance(); }
+    while (ry) { hot1(y.d); y.after_hot = true; ry = y.advance(); }
+}
+
 inline void decode_chunk(const RoundCtx &rc, Chunk &c, int self, bool known, const uint8_t *window, int wlen)
 {
-    c.ok = false;
-    c.body.clear();                         // (keeps the capacity of a recycled buffer)
-    c.head.n = 0;
-    if (c.start_bit < 0) return;
-    CrossTracker ct;
-    ct.init(rc.piece_base, c.start_bit, rc.fsize);
-    int64_t pos = c.start_bit;
-    if (!known) {
-        // ---- without history: the whole chunk into marker cells (in a FastQ the markers never die out --
-        // every header line copies from the one before it -- so there is no point in looking for a clean window)
-        for (;;) {
-            if (chunk_stops_here(rc, c, self, pos)) { c.end_bit = pos; c.cross.swap(ct.list); c.ok = true; return; }
-            bool fin;
-            const int64_t e = marker_block(rc.bits, pos, c.head, ct, &fin, (int64_t) 1 << 31);
-            if (e < 0) return;
-            pos = e;
-        }
-    }
-    std::vector<uint8_t> dict;
-    if (wlen > 0) dict.assign(window, window + wlen);
-    // ---- zlib from the block boundary `pos` with the history in `dict`
-    z_stream zs;
-    memset(&zs, 0, sizeof(zs));
-    if (inflateInit2(&zs, -15) != Z_OK) return;
-    struct Guard { z_stream *z; ~Guard() { inflateEnd(z); } } guard{&zs};
-    int64_t in_at = pos >> 3;                                       // file offset of next_in
-    if (pos & 7) {
-        if (inflatePrime(&zs, 8 - (int) (pos & 7), rc.file[in_at] >> (pos & 7)) != Z_OK) return;
-        in_at++;
-    }
-    if (!dict.empty() && inflateSetDictionary(&zs, dict.data(), (uInt) dict.size()) != Z_OK) return;
-    if (chunk_stops_here(rc, c, self, pos)) { c.end_bit = pos; c.cross.swap(ct.list); c.ok = true; return; }
-    // (ct.next was advanced by the marker phase; a boundary at or in front of in_at cannot be pending:
-    //  the symbol that took the last bits in front of `pos` crossed it)
-    const int64_t head_n = c.head.n;
-    size_t used = 0;
-    c.body.resize(std::max<size_t>(c.body.capacity(), 8u << 20));
-    zs.next_in = const_cast<Bytef *>(rc.file + in_at);
-    for (;;) {
-        const int64_t lim = std::min<int64_t>(ct.next == NO_BOUNDARY ? rc.fsize : ct.next, rc.fsize);
-        zs.avail_in = (uInt) std::min<int64_t>(lim - in_at, 1 << 30);
-        if (c.body.size() - used < (1u << 20)) c.body.resize(c.body.size() * 2);
-        zs.next_out = c.body.data() + used;
-        zs.avail_out = (uInt) std::min<size_t>(c.body.size() - used, 1u << 30);
-        const uInt in0 = zs.avail_in, out0 = zs.avail_out;
-        const int st = inflate(&zs, Z_BLOCK);
-        in_at += in0 - zs.avail_in; used += out0 - zs.avail_out;
-        if (st != Z_OK && st != Z_BUF_ERROR) { c.body.clear(); return; }    // (Z_STREAM_END cannot happen: final blocks are not entered)
-        if ((zs.data_type & 128) && !(zs.data_type & 64)) {         // at a block boundary
-            pos = 8 * in_at - (zs.data_type & 63);
-            if (chunk_stops_here(rc, c, self, pos)) break;
-        }
-        if (zs.avail_in == 0 && in_at == lim) {
-            if (ct.next != NO_BOUNDARY && in_at == ct.next) {         // the input piece is used up: everything it can give is out
-                ct.list.push_back(Crossing{ct.next, head_n + (int64_t) used});
-                ct.next += PIECE;
-                if (ct.next >= rc.fsize) ct.next = NO_BOUNDARY;
-            } else if (in_at >= rc.fsize) { c.body.clear(); return; }      // ran off the file without reaching a stop
-        } else if (st == Z_BUF_ERROR && zs.avail_out != 0 && zs.avail_in != 0) { c.body.clear(); return; }
-    }
-    c.body.resize(used);
-    c.end_bit = pos;
-    c.cross.swap(ct.list);
-    c.ok = true;
+    ChunkRun x, none;
+    x.start(rc, c, self, known, window, wlen);
+    decode_pair(x, none);
 }
 
 // ------------------------------------------------------------------------------- the file reader
@@ -473,13 +664,14 @@ public:
 
     int64_t disk_pos() const { return rd_; }
     int64_t produced() const { return produced_; }
+    bool parallel_mode() const { return par_ok_ && threads_ > 1 && !done_; }   // the next call of next() tries a parallel round
     int64_t parallel_bytes() const { return par_bytes_; }      // inflated bytes that came out of parallel rounds
 
     // Appends the next stretch of output (one or more buffers) and the read events that fall into it.
     // Returns false when the stream has ended (nothing appended).
     // `spares`: buffers handed out earlier that the caller is done with (their pages are reused:
     // fresh pages cost more than the decoding).
-    bool next(std::vector<std::vector<uint8_t>> &outs, std::vector<Event> &ev, std::vector<std::vector<uint8_t>> *spares = nullptr)
+    bool next(std::vector<Bytes> &outs, std::vector<Event> &ev, std::vector<Bytes> *spares = nullptr)
     {
         if (spares) { for (auto &b : *spares) if (spare_.size() < 64) spare_.push_back(std::move(b)); spares->clear(); }
         if (done_) return false;
@@ -488,7 +680,7 @@ public:
             par_ok_ = false;
             handover(par_bit_);                     // the sequential reader takes the member from here
         }
-        std::vector<uint8_t> buf = take_spare((size_t) 4 << 20);
+        Bytes buf = take_spare((size_t) 4 << 20);
         bool filled = false;
         const int64_t got = fill(buf.data(), (int64_t) buf.size(), &filled, ev);
         buf.resize((size_t) got);
@@ -588,20 +780,20 @@ private:
         remaining_ = size_ - rd_;
     }
 
-    bool parallel_round(std::vector<std::vector<uint8_t>> &outs, std::vector<Event> &ev);
+    bool parallel_round(std::vector<Bytes> &outs, std::vector<Event> &ev);
 
-    std::vector<uint8_t> take_spare(size_t n)       // a buffer of n bytes, from the spares when one is large enough
+    Bytes take_spare(size_t n)       // a buffer of n bytes, from the spares when one is large enough
     {
         size_t best = spare_.size();
         for (size_t i = 0; i < spare_.size(); i++)
             if (spare_[i].capacity() >= n && (best == spare_.size() || spare_[i].capacity() < spare_[best].capacity())) best = i;
-        std::vector<uint8_t> b;
+        Bytes b;
         if (best < spare_.size()) { b.swap(spare_[best]); spare_.erase(spare_.begin() + (long) best); }
         b.resize(n);
         return b;
     }
-    std::vector<std::vector<uint8_t>> spare_;
-    std::vector<std::vector<uint16_t>> cells_pool_;
+    std::vector<Bytes> spare_;
+    std::vector<Cells> cells_pool_;
 
     const uint8_t *f_; int64_t size_; int threads_;
     z_stream zs_; bool live_ = false;
@@ -610,12 +802,17 @@ private:
     int64_t par_bit_ = 0; std::vector<uint8_t> window_;
 };
 
-inline bool FileDecoder::parallel_round(std::vector<std::vector<uint8_t>> &outs, std::vector<Event> &ev)
+inline bool FileDecoder::parallel_round(std::vector<Bytes> &outs, std::vector<Event> &ev)
 {
-    constexpr int64_t CHUNK = 2 << 20;              // compressed bytes per chunk
+    // Two chunks per thread (decode_pair), 2 MiB of compressed bytes each; towards the end of the file the chunks
+    // shrink so that every thread still has its pair (down to 256 KiB: below that the sequential reader finishes).
     const int64_t sb = par_bit_ >> 3;
-    if (size_ - sb < 3 * CHUNK) return false;       // not worth a round: the sequential reader finishes the file
-    const int T = (int) std::min<int64_t>(threads_, (size_ - sb) / CHUNK);
+    int64_t CHUNK = 2 << 20;
+    if (par_bit_ == 8 * piece_base_) CHUNK = 512 << 10;      // a member's first round is short: the scan behind it starts sooner
+    if (size_ - sb < 2 * (int64_t) threads_ * CHUNK) CHUNK = std::max<int64_t>(256 << 10, (size_ - sb) / (2 * (int64_t) threads_));
+    if (size_ - sb < 3 * CHUNK) return false;       // not worth a round
+    const int T = (int) std::min<int64_t>(2 * (int64_t) threads_, (size_ - sb) / CHUNK);      // chunks
+    const int W = (T + 1) / 2;                                                              // threads
     std::vector<Chunk> chunks((size_t) T);
     RoundCtx rc;
     rc.bits = Bits{f_, 8 * size_}; rc.file = f_; rc.fsize = size_; rc.piece_base = piece_base_;
@@ -623,11 +820,10 @@ inline bool FileDecoder::parallel_round(std::vector<std::vector<uint8_t>> &outs,
     rc.chunks = &chunks;
     chunks[0].start_bit = par_bit_;
     if ((int) cells_pool_.size() < T) cells_pool_.resize((size_t) T);
-    for (int i = 1; i < T; i++) chunks[(size_t) i].head.cells.swap(cells_pool_[(size_t) i]);
-    chunks[0].body = take_spare((size_t) 10 << 20);
+    for (int i = 0; i < T; i++) chunks[(size_t) i].head.cells.swap(cells_pool_[(size_t) i]);
     struct GiveBack {                               // the cell buffers go back to the pool whatever happens
-        std::vector<Chunk> &ch; std::vector<std::vector<uint16_t>> &pool; int T;
-        ~GiveBack() { for (int i = 1; i < T; i++) if (ch[(size_t) i].head.cells.capacity() > pool[(size_t) i].capacity()) ch[(size_t) i].head.cells.swap(pool[(size_t) i]); }
+        std::vector<Chunk> &ch; std::vector<Cells> &pool; int T;
+        ~GiveBack() { for (int i = 0; i < T; i++) if (ch[(size_t) i].head.cells.capacity() > pool[(size_t) i].capacity()) ch[(size_t) i].head.cells.swap(pool[(size_t) i]); }
     } give_back{chunks, cells_pool_, T};
     auto in_threads = [&](int n, const std::function<void(int)> &fn) {
         std::vector<std::thread> th;
@@ -642,9 +838,10 @@ inline bool FileDecoder::parallel_round(std::vector<std::vector<uint8_t>> &outs,
     const double t0 = now();
     // phase 0: the first block that starts in every chunk (looked for in the chunk's first quarter: deflate
     // blocks of text are tens of KB; data without such blocks -- stored, incompressible -- is not worth a round)
-    in_threads(T, [&](int i) {
-        if (i > 0) chunks[(size_t) i].start_bit = find_block_start(rc.bits, 8 * (sb + (int64_t) i * CHUNK),
-                                                                   std::min<int64_t>(8 * (sb + (int64_t) i * CHUNK + CHUNK / 4), 8 * size_ - 64));
+    in_threads(W, [&](int t) {
+        for (int i = std::max(1, 2 * t); i < std::min(T, 2 * t + 2); i++)
+            chunks[(size_t) i].start_bit = find_block_start(rc.bits, 8 * (sb + (int64_t) i * CHUNK),
+                                                            std::min<int64_t>(8 * (sb + (int64_t) i * CHUNK + CHUNK / 4), 8 * size_ - 64));
     });
     int found = 0;
     for (int i = 1; i < T; i++) found += chunks[(size_t) i].start_bit >= 0;
@@ -652,9 +849,16 @@ inline bool FileDecoder::parallel_round(std::vector<std::vector<uint8_t>> &outs,
     const double t1 = now();
     // phase 1: every chunk from its start to the next start it lands on
     const bool known0 = true;                       // chunk 0 starts at a known boundary with the history in window_ (empty at a member's start)
-    in_threads(T, [&](int i) {
-        try { decode_chunk(rc, chunks[(size_t) i], i, i == 0 && known0, window_.data(), (int) window_.size()); }
-        catch (...) { chunks[(size_t) i].ok = false; }
+    in_threads(W, [&](int t) {
+        const double ta = now();
+        ChunkRun x, y;
+        try {
+            x.start(rc, chunks[(size_t) (2 * t)], 2 * t, t == 0 && known0, window_.data(), (int) window_.size());
+            if (2 * t + 1 < T) y.start(rc, chunks[(size_t) (2 * t + 1)], 2 * t + 1, false, nullptr, 0);
+            decode_pair(x, y);
+        } catch (...) { chunks[(size_t) (2 * t)].ok = false; if (2 * t + 1 < T) chunks[(size_t) (2 * t + 1)].ok = false; }
+        chunks[(size_t) (2 * t)].ms = now() - ta;
+        if (2 * t + 1 < T) chunks[(size_t) (2 * t + 1)].ms = chunks[(size_t) (2 * t)].ms;
     });
     const double t2 = now();
     // phase 2a: chain the chunks in stream order (a start nobody lands on was a false positive); the 32 KiB in
@@ -671,8 +875,8 @@ inline bool FileDecoder::parallel_round(std::vector<std::vector<uint8_t>> &outs,
         Chunk &c = chunks[(size_t) order[k]];
         const std::vector<uint8_t> &w = wins[k];
         std::vector<uint8_t> &t = wins[k + 1];
-        const int64_t need_head = std::min<int64_t>(c.head.n, std::max<int64_t>(0, WSIZE - (int64_t) c.body.size()));
-        const int64_t need_prev = std::max<int64_t>(0, WSIZE - (int64_t) c.body.size() - c.head.n);
+        const int64_t need_head = std::min<int64_t>(c.head.n, WSIZE);
+        const int64_t need_prev = std::max<int64_t>(0, WSIZE - c.head.n);
         if (need_prev > 0) t.assign(w.end() - std::min<int64_t>(need_prev, (int64_t) w.size()), w.end());
         const int64_t have = (int64_t) w.size();
         for (int64_t q = c.head.n - need_head; q < c.head.n && !broken; q++) {
@@ -683,21 +887,41 @@ inline bool FileDecoder::parallel_round(std::vector<std::vector<uint8_t>> &outs,
             } else t.push_back((uint8_t) x);
         }
         if (broken) { order.resize(k); break; }      // (reaches in front of the member: not a valid stream; zlib will say so)
-        const size_t nb = std::min<size_t>(c.body.size(), (size_t) WSIZE);
-        t.insert(t.end(), c.body.end() - nb, c.body.end());
     }
     // phase 2b: markers -> bytes, every chunk of the chain on its own thread
-    std::vector<std::vector<uint8_t>> heads(order.size());
+    std::vector<Bytes> heads(order.size());
     for (size_t k = 0; k < order.size(); k++)
         if (chunks[(size_t) order[k]].head.n) heads[k] = take_spare((size_t) chunks[(size_t) order[k]].head.n);
     std::atomic<int> bad{0};
-    in_threads((int) order.size(), [&](int k) {
+    auto resolve_one = [&](int k) {
         Chunk &c = chunks[(size_t) order[(size_t) k]];
         if (c.head.n == 0) return;
         const std::vector<uint8_t> &w = wins[(size_t) k];
         const int64_t have = (int64_t) w.size();
-        std::vector<uint8_t> &hb = heads[(size_t) k];
+        Bytes &hb = heads[(size_t) k];
         const uint16_t *cells = c.head.cells.data();
+        if (have == WSIZE || k == 0) {
+            // the usual case, branch-free: one table look-up per cell (0..255 -> itself, 0x8000 | k -> window[k]);
+            // the round's first chunk holds no markers
+            Bytes lut(65536);
+            for (int v = 0; v < 256; v++) lut[(size_t) v] = (uint8_t) v;
+            if (have) memcpy(lut.data() + 0x8000 + (WSIZE - have), w.data(), (size_t) have);
+            const uint8_t *t = lut.data();
+            uint8_t *o = hb.data();
+            const int64_t n = c.head.n;
+            int64_t q = 0;
+#if defined(__SSE2__)
+            // 16 cells at a time: without a marker among them (4 groups in 5: markers are 5 % of the cells and sit
+            // in the header lines) they are narrowed in registers
+            for (; q + 16 <= n; q += 16) {
+                const __m128i a = _mm_loadu_si128((const __m128i *) (cells + q)), b = _mm_loadu_si128((const __m128i *) (cells + q + 8));
+                if ((_mm_movemask_epi8(_mm_or_si128(a, b)) & 0xAAAA) == 0) { _mm_storeu_si128((__m128i *) (o + q), _mm_packus_epi16(a, b)); continue; }
+                for (int j = 0; j < 16; j++) o[q + j] = t[cells[q + j]];
+            }
+#endif
+            for (; q < n; q++) o[q] = t[cells[q]];
+            return;
+        }
         for (int64_t q = 0; q < c.head.n; q++) {
             const uint16_t x = cells[q];
             if (x & 0x8000) {
@@ -706,13 +930,14 @@ inline bool FileDecoder::parallel_round(std::vector<std::vector<uint8_t>> &outs,
                 hb[(size_t) q] = w[(size_t) wi];
             } else hb[(size_t) q] = (uint8_t) x;
         }
-    });
+    };
+    in_threads(W, [&](int t) { for (int k = t; k < (int) order.size(); k += W) resolve_one(k); });
     const double t3 = now();
     if (trace) {
         fprintf(stderr, "[gz] round at byte %ld: search %.1f ms, decode %.1f ms, resolve %.1f ms, chain %zu of %d;", (long) sb, t1 - t0, t2 - t1, t3 - t2, order.size(), T);
         for (int i = 0; i < T; i++)
-            fprintf(stderr, " [%d: +%ld ok=%d head=%ld body=%zu land=%d]", i, (long) (chunks[(size_t) i].start_bit / 8 - sb - (int64_t) i * CHUNK),
-                    chunks[(size_t) i].ok, (long) chunks[(size_t) i].head.n, chunks[(size_t) i].body.size(), chunks[(size_t) i].landed);
+            fprintf(stderr, " [%d: +%ld ok=%d out=%ld land=%d %.1f ms]", i, (long) (chunks[(size_t) i].start_bit / 8 - sb - (int64_t) i * CHUNK),
+                    chunks[(size_t) i].ok, (long) chunks[(size_t) i].head.n, chunks[(size_t) i].landed, chunks[(size_t) i].ms);
         fprintf(stderr, "\n");
     }
     if (bad.load() || order.empty()) return false;
@@ -733,7 +958,6 @@ inline bool FileDecoder::parallel_round(std::vector<std::vector<uint8_t>> &outs,
         }
         at += c.out_size();
         if (!heads[k].empty()) outs.push_back(std::move(heads[k]));
-        if (!c.body.empty()) outs.push_back(std::move(c.body));
     }
     // the sequential state follows: block boundary end_bit, history = tail of the chain
     produced_ += round_out; par_bytes_ += round_out;

@@ -17,7 +17,7 @@ int main(int argc, char **argv)
     long long par = 0;
     try {
         FileDecoder d(file.data(), n, atoi(argv[1]));
-        std::vector<std::vector<uint8_t>> outs, spares;
+        std::vector<Bytes> outs, spares;
         bool more = true;
         while (more) {
             more = d.next(outs, ev, &spares);
