@@ -160,9 +160,19 @@ int kvq_comm_info(kvq_engine *e, int *rank, int *world, int *nccl_version);
  * writes the sums into r: coverage, mutcount, nseqhits, nseqbasehits, readlengths, records_parsed,
  * parsed, bases.  Hits stay per rank.  reduce_ms (may be NULL): device time of the collective. */
 int kvq_allreduce(kvq_engine *e, kvq_result *r, double *reduce_ms);
+/* kvq_scan_staged + kvq_allreduce in one call: the collective is enqueued right behind the scan kernels on
+ * its own stream (the tail of the row -- readlengths, records, bases -- is written by a kernel from the
+ * batch's device counters) and runs beside the kernels that order the hits; one host synchronisation per
+ * scan instead of two.  *out holds this rank's hits and the counters summed over all ranks.  Every rank of
+ * the communicator must make the call.  Should a rank have to run its batch again (survivor queue, line
+ * phases), every rank sees that in the sum and the collective is repeated.  Without a communicator: the
+ * same as kvq_scan_staged. */
+int kvq_scan_staged_reduce(kvq_engine *e, kvq_staged *st,
+                           const char *const *seqs, const int32_t *seqlens, int nseqs, int nplus,
+                           int want_hits, kvq_result **out, double *reduce_ms);
 /* Batch of isolates (docs/tutorial.rst:378 "hundreds of genomes"): [nslots][row] int64 matrix in HBM,
  * row = counters of one scan (kvq_job_row_words: nseqhits, nseqbasehits, coverage, mutcount[6],
- * readlengths[1024], records, bases, parsed, longest+1); each rank stores the isolates it scanned,
+ * readlengths[1024], records, bases, parsed, longest+1, 0); each rank stores the isolates it scanned,
  * one all-reduce at the end gives every rank the whole matrix. */
 int kvq_job_begin(kvq_engine *e, int nslots, int64_t row_words);
 int64_t kvq_job_row_words(kvq_engine *e);

@@ -52,6 +52,8 @@ SIGNATURES = {
     'kvq_stage_mem': (C.c_int, [VP, P(C.c_void_p), P(C.c_int64), C.c_int, P(VP)]),
     'kvq_scan_staged': (C.c_int, [VP, VP, P(C.c_char_p), P(C.c_int32), C.c_int, C.c_int, C.c_int,
                                   P(VP)]),
+    'kvq_scan_staged_reduce': (C.c_int, [VP, VP, P(C.c_char_p), P(C.c_int32), C.c_int, C.c_int, C.c_int,
+                                         P(VP), P(C.c_double)]),
     'kvq_staged_free': (None, [VP]),
     'kvq_host_alloc': (VP, [C.c_int64]),
     'kvq_host_free': (None, [VP]),

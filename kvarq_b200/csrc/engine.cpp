@@ -1066,8 +1066,9 @@ struct Slot {                           // one batch in flight
 
 struct Accum {                          // device-wide accumulators of one scan, one allocation:
     DevBuf d_all; size_t ns = 0, nc = 0;    // [nseqhits ns][nseqbasehits ns][coverage nc][mutcount 6 nc][tail]
-    // tail (filled from the host totals right before a reduce): [readlengths 1024][records][bases][parsed][longest + 1]
-    static constexpr size_t TAIL = KVQ_HIST + 4;
+    // tail (filled from the host totals right before a reduce, or by kvq_launch_tail): [readlengths 1024][records][bases]
+    // [parsed][longest + 1][ranks whose batch was not complete when the row was reduced]
+    static constexpr size_t TAIL = KVQ_HIST + 5;
     size_t row_words() const { return words() + TAIL; }
     unsigned long long *seqhits() const { return d_all.as<unsigned long long>(); }
     unsigned long long *seqbase() const { return seqhits() + ns; }
@@ -1102,7 +1103,9 @@ struct kvq_engine {
     std::unique_ptr<WorkPool> pool; int pool_threads = 0;      // reader threads (plain files)
     // multi-GPU: one NCCL communicator per engine (one engine per process and GPU)
     ncclComm_t comm = nullptr; int rank = 0, world = 1;
-    DevBuf d_job, d_max; int job_slots = 0; size_t job_row = 0; PinBuf pin_tail;               // page-locked staging of the result copies
+    DevBuf d_job, d_max; int job_slots = 0; size_t job_row = 0; PinBuf pin_tail;
+    // reduce behind the kernels (kvq_scan_staged_reduce): the collective runs on its own stream beside the ordering kernels
+    cudaStream_t red_stream = nullptr; cudaEvent_t ev_ra = nullptr, ev_rb = nullptr, ev_r0 = nullptr, ev_r1 = nullptr; DevBuf d_red;               // page-locked staging of the result copies
     SortScratch scratch;
 
     void set_error(int cls, const std::string &m) { std::lock_guard<std::mutex> g(mu); err_cls = cls; err_msg = m; }
@@ -1640,6 +1643,8 @@ void kvq_destroy(kvq_engine *e)
         if (s.ev_copied) cudaEventDestroy(s.ev_copied);
     }
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    if (e->red_stream) cudaStreamDestroy(e->red_stream);
+    for (cudaEvent_t ev : {e->ev_ra, e->ev_rb, e->ev_r0, e->ev_r1}) if (ev) cudaEventDestroy(ev);
     if (e->comm && kvq_nccl::api().CommDestroy) kvq_nccl::api().CommDestroy(e->comm);
     delete e;
 }
@@ -1799,10 +1804,19 @@ int kvq_stage_mem(kvq_engine *e, const char *const *bufs, const int64_t *buflens
     });
 }
 
-int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, const int32_t *seqlens,
-                    int nseqs, int nplus, int want_hits, kvq_result **out)
+} // extern "C"
+
+namespace {
+void nccl_check(ncclResult_t r, const char *what);
+kvq_nccl::Api &need_nccl();
+void unpack_reduced(kvq_engine *e, kvq_result *r, const int64_t *all);
+}
+
+static int scan_staged_impl(kvq_engine *e, kvq_staged *st, const char *const *seqs, const int32_t *seqlens,
+                            int nseqs, int nplus, int want_hits, kvq_result **out, bool reduce, double *reduce_ms)
 {
     if (out) *out = nullptr;
+    if (reduce_ms) *reduce_ms = 0;
     return guarded(e, [&] {
         if (!out || !st || st->e != e) throw KvqError(KVQ_ERR_TYPE, "bad staged stream");
         RunGuard run(e);
@@ -1830,7 +1844,30 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         KvqOut o = make_out(e, bufs_of(*st));
         enqueue_kernels(e, b, e->tpl.par, o, s0.stream, s0.ev0, s0.ev1);
         CK(cudaMemcpyAsync(s0.h_ctr.p, st->d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s0.stream));
-        {   // the per-template accumulators ride behind the kernels instead of a blocking copy later
+        const bool red = reduce && e->comm != nullptr;
+        const size_t row = e->acc.row_words();
+        auto enqueue_reduce = [&](cudaStream_t rs) {
+            // tail of the row from the batch's device counters, then the sum over the ranks into d_red (the rank's own
+            // row stays intact: a repeated collective needs it) and the sums to the host
+            kvq_nccl::Api &a = need_nccl();
+            cuda_check((cudaError_t) kvq_launch_tail(st->d_ctr.as<KvqCounters>(), e->acc.seqhits() + e->acc.words(), st->parsed,
+                                                     (unsigned long long) st->surv_cap, s0.stream), "tail kernel launch");
+            if (rs != s0.stream) { CK(cudaEventRecord(e->ev_ra, s0.stream)); CK(cudaStreamWaitEvent(rs, e->ev_ra, 0)); }
+            CK(cudaEventRecord(e->ev_r0, rs));
+            nccl_check(a.AllReduce(e->acc.d_all.p, e->d_red.p, row, ncclInt64, ncclSum, e->comm, rs), "ncclAllReduce");
+            CK(cudaEventRecord(e->ev_r1, rs));
+            CK(cudaMemcpyAsync(e->pin_acc.p, e->d_red.p, row * 8, cudaMemcpyDeviceToHost, rs));
+            if (rs != s0.stream) CK(cudaEventRecord(e->ev_rb, rs));
+        };
+        if (red) {
+            if (!e->red_stream) {
+                CK(cudaStreamCreateWithFlags(&e->red_stream, cudaStreamNonBlocking));
+                CK(cudaEventCreateWithFlags(&e->ev_ra, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&e->ev_rb, cudaEventDisableTiming));
+                CK(cudaEventCreate(&e->ev_r0)); CK(cudaEventCreate(&e->ev_r1));
+            }
+            e->d_red.ensure(row * 8); e->pin_acc.ensure(row * 8);
+            enqueue_reduce(e->red_stream);
+        } else {   // the per-template accumulators ride behind the kernels instead of a blocking copy later
             const bool want_cov = e->tpl.nplus > 0 && e->tpl.cov_total > 0;
             const size_t words = want_cov ? e->acc.words() : 2 * e->acc.ns;
             e->pin_acc.ensure(words * 8);
@@ -1865,6 +1902,7 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
             CK(cudaMemcpyAsync(e->pin_ord.p, ord.status, 4, cudaMemcpyDeviceToHost, s0.stream));
         }
         mark();
+        if (red) CK(cudaStreamWaitEvent(s0.stream, e->ev_rb, 0));
         CK(cudaStreamSynchronize(s0.stream));
         mark();
         float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1));
@@ -1873,6 +1911,23 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
         const int64_t launches0 = tot.launches;
         const KvqParams used = rerun_for_survivors(e, b, bufs_of(*st), c, s0.h_ctr, s0.stream, tot);
         add_counters(e, c, tot);
+        int red_launches = 0;
+        if (red) {
+            float rms = 0; CK(cudaEventElapsedTime(&rms, e->ev_r0, e->ev_r1));
+            red_launches += 2; tot.d2h += (int64_t) row * 8;
+            if (e->pin_acc.as<int64_t>()[e->acc.words() + KVQ_HIST + 4] != 0) {
+                // some rank's batch was not complete when its row went into the sum (it has run the batch again by now):
+                // every rank sees that in the sum, and every rank repeats the collective with its final row
+                enqueue_reduce(s0.stream);
+                CK(cudaStreamSynchronize(s0.stream));
+                float r2 = 0; CK(cudaEventElapsedTime(&r2, e->ev_r0, e->ev_r1)); rms += r2;
+                red_launches += 2; tot.d2h += (int64_t) row * 8;
+                if (e->pin_acc.as<int64_t>()[e->acc.words() + KVQ_HIST + 4] != 0)
+                    throw KvqError(KVQ_ERR_RUNTIME, "internal: a rank's batch is still incomplete in the repeated reduce");
+            }
+            tot.acc_fetched = true;
+            if (reduce_ms) *reduce_ms = rms;
+        }
         if (want_hits) {
             // ordered on the device unless the batch had to be run again or a buffer overflowed
             const bool ordered = dev_order && tot.launches == launches0 && c.hit_count <= st->hit_cap && c.blob_used <= st->blob_cap
@@ -1887,15 +1942,31 @@ int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, cons
                 collect_hits(e, b, bufs_of(*st), used, c, s0.stream, tot);
             }
         }
+        tot.launches += red_launches;           // (tail kernel + the collective's kernel)
         mark();
         if (tot.err_key != ~0ULL) throw KvqError(KVQ_ERR_FASTQ_FORMAT, format_error_message(tot.err_key));
         *out = finish_result(e, tot, now_ms() - t_begin);
+        if (red) unpack_reduced(e, *out, e->pin_acc.as<int64_t>());
         mark();
         if (trace) {
             fprintf(stderr, "[kvq trace] build %.3f reset %.3f enqueue %.3f sync %.3f hits %.3f finish %.3f (kernel %.3f)\n",
                     tp[0] - t_begin, tp[1] - tp[0], tp[2] - tp[1], tp[3] - tp[2], tp[4] - tp[3], tp[5] - tp[4], ms);
         }
     });
+}
+
+extern "C" {
+
+int kvq_scan_staged(kvq_engine *e, kvq_staged *st, const char *const *seqs, const int32_t *seqlens,
+                    int nseqs, int nplus, int want_hits, kvq_result **out)
+{
+    return scan_staged_impl(e, st, seqs, seqlens, nseqs, nplus, want_hits, out, false, nullptr);
+}
+
+int kvq_scan_staged_reduce(kvq_engine *e, kvq_staged *st, const char *const *seqs, const int32_t *seqlens,
+                           int nseqs, int nplus, int want_hits, kvq_result **out, double *reduce_ms)
+{
+    return scan_staged_impl(e, st, seqs, seqlens, nseqs, nplus, want_hits, out, true, reduce_ms);
 }
 
 void kvq_staged_free(kvq_staged *st) { delete st; }
@@ -1931,6 +2002,24 @@ kvq_nccl::Api &need_nccl()
     return a;
 }
 
+// the reduced row -> the result's counters
+void unpack_reduced(kvq_engine *e, kvq_result *r, const int64_t *all)
+{
+    const size_t ns = e->acc.ns, nc = e->acc.nc;
+    for (int i = 0; i < e->tpl.nseqs; i++) { r->nseqhits[i] = all[i]; r->nseqbasehits[i] = all[ns + i]; }
+    if (!r->coverage.empty()) {
+        r->coverage.assign(all + 2 * ns, all + 2 * ns + r->coverage.size());
+        r->mutcount.assign(all + 2 * ns + nc, all + 2 * ns + nc + r->mutcount.size());
+    }
+    const int64_t *t = all + e->acc.words();
+    // the longest read length is a maximum, not a sum: every rank's histogram is in the sum, so it is
+    // the last non-empty bin -- or, beyond the histogram (>= 1024, workhorse.c:397-400), left per rank
+    int64_t longest = -1;
+    for (int i = 0; i < KVQ_HIST; i++) { r->stats.readlengths[i] = t[i]; if (t[i]) longest = i; }
+    r->stats.rls_longest = std::max(r->stats.rls_longest, longest);
+    r->stats.records_parsed = t[KVQ_HIST]; r->timing.bases = t[KVQ_HIST + 1]; r->stats.parsed = t[KVQ_HIST + 2];
+}
+
 // host totals of the last scan -> tail of the device accumulator row (see Accum)
 void upload_tail(kvq_engine *e, const kvq_result *r, cudaStream_t st)
 {
@@ -1938,7 +2027,7 @@ void upload_tail(kvq_engine *e, const kvq_result *r, cudaStream_t st)
     int64_t *t = e->pin_tail.as<int64_t>();
     for (int i = 0; i < KVQ_HIST; i++) t[i] = r->stats.readlengths[i];
     t[KVQ_HIST] = r->stats.records_parsed; t[KVQ_HIST + 1] = r->timing.bases;
-    t[KVQ_HIST + 2] = r->stats.parsed; t[KVQ_HIST + 3] = r->stats.rls_longest + 1;
+    t[KVQ_HIST + 2] = r->stats.parsed; t[KVQ_HIST + 3] = r->stats.rls_longest + 1; t[KVQ_HIST + 4] = 0;
     CK(cudaMemcpyAsync(e->acc.seqhits() + e->acc.words(), t, Accum::TAIL * 8, cudaMemcpyHostToDevice, st));
 }
 
@@ -2021,20 +2110,7 @@ int kvq_allreduce(kvq_engine *e, kvq_result *r, double *reduce_ms)
         CK(cudaMemcpyAsync(e->pin_acc.p, e->acc.d_all.p, n * 8, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         if (reduce_ms) { float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1)); *reduce_ms = ms; }
-        const int64_t *all = e->pin_acc.as<int64_t>();
-        const size_t ns = e->acc.ns, nc = e->acc.nc;
-        for (int i = 0; i < e->tpl.nseqs; i++) { r->nseqhits[i] = all[i]; r->nseqbasehits[i] = all[ns + i]; }
-        if (!r->coverage.empty()) {
-            r->coverage.assign(all + 2 * ns, all + 2 * ns + r->coverage.size());
-            r->mutcount.assign(all + 2 * ns + nc, all + 2 * ns + nc + r->mutcount.size());
-        }
-        const int64_t *t = all + e->acc.words();
-        // the longest read length is a maximum, not a sum: every rank's histogram is in the sum, so it is
-        // the last non-empty bin -- or, beyond the histogram (>= 1024, workhorse.c:397-400), left per rank
-        int64_t longest = -1;
-        for (int i = 0; i < KVQ_HIST; i++) { r->stats.readlengths[i] = t[i]; if (t[i]) longest = i; }
-        r->stats.rls_longest = std::max(r->stats.rls_longest, longest);
-        r->stats.records_parsed = t[KVQ_HIST]; r->timing.bases = t[KVQ_HIST + 1]; r->stats.parsed = t[KVQ_HIST + 2];
+        unpack_reduced(e, r, e->pin_acc.as<int64_t>());
     });
 }
 

@@ -36,6 +36,9 @@
 #include <algorithm>
 #include <atomic>
 #include <functional>
+#include <memory>
+#include <mutex>
+#include <condition_variable>
 #include <stdexcept>
 #include <string>
 #include <thread>
@@ -638,6 +641,57 @@ inline void decode_chunk(const RoundCtx &rc, Chunk &c, int self, bool known, con
     decode_pair(x, none);
 }
 
+// ------------------------------------------------------------------------------- worker team
+// The threads of the parallel rounds, started once per file (three phases per round: starting sixteen threads
+// for each costs more than a millisecond of a 30 ms round).  run(n, fn): fn(0 .. n-1), fn(0) on the caller.
+class Team {
+public:
+    explicit Team(int n) { for (int i = 1; i < n; i++) th_.emplace_back([this, i] { work(i); }); }
+    ~Team() {
+        { std::lock_guard<std::mutex> g(mu_); quit_ = true; gen_++; }
+        cv_.notify_all();
+        for (auto &t : th_) t.join();
+    }
+    int size() const { return (int) th_.size() + 1; }
+    bool run(int n, const std::function<void(int)> &fn) {
+        n = std::min(n, size());
+        {
+            std::lock_guard<std::mutex> g(mu_);
+            fn_ = &fn; n_ = n; pending_ = n - 1; failed_ = 0; gen_++;
+        }
+        cv_.notify_all();
+        try { fn(0); } catch (...) { std::lock_guard<std::mutex> g(mu_); failed_++; }
+        std::unique_lock<std::mutex> g(mu_);
+        done_.wait(g, [&] { return pending_ == 0; });
+        fn_ = nullptr;
+        return failed_ == 0;
+    }
+private:
+    void work(int i) {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void(int)> *fn;
+            {
+                std::unique_lock<std::mutex> g(mu_);
+                cv_.wait(g, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (quit_) return;
+                if (i >= n_) continue;
+                fn = fn_;
+            }
+            bool bad = false;
+            try { (*fn)(i); } catch (...) { bad = true; }
+            std::lock_guard<std::mutex> g(mu_);
+            failed_ += bad;
+            if (--pending_ == 0) done_.notify_all();
+        }
+    }
+    std::vector<std::thread> th_;
+    std::mutex mu_; std::condition_variable cv_, done_;
+    const std::function<void(int)> *fn_ = nullptr;
+    int n_ = 0, pending_ = 0, failed_ = 0; uint64_t gen_ = 0; bool quit_ = false;
+};
+
 // ------------------------------------------------------------------------------- the file reader
 // One .gz file in memory -> its inflated bytes and the reference's read positions, in order.
 // The sequential part restates the round-1 GzFileSource (engine.cpp) on a memory buffer; parallel
@@ -794,6 +848,7 @@ private:
     }
     std::vector<Bytes> spare_;
     std::vector<Cells> cells_pool_;
+    std::unique_ptr<Team> team_;
 
     const uint8_t *f_; int64_t size_; int threads_;
     z_stream zs_; bool live_ = false;
@@ -825,14 +880,8 @@ inline bool FileDecoder::parallel_round(std::vector<Bytes> &outs, std::vector<Ev
         std::vector<Chunk> &ch; std::vector<Cells> &pool; int T;
         ~GiveBack() { for (int i = 0; i < T; i++) if (ch[(size_t) i].head.cells.capacity() > pool[(size_t) i].capacity()) ch[(size_t) i].head.cells.swap(pool[(size_t) i]); }
     } give_back{chunks, cells_pool_, T};
-    auto in_threads = [&](int n, const std::function<void(int)> &fn) {
-        std::vector<std::thread> th;
-        std::atomic<int> failed{0};
-        for (int i = 1; i < n; i++) th.emplace_back([&, i] { try { fn(i); } catch (...) { failed++; } });
-        try { fn(0); } catch (...) { failed++; }
-        for (auto &t : th) t.join();
-        return failed.load() == 0;
-    };
+    if (!team_) team_.reset(new Team(threads_));
+    auto in_threads = [&](int n, const std::function<void(int)> &fn) { return team_->run(n, fn); };
     const bool trace = getenv("KVQ_GZ_TRACE") != nullptr;
     auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     const double t0 = now();
@@ -879,12 +928,17 @@ inline bool FileDecoder::parallel_round(std::vector<Bytes> &outs, std::vector<Ev
         const int64_t need_prev = std::max<int64_t>(0, WSIZE - c.head.n);
         if (need_prev > 0) t.assign(w.end() - std::min<int64_t>(need_prev, (int64_t) w.size()), w.end());
         const int64_t have = (int64_t) w.size();
-        for (int64_t q = c.head.n - need_head; q < c.head.n && !broken; q++) {
-            const uint16_t x = c.head.cells[(size_t) q];
+        const size_t t0n = t.size();
+        t.resize(t0n + (size_t) need_head);
+        uint8_t *to = t.data() + t0n;
+        const uint16_t *from = c.head.cells.data() + (c.head.n - need_head);
+        for (int64_t q = 0; q < need_head; q++) {
+            const uint16_t x = from[q];
             if (x & 0x8000) {
                 const int64_t wi = (int64_t) (x & 0x7FFF) - (WSIZE - have);
-                if (wi < 0) broken = true; else t.push_back(w[(size_t) wi]);
-            } else t.push_back((uint8_t) x);
+                if (wi < 0) { broken = true; break; }
+                to[q] = w[(size_t) wi];
+            } else to[q] = (uint8_t) x;
         }
         if (broken) { order.resize(k); break; }      // (reaches in front of the member: not a valid stream; zlib will say so)
     }

@@ -192,3 +192,6 @@ struct KvqOrder {
 };
 
 int kvq_launch_order(const KvqBatch &b, const KvqOut &o, const KvqOrder &ord, void *stream);
+// tail of the accumulator row from the batch's device counters (see scan_kernel.cu); tail[KVQ_HIST + 4] = 1 when the
+// batch has to be run again (survivor queue overflow, contradicted line phase)
+int kvq_launch_tail(const KvqCounters *ctr, unsigned long long *tail, long long parsed, unsigned long long surv_cap, void *stream);

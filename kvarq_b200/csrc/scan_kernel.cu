@@ -1608,6 +1608,28 @@ int kvq_launch_order(const KvqBatch &b, const KvqOut &o, const KvqOrder &ord, vo
     return (int) cudaGetLastError();
 }
 
+// ---- tail of the accumulator row (multi-GPU scans that reduce their counters right behind the kernels) ----
+// [readlengths KVQ_HIST][records][bases][parsed][longest + 1][this rank's batch has to be run again]: what the
+// host adds to the row before a reduce (engine.cpp:upload_tail), written from the batch's device counters so
+// that the all-reduce can be enqueued before the host has seen them.
+namespace {
+__global__ void kvq_tail_kernel(const KvqCounters *ctr, unsigned long long *tail, long long parsed, unsigned long long surv_cap)
+{
+    for (int i = threadIdx.x; i < KVQ_HIST; i += blockDim.x) tail[i] = ctr->rls[i];
+    if (threadIdx.x == 0) {
+        tail[KVQ_HIST] = ctr->records; tail[KVQ_HIST + 1] = ctr->bases; tail[KVQ_HIST + 2] = (unsigned long long) parsed;
+        tail[KVQ_HIST + 3] = (unsigned long long) (ctr->longest + 1);
+        tail[KVQ_HIST + 4] = (ctr->surv_count > surv_cap || ctr->phase_retry) ? 1ull : 0ull;
+    }
+}
+} // namespace
+
+int kvq_launch_tail(const KvqCounters *ctr, unsigned long long *tail, long long parsed, unsigned long long surv_cap, void *stream)
+{
+    kvq_tail_kernel<<<1, 256, 0, (cudaStream_t) stream>>>(ctr, tail, parsed, surv_cap);
+    return (int) cudaGetLastError();
+}
+
 // ---- hit ordering without any allocation (kvq_order_hits_static, include/kvarq_b200.h) ----------
 // No counterpart in the reference; added for callers that
 // cannot call cudaMalloc (CUDA graph capture, tight serving loops).  A single-block variant of the

@@ -269,17 +269,28 @@ class Engine(object):
             self._raise(rc)
         return Staged(self, st)
 
-    def scan_staged(self, staged, seqlist, nplus=0, want_hits=True, convert=None):
+    def scan_staged(self, staged, seqlist, nplus=0, want_hits=True, convert=None, reduce=False):
         """want_hits=False: the kernels only count hits (no hit records / hitseqs written);
         convert=False: hits are produced and copied back but not turned into Python tuples;
-        convert='timing': only nhits, records_parsed and the timing block are read."""
+        convert='timing': only nhits, records_parsed and the timing block are read;
+        reduce=True (every rank of the communicator must make the call): the counters of the result
+        are the sums over all ranks -- the all-reduce runs behind the scan kernels, beside the
+        ordering of this rank's hits (kvq_scan_staged_reduce); timing['reduce_ms'] = its device time."""
         _, arr, lens, n = self._seq_args(seqlist)
         res = C.c_void_p()
-        rc = self._lib.kvq_scan_staged(self._h, staged._h, arr, lens, n, nplus, 1 if want_hits else 0,
-                                       C.byref(res))
+        if reduce:
+            ms = C.c_double()
+            rc = self._lib.kvq_scan_staged_reduce(self._h, staged._h, arr, lens, n, nplus, 1 if want_hits else 0,
+                                                  C.byref(res), C.byref(ms))
+        else:
+            rc = self._lib.kvq_scan_staged(self._h, staged._h, arr, lens, n, nplus, 1 if want_hits else 0,
+                                           C.byref(res))
         if rc != 0:
             self._raise(rc)
-        return self._take_result(res, want_hits if convert is None else convert)
+        out = self._take_result(res, want_hits if convert is None else convert)
+        if reduce:
+            out.timing['reduce_ms'] = ms.value
+        return out
 
     # -- multi-GPU: one engine per process and GPU, NCCL inside the library (SURVEY 8e) -------
     @staticmethod

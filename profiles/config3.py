@@ -4,7 +4,7 @@ scanned end to end from the two .fastq.gz files (host inflate -> pinned batches 
 KVQ_C3_PAIRS pairs (default: the stated 1 764 613 = 200x, 2 x 0.92 GB FastQ).  Prints one line per
 input kind: the same reads as plain files, as single-member gz (chunk-parallel inflate, gz_parallel.h),
 as single-member gz with one zlib stream per file (KVQ_GZ_THREADS=1, the round-1 path) and -- with
-KVQ_C3_GZM=1 -- as multi-member gz (one member per 16 MiB).
+KVQ_C3_GZM=1 -- as multi-member gz (one member per 16 MiB); KVQ_C3_SWEEP=12,14 adds lines with that many inflate threads.
 Parity at this size: hits / hitseqs / stats of every gz scan == those of the plain-file scan of the same
 reads (the plain path is pinned to the reference by tests/), and the first KVQ_C3_ORACLE_PAIRS pairs,
 gzipped on their own, are checked against the CPU checker (oracle/, nthreads = cores).
@@ -70,14 +70,15 @@ def main():
     e.config(nthreads=os.cpu_count() or 8, **CFG)
     ref = None
     kinds = [('plain', 'plain', None), ('gz', 'gz', None), ('gz-1thread', 'gz', '1')] + ([('gzm', 'gzm', None)] if gzm else [])
+    kinds += [('gz-%sthreads' % n, 'gz', n) for n in os.environ.get('KVQ_C3_SWEEP', '').split(',') if n]      # inflate thread sweep
     for name, key, threads in kinds:
         files = [m[key] for m in mates]
         if threads:
             os.environ['KVQ_GZ_THREADS'] = threads
         else:
             os.environ.pop('KVQ_GZ_THREADS', None)
-        reps = 1 if threads else 3
-        if not threads:
+        reps = 1 if threads == '1' else 3
+        if threads != '1':
             e.findseqs(files, seqs, nplus=ts.nplus, convert=False)             # warm-up (page cache, tables)
         t = []
         for _ in range(reps):

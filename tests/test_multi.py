@@ -164,4 +164,34 @@ def test_engine_job_rows_and_allreduce_single_rank(tmp_path):
     red = e.allreduce()
     assert red.coverage.tolist() == r.coverage.tolist() and red['stats'] == r['stats']
     assert red.timing['reduce_ms'] > 0
+    # the one-call form (kvq_scan_staged_reduce: the collective enqueued behind the scan kernels, tail of the row
+    # written on the device) gives the same hits and the same counters -- also when the batch has to be run
+    # again because the survivor queue overflowed (the collective is repeated then)
+    st = e.stage([fq])
+    plain = e.scan_staged(st, ts.seqs(), nplus=ts.nplus)
+    fused = e.scan_staged(st, ts.seqs(), nplus=ts.nplus, reduce=True)
+    assert fused['hits'] == plain['hits'] == r['hits'] and fused['hitseqs'] == plain['hitseqs']
+    assert fused['stats'] == plain['stats'] and fused.coverage.tolist() == plain.coverage.tolist()
+    assert fused.mutcount.tolist() == plain.mutcount.tolist() and fused.timing['reduce_ms'] > 0
+    e.close()
+
+
+@pytest.mark.gpu
+def test_fused_reduce_repeats_the_collective_after_a_rerun(monkeypatch):
+    """KVQ_SURV_CAP=16: the first pass overflows the survivor queue, the rank runs the batch again; its row in the
+    first sum carries the 'incomplete' flag, so the collective is made a second time with the final counters"""
+    from kvarq_b200 import synth
+    from kvarq_b200.engine import Engine
+    monkeypatch.setenv('KVQ_SURV_CAP', '16')
+    g = synth.genome(150000, seed=31)
+    ts = synth.mtbc_templates(g, seed=32)
+    fq = synth.fastq_reads(synth.isolate(g, ts, seed=52), 4000, readlen=150, seed=62)
+    e = Engine(0)
+    e.config(maxerrors=2, minoverlap=25, minreadlength=25, Amin='.')
+    e.comm_init(Engine.unique_id(), 0, 1)
+    st = e.stage([fq])
+    fused = e.scan_staged(st, ts.seqs(), nplus=ts.nplus, reduce=True)
+    plain = e.scan_staged(st, ts.seqs(), nplus=ts.nplus)
+    assert len(fused['hits']) > 50 and fused['hits'] == plain['hits'] and fused['stats'] == plain['stats']
+    assert fused.coverage.tolist() == plain.coverage.tolist() and fused.timing['launches'] >= plain.timing['launches']
     e.close()
