@@ -6,6 +6,7 @@
 #include <zlib.h>
 #include <fcntl.h>
 #include <unistd.h>
+#include <math.h>
 #include <sys/stat.h>
 #include <sys/mman.h>
 #include <set>
@@ -1559,7 +1560,10 @@ kvq_result *run_stream_scan(kvq_engine *e, std::vector<std::string> names,
     // a format error lies in data already scanned, i.e. before whatever stopped the reader
     if (tot.err_key != ~0ULL) throw KvqError(KVQ_ERR_FASTQ_FORMAT, format_error_message(tot.err_key));
     if (producer_err) throw *producer_err;
-    return finish_result(e, tot, now_ms() - t_begin);
+    if (trace_stream) fprintf(stderr, "[kvq trace] stream scan: begin t=%.1f, batches done t=%.1f\n", fmod(t_begin, 1e6), fmod(now_ms(), 1e6));
+    kvq_result *res = finish_result(e, tot, now_ms() - t_begin);
+    if (trace_stream) fprintf(stderr, "[kvq trace] stream scan: result t=%.1f\n", fmod(now_ms(), 1e6));
+    return res;
 }
 
 } // namespace

@@ -32,6 +32,7 @@
 #include <zlib.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <math.h>
 #include <chrono>
 #include <algorithm>
 #include <atomic>
@@ -988,7 +989,7 @@ inline bool FileDecoder::parallel_round(std::vector<Bytes> &outs, std::vector<Ev
     in_threads(W, [&](int t) { for (int k = t; k < (int) order.size(); k += W) resolve_one(k); });
     const double t3 = now();
     if (trace) {
-        fprintf(stderr, "[gz] round at byte %ld: search %.1f ms, decode %.1f ms, resolve %.1f ms, chain %zu of %d;", (long) sb, t1 - t0, t2 - t1, t3 - t2, order.size(), T);
+        fprintf(stderr, "[gz] t=%.1f round at byte %ld: search %.1f ms, decode %.1f ms, resolve %.1f ms, chain %zu of %d;", fmod(t0, 1e6), (long) sb, t1 - t0, t2 - t1, t3 - t2, order.size(), T);
         for (int i = 0; i < T; i++)
             fprintf(stderr, " [%d: +%ld ok=%d out=%ld land=%d %.1f ms]", i, (long) (chunks[(size_t) i].start_bit / 8 - sb - (int64_t) i * CHUNK),
                     chunks[(size_t) i].ok, (long) chunks[(size_t) i].head.n, chunks[(size_t) i].landed, chunks[(size_t) i].ms);
