@@ -9,6 +9,9 @@
 #include <math.h>
 #include <sys/stat.h>
 #include <sys/mman.h>
+#if defined(__x86_64__)
+#include <immintrin.h>
+#endif
 #include <set>
 #include <functional>
 #include <stdint.h>
@@ -149,8 +152,38 @@ struct MemSource : Source {
     const char *direct() const override { return p + at; }
 };
 
+// Copy out of a mapped file into a batch buffer with non-temporal stores: the destination is page-locked memory
+// the GPU reads by DMA next, so there is no point in pulling its lines into the cache first (read-for-ownership
+// is a third of a plain copy's DRAM traffic).  Measured against pread() on the same threads: 1.4x
+// (profiles/microbench/read_modes.cpp).
+#if defined(__x86_64__)
+__attribute__((target("avx2"))) void stream_copy_avx2(char *dst, const char *src, size_t n)
+{
+    size_t head = (size_t) (-(intptr_t) dst & 31);
+    if (head > n) head = n;
+    memcpy(dst, src, head);
+    size_t i = head;
+    for (; i + 128 <= n; i += 128) {
+        const __m256i a = _mm256_loadu_si256((const __m256i *) (src + i)), b = _mm256_loadu_si256((const __m256i *) (src + i + 32));
+        const __m256i c = _mm256_loadu_si256((const __m256i *) (src + i + 64)), d = _mm256_loadu_si256((const __m256i *) (src + i + 96));
+        _mm256_stream_si256((__m256i *) (dst + i), a); _mm256_stream_si256((__m256i *) (dst + i + 32), b);
+        _mm256_stream_si256((__m256i *) (dst + i + 64), c); _mm256_stream_si256((__m256i *) (dst + i + 96), d);
+    }
+    _mm_sfence();
+    memcpy(dst + i, src + i, n - i);
+}
+void stream_copy(char *dst, const char *src, size_t n)
+{
+    static const bool avx2 = __builtin_cpu_supports("avx2");
+    if (avx2 && n >= 4096) stream_copy_avx2(dst, src, n); else memcpy(dst, src, n);
+}
+#else
+void stream_copy(char *dst, const char *src, size_t n) { memcpy(dst, src, n); }
+#endif
+
 struct PlainFileSource : Source {
     int fd; int64_t size, pos = 0; WorkPool *pool;
+    const char *map = nullptr;          // the file mapped (regular files; KVQ_READ_MMAP=0: pread instead)
     // file bytes [stg_off, stg_off + stg_len) already in memory at stg_ptr (the batch buffer, or `spill`)
     char *stg_ptr = nullptr; int64_t stg_off = 0, stg_len = 0; std::vector<char> spill;
     PlainFileSource(const char *name, WorkPool *pool_) : pool(pool_) {
@@ -158,9 +191,18 @@ struct PlainFileSource : Source {
         struct stat st;
         if (fd < 0 || fstat(fd, &st) != 0) { if (fd >= 0) close(fd); throw KvqError(KVQ_ERR_IO, "cannot open file"); }   // workhorse.c:577
         size = (int64_t) st.st_size;
+        static const bool use_map = !(getenv("KVQ_READ_MMAP") && atoi(getenv("KVQ_READ_MMAP")) == 0);
+        if (use_map && S_ISREG(st.st_mode) && size > 0) {
+            void *m = mmap(nullptr, (size_t) size, PROT_READ, MAP_SHARED, fd, 0);
+            if (m != MAP_FAILED) { map = (const char *) m; madvise(m, (size_t) size, MADV_SEQUENTIAL); }
+        }
     }
-    ~PlainFileSource() override { if (fd >= 0) close(fd); }
-    static void read_range(int fd, char *dst, int64_t off, int64_t n) {
+    ~PlainFileSource() override { if (map) munmap((void *) map, (size_t) size); if (fd >= 0) close(fd); }
+    void read_range(int fd, char *dst, int64_t off, int64_t n) const {
+        if (map) {                          // (the mapping ends at `size`; callers never ask for more)
+            stream_copy(dst, map + off, (size_t) n);
+            return;
+        }
         while (n > 0) {
             const ssize_t m = pread(fd, dst, (size_t) n, (off_t) off);
             if (m < 0) throw KvqError(KVQ_ERR_IO, "error while reading from file in fastq_read");   // :894
@@ -359,7 +401,7 @@ public:
             kvq_gz::Bytes &bk = blocks_.front();
             const int64_t m = std::min<int64_t>(cap - got, (int64_t) bk.size() - front_off_);
             g.unlock();
-            memcpy(dst + got, bk.data() + front_off_, (size_t) m);
+            stream_copy(dst + got, (const char *) bk.data() + front_off_, (size_t) m);
             g.lock();
             got += m; front_off_ += m; buffered_ -= m;
             if (front_off_ == (int64_t) bk.size()) {
@@ -1496,9 +1538,14 @@ kvq_result *run_stream_scan(kvq_engine *e, std::vector<std::string> names,
         if (!names.empty() && (!e->pool || e->pool_threads != want)) { e->pool.reset(new WorkPool(want - 1)); e->pool_threads = want; }
     }
     int inflate_threads;
-    {   // inflate threads: engine.config(nthreads) when set (> 1), else the machine's cores; KVQ_GZ_THREADS overrides (1: one zlib stream per file)
+    {   // inflate threads: engine.config(nthreads) when set (> 1), else the machine's hardware threads -- but two of those are
+        // left to the thread that copies the inflated bytes into the batches and to the one that drives the GPU (measured,
+        // config 3 on a 16-thread host: 16 inflate threads 1.88 Gbp/s, 14: 2.07); KVQ_GZ_THREADS overrides (1: one zlib
+        // stream per file)
         kvq_config_t cfg; { std::lock_guard<std::mutex> g(e->mu); cfg = e->cfg; }
-        inflate_threads = cfg.nthreads > 1 ? cfg.nthreads : (int) std::max(1u, std::thread::hardware_concurrency());
+        const int hw = (int) std::max(1u, std::thread::hardware_concurrency());
+        inflate_threads = cfg.nthreads > 1 ? cfg.nthreads : hw;
+        if (hw >= 8) inflate_threads = std::min(inflate_threads, hw - 2);
         if (const char *v = getenv("KVQ_GZ_THREADS")) inflate_threads = atoi(v);
         inflate_threads = std::max(1, std::min(inflate_threads, 128));
     }
