@@ -201,6 +201,11 @@ struct PlainFileSource : Source {
     void read_range(int fd, char *dst, int64_t off, int64_t n) const {
         if (map) {                          // (the mapping ends at `size`; callers never ask for more)
             stream_copy(dst, map + off, (size_t) n);
+            // the pages are not needed again: dropping them from the page table here, on the reader threads, keeps the
+            // final munmap from walking a gigabyte of entries on one thread (8 ms per GB after the last batch)
+            static const int64_t page = (int64_t) sysconf(_SC_PAGESIZE);
+            const int64_t a = (off + page - 1) / page * page, b = (off + n) / page * page;
+            if (b - a >= (64 << 10)) madvise((void *) (map + a), (size_t) (b - a), MADV_DONTNEED);
             return;
         }
         while (n > 0) {
@@ -622,14 +627,20 @@ public:
         int64_t win = 0;
         // plain files: everything this batch can take is read now, by all reader threads, to where
         // the fill() calls below expect it (they find it in place and copy nothing)
-        if (!finished_ && src_ && !b.borrowed) src_->preload(b.data + left, BATCH_BYTES - left);
+        static const bool trace = getenv("KVQ_TRACE") != nullptr;
+        const double tb0 = trace ? now_ms() : 0;
+        // the first batches of a scan are short (8, 24 MiB, then 64): the GPU has its first bytes after 0.3 ms instead of 2.4
+        const int64_t room = std::max<int64_t>(2 * REF_CHUNK, batch_no_ == 0 ? (8ll << 20) : batch_no_ == 1 ? (24ll << 20) : BATCH_BYTES);
+        batch_no_++;
+        if (!finished_ && src_ && !b.borrowed) src_->preload(b.data + left, room - left);
+        const double tb1 = trace ? now_ms() : 0;
         while (!finished_) {
             if (stop.load(std::memory_order_relaxed)) { finished_ = true; left = 0; break; }
-            if (win + REF_CHUNK > BATCH_BYTES) break;                       // batch full
+            if (win + REF_CHUNK > room) break;                              // batch full
             if (at_eof_ && next_file_ < nfiles_) {                          // :749-753
                 if (b.borrowed) break;                                      // next buffer = next batch
                 open_next();
-                src_->preload(b.data + win + left, BATCH_BYTES - win - left);
+                src_->preload(b.data + win + left, room - win - left);
             }
             at_eof_ = false;
             bool filled = false;
@@ -661,6 +672,7 @@ public:
         if (src_) src_->end_batch();
         b.nbytes = win;
         if (!b.borrowed) memset(b.data + win, 0, BATCH_PAD);
+        if (trace) fprintf(stderr, "[kvq trace] producer t=%.3f: preload %.3f ms, cut %.3f ms, %ld bytes\n", fmod(tb0, 1e6), tb1 - tb0, now_ms() - tb1, (long) win);
         return win > 0;
     }
 
@@ -704,7 +716,7 @@ private:
     LiveStats *live_;
     WorkPool *pool_ = nullptr; int gz_threads_ = 1;
     std::shared_ptr<GzGate> gate_;
-    int nfiles_ = 0, next_file_ = 0;
+    int nfiles_ = 0, next_file_ = 0, batch_no_ = 0;
     std::unique_ptr<Source> src_;
     bool at_eof_ = false, compressed_ = false, finished_ = false;
     int64_t size_all_ = 0, done_disk_ = 0, fpos_ = 0;
@@ -1582,8 +1594,8 @@ kvq_result *run_stream_scan(kvq_engine *e, std::vector<std::string> names,
                 int done = inflight.front(); inflight.pop_front();
                 harvest_slot(e, e->slots[done], tot);
                 if (trace_stream)
-                    fprintf(stderr, "[kvq trace] t %.3f wait-ready %.3f launch %.3f harvest %.3f\n",
-                            tq0 - t_begin, tq1 - tq0, tq2 - tq1, now_ms() - tq2);
+                    fprintf(stderr, "[kvq trace] consumer t=%.3f: wait-ready %.3f launch %.3f harvest %.3f\n",
+                            fmod(tq0, 1e6), tq1 - tq0, tq2 - tq1, now_ms() - tq2);
                 free_q.push(done);
                 if (tot.err_key != ~0ULL) e->stop = 1;          // first format error ends the scan
             }
