@@ -730,6 +730,7 @@ public:
     {
         if (spares) { for (auto &b : *spares) if (spare_.size() < 64) spare_.push_back(std::move(b)); spares->clear(); }
         if (done_) return false;
+        if (small_members_ && at_member_start_ && threads_ > 1 && member_round(outs, ev)) return true;
         if (par_ok_ && threads_ > 1) {
             if (parallel_round(outs, ev)) return true;
             par_ok_ = false;
@@ -771,7 +772,8 @@ private:
     {
         piece_base_ = data_at;
         member_out0_ = produced_;
-        par_ok_ = true; par_bit_ = 8 * data_at; window_.clear();
+        par_ok_ = !small_members_; par_bit_ = 8 * data_at; window_.clear();
+        at_member_start_ = true;
     }
 
     // ---- the reference's reader (workhorse.c:781-885), zlib instead of miniz
@@ -782,6 +784,7 @@ private:
         zs_.next_out = dst; zs_.avail_out = (uInt) cap;
         do {
             if (zs_.avail_in == 0) {
+                at_member_start_ = false;
                 const int64_t m = std::min<int64_t>(PIECE, remaining_);
                 if (rd_ + m > size_) throw Error(true, "could not read enough bytes from .fastq.gz");
                 zs_.next_in = const_cast<Bytef *>(f_ + rd_); zs_.avail_in = (uInt) m;
@@ -836,6 +839,7 @@ private:
     }
 
     bool parallel_round(std::vector<Bytes> &outs, std::vector<Event> &ev);
+    bool member_round(std::vector<Bytes> &outs, std::vector<Event> &ev);
 
     Bytes take_spare(size_t n)       // a buffer of n bytes, from the spares when one is large enough
     {
@@ -854,7 +858,7 @@ private:
     const uint8_t *f_; int64_t size_; int threads_;
     z_stream zs_; bool live_ = false;
     int64_t rd_ = 0, remaining_ = 0, produced_ = 0, piece_base_ = 0, member_out0_ = 0, par_bytes_ = 0;
-    bool done_ = false, par_ok_ = false;
+    bool done_ = false, par_ok_ = false, small_members_ = false, at_member_start_ = false; int short_rounds_ = 0;
     int64_t par_bit_ = 0; std::vector<uint8_t> window_;
 };
 
@@ -1015,11 +1019,122 @@ inline bool FileDecoder::parallel_round(std::vector<Bytes> &outs, std::vector<Ev
         if (!heads[k].empty()) outs.push_back(std::move(heads[k]));
     }
     // the sequential state follows: block boundary end_bit, history = tail of the chain
-    produced_ += round_out; par_bytes_ += round_out;
+    produced_ += round_out; par_bytes_ += round_out; at_member_start_ = false;
+    // A round that ran into the member's final block after a fraction of what its threads decoded: members much
+    // shorter than a round (BGZF: 64 KiB each).  More rounds would decode megabytes to keep kilobytes, so the rest of
+    // the file goes through the sequential reader.
+    if (chunks[(size_t) order.back()].at_final && round_out < (int64_t) T * CHUNK / 2 && ++short_rounds_ >= 2) small_members_ = true;
     par_bit_ = chunks[(size_t) order.back()].end_bit;
     window_.swap(wins[order.size()]);
     if (broken) par_ok_ = false;                    // what the chain has is good; the rest of the member goes sequentially
     if (!par_ok_) handover(par_bit_);
+    return true;
+}
+
+// Files made of many short members (BGZF and the .fastq.gz of Illumina's converters: one member per <= 64 KiB;
+// detected by parallel_round): members are independent streams, so a round decodes every member that starts in
+// the next stretch of the file on its own -- candidates are the places where a valid member header stands --
+// and chains them the way the reference walks from member to member (end of the deflate data, <= 10 bytes of
+// junk (the trailer), next header: workhorse.c:842-866).  A candidate nobody arrives at was not a member.  The
+// read positions follow from the layout: every member here lies inside the first 1 MiB piece read at its start.
+// State on entry and on return true: at a member's data start, nothing of it read (as after fill()'s `at_member`).
+inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Event> &ev)
+{
+    const int64_t P = rd_;                                          // data start of the current member
+    constexpr int64_t STRETCH = 1 << 20, MARGIN = 2 << 20;          // per thread; the end of the file is the sequential reader's
+    const int64_t scan_end = std::min(size_ - MARGIN, P + (int64_t) threads_ * STRETCH);
+    if (scan_end <= P + 4096) return false;
+    struct Cand { int64_t data, end = -1; size_t off = 0, len = 0; bool ok = false; };
+    std::vector<Cand> cand;
+    cand.push_back(Cand{P});
+    for (int64_t q = P; q + 18 < scan_end; q++) {
+        if (f_[q] != 0x1F || f_[q + 1] != 0x8B || f_[q + 2] != 8 || (f_[q + 3] & (0x02 | 0x20 | 0xC0))) continue;
+        int64_t d = q;
+        if (skip_header(d, 0) == nullptr && d < scan_end && d > P) cand.push_back(Cand{d});
+    }
+    if (cand.size() < 4) return false;                              // not that kind of file after all
+    if (!team_) team_.reset(new Team(threads_));
+    const int W = (int) std::min<size_t>((size_t) threads_, cand.size());
+    std::vector<Bytes> bufs((size_t) W);
+    for (int t = 0; t < W; t++) bufs[(size_t) t] = take_spare((size_t) 4 << 20);
+    auto range = [&](int t) { return std::make_pair(cand.size() * (size_t) t / (size_t) W, cand.size() * (size_t) (t + 1) / (size_t) W); };
+    team_->run(W, [&](int t) {
+        z_stream z; memset(&z, 0, sizeof(z));
+        if (inflateInit2(&z, -15) != Z_OK) return;
+        Bytes &buf = bufs[(size_t) t];
+        size_t used = 0;
+        const auto r = range(t);
+        for (size_t i = r.first; i < r.second; i++) {
+            Cand &c = cand[i];
+            inflateReset2(&z, -15);
+            const int64_t lim = std::min(size_, c.data + PIECE);    // the member must end inside the piece read at its start
+            z.next_in = const_cast<Bytef *>(f_ + c.data); z.avail_in = (uInt) (lim - c.data);
+            c.off = used;
+            for (;;) {
+                if (buf.size() - used < (256u << 10)) buf.resize(buf.size() * 2);
+                z.next_out = buf.data() + used; z.avail_out = (uInt) std::min<size_t>(buf.size() - used, 1u << 30);
+                const uInt out0 = z.avail_out;
+                const int st = inflate(&z, Z_NO_FLUSH);
+                used += out0 - z.avail_out;
+                if (st == Z_STREAM_END) { c.ok = true; c.end = lim - (int64_t) z.avail_in; break; }
+                if (st != Z_OK || (z.avail_in == 0 && z.avail_out != 0) || used - c.off > ((size_t) 64 << 20)) break;
+            }
+            if (!c.ok) used = c.off;
+            c.len = used - c.off;
+        }
+        inflateEnd(&z);
+    });
+    // chain from the current member on
+    std::vector<size_t> chain;
+    size_t cur = 0;
+    int64_t next_data = -1;
+    for (;;) {
+        const Cand &c = cand[cur];
+        if (!c.ok || size_ - c.end <= MARGIN) break;
+        int64_t d = c.end;
+        if (skip_header(d, 10) != nullptr) break;                   // (the sequential reader ends the stream there)
+        chain.push_back(cur); next_data = d;
+        size_t nxt = cur + 1;
+        while (nxt < cand.size() && cand[nxt].data < d) nxt++;
+        if (nxt >= cand.size() || cand[nxt].data != d) break;
+        cur = nxt;
+    }
+    if (chain.empty()) { for (auto &b : bufs) if (spare_.size() < 64) spare_.push_back(std::move(b)); return false; }
+    // events and output in stream order
+    int64_t out = produced_;
+    ev.push_back(Event{out, std::min(size_, P + std::min<int64_t>(PIECE, size_ - P)), false});    // the piece read at the current member's start
+    for (size_t k = 0; k < chain.size(); k++) {
+        const Cand &c = cand[chain[k]];
+        out += (int64_t) c.len;
+        const int64_t d = k + 1 < chain.size() ? cand[chain[k + 1]].data : next_data;
+        ev.push_back(Event{out, d, true});
+        if (k + 1 < chain.size()) ev.push_back(Event{out, std::min(size_, d + std::min<int64_t>(PIECE, size_ - d)), false});
+    }
+    size_t k = 0;
+    for (int t = 0; t < W && k < chain.size(); t++) {
+        const auto r = range(t);
+        // the thread's members that are in the chain, in order; usually all of them, back to back in its buffer
+        size_t k0 = k; bool whole = true; size_t expect = 0;
+        while (k < chain.size() && chain[k] < r.second) {
+            if (cand[chain[k]].off != expect) whole = false;
+            expect = cand[chain[k]].off + cand[chain[k]].len; k++;
+        }
+        if (k == k0) continue;
+        Bytes &buf = bufs[(size_t) t];
+        if (whole) { buf.resize(expect); if (expect) outs.push_back(std::move(buf)); }
+        else {
+            Bytes b2;
+            for (size_t j = k0; j < k; j++) b2.insert(b2.end(), buf.begin() + (long) cand[chain[j]].off, buf.begin() + (long) (cand[chain[j]].off + cand[chain[j]].len));
+            if (!b2.empty()) outs.push_back(std::move(b2));
+        }
+    }
+    par_bytes_ += out - produced_;
+    produced_ = out;
+    // the sequential state: at the data start of the member behind the chain, nothing of it read
+    inflateReset2(&zs_, -15);
+    zs_.avail_in = 0;
+    rd_ = next_data; remaining_ = size_ - next_data;
+    member_start(next_data);
     return true;
 }
 

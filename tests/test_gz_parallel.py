@@ -80,3 +80,43 @@ def test_parallel_equals_sequential(harness, tmp_path):
         if name in ('level6', 'level1', 'level9', 'members'):
             assert nb > 0.4 * len(seq), name + ': the parallel path was not taken'
     assert used_parallel >= 5
+
+
+def bgzf(data, block=65280, junk=b''):
+    """BGZF: one gzip member per <= 64 KiB of input, each with the 'BC' extra field (BSIZE) of the SAM spec;
+    `junk` goes between the members (the reference tolerates <= 10 bytes incl. the 8-byte trailer)."""
+    import struct
+    out = bytearray()
+    for i in range(0, len(data), block):
+        c = zlib.compressobj(6, zlib.DEFLATED, -15)
+        body = c.compress(data[i:i + block]) + c.flush()
+        bsize = 12 + 6 + len(body) + 8 - 1
+        out += b'\x1f\x8b\x08\x04' + b'\0' * 4 + b'\x00\xff' + struct.pack('<H', 6) + b'BC' + struct.pack('<HH', 2, bsize & 0xFFFF)
+        out += body + struct.pack('<II', zlib.crc32(data[i:i + block]), len(data[i:i + block]) & 0xFFFFFFFF) + junk
+    return bytes(out)
+
+
+def test_files_of_many_short_members(harness, tmp_path):
+    """BGZF-like files (the .fastq.gz of Illumina's converters): the chunk rounds give up after two members, the
+    member rounds decode the members side by side; bytes and read positions as the sequential reader's"""
+    g = synth.genome(300000, seed=4)
+    fq = synth.fastq_reads(g, 100000, readlen=150, seed=6).tobytes()                   # ~33 MB, ~500 members
+    plain = b''.join(gzip.compress(fq[i:i + 65280], 6) for i in range(0, len(fq), 65280))
+    cases = {
+        'bgzf': bgzf(fq) + bgzf(b''),                                                    # (with the empty EOF member)
+        'members64k': plain,
+        'junk2': bgzf(fq, junk=b'\x00\x01'),
+        'uneven': b''.join(gzip.compress(fq[a:b], 6) for a, b in zip([0, 30000, 9000000, 9100000, 20000000], [30000, 9000000, 9100000, 20000000, len(fq)])),
+        'magic': b''.join(gzip.compress(fq[i:i + 65280].replace(b'@SYN', b'\x1f\x8b\x08\x00'), 0) for i in range(0, 8000000, 65280)) + plain,
+    }
+    for name, blob in cases.items():
+        fn = str(tmp_path / (name + '.fastq.gz'))
+        open(fn, 'wb').write(blob)
+        seq, ev_seq, _ = run(harness, 1, fn, str(tmp_path / 'seq.bin'))
+        for threads in (2, 5):
+            par, ev_par, nb = run(harness, threads, fn, str(tmp_path / 'par.bin'))
+            assert par == seq, name + ': bytes differ'
+            assert ev_par == ev_seq, name + ': read events differ'
+            if name in ('bgzf', 'members64k', 'junk2'):
+                assert nb > 0.5 * len(seq), name + ': the member rounds were not taken'
+        assert seq == inflate_members(blob), name + ': sequential reader differs from zlib'

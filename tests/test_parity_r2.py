@@ -196,3 +196,27 @@ def test_large_gz_parallel_inflate(checker, tmp_path, monkeypatch):
         got = e.findseqs(small, seqs[:8])
         assert_same_result(got, oracle(checker, small, seqs[:8], DEFAULT, impl='ref'), what='parallel inflate vs the reference C')
     e.close()
+
+
+def test_bgzf_members_inflated_side_by_side(checker, tmp_path, monkeypatch):
+    """A .fastq.gz made of 64 KiB members (BGZF, what Illumina's converters write): the member rounds of
+    gz_parallel.h decode the members side by side; hits, hitseqs and stats (incl. the size estimate, which moves
+    with every member: csrc/workhorse.c:842-884) against the CPU checker and against one zlib stream."""
+    import gzip
+    from kvarq_b200.engine import Engine
+    g = synth.genome(300000, seed=91)
+    ts = synth.mtbc_templates(g, seed=92, n_phylo=6, n_res=10, regions=(3, 81), n_spacers=5)
+    iso = synth.isolate(g, ts, seed=93)
+    seqs = ts.seqs()
+    fq = synth.fastq_reads(iso, 120000, readlen=150, seed=94).tobytes()                 # ~40 MB, ~600 members
+    fn = str(tmp_path / 'blocks.fastq.gz')
+    open(fn, 'wb').write(b''.join(gzip.compress(fq[i:i + 65280], 6) for i in range(0, len(fq), 65280)))
+    e = Engine(0)
+    e.config(nthreads=8, **DEFAULT)
+    want = oracle(checker, fn, seqs, DEFAULT, impl='oracle', nthreads=os.cpu_count() or 8)
+    assert want['stats']['records_parsed'] == 120000 and len(want['hits']) > 200
+    got = e.findseqs(fn, seqs, nplus=ts.nplus)
+    assert_same_result(got, want, what='member rounds')
+    monkeypatch.setenv('KVQ_GZ_THREADS', '1')
+    assert_same_result(e.findseqs(fn, seqs, nplus=ts.nplus), want, what='one zlib stream')
+    e.close()
