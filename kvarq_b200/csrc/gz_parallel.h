@@ -1048,7 +1048,10 @@ inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Even
     std::vector<Cand> cand;
     cand.push_back(Cand{P});
     for (int64_t q = P; q + 18 < scan_end; q++) {
-        if (f_[q] != 0x1F || f_[q + 1] != 0x8B || f_[q + 2] != 8 || (f_[q + 3] & (0x02 | 0x20 | 0xC0))) continue;
+        const void *hit = memchr(f_ + q, 0x1F, (size_t) (scan_end - 18 - q));
+        if (!hit) break;
+        q = (const uint8_t *) hit - f_;
+        if (f_[q + 1] != 0x8B || f_[q + 2] != 8 || (f_[q + 3] & (0x02 | 0x20 | 0xC0))) continue;
         int64_t d = q;
         if (skip_header(d, 0) == nullptr && d < scan_end && d > P) cand.push_back(Cand{d});
     }
