@@ -1906,8 +1906,19 @@ static int scan_staged_impl(kvq_engine *e, kvq_staged *st, const char *const *se
         st->tiles.fill(b);
         KvqOut o = make_out(e, bufs_of(*st));
         enqueue_kernels(e, b, e->tpl.par, o, s0.stream, s0.ev0, s0.ev1);
-        CK(cudaMemcpyAsync(s0.h_ctr.p, st->d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s0.stream));
         const bool red = reduce && e->comm != nullptr;
+        // the copies of the counters (and the reduce) run on a side stream beside the kernels that order the hits:
+        // in stream order they would stand between the scan and the ordering (~20 us of copy latency per step)
+        static const bool side_copies = !(getenv("KVQ_SIDE_COPIES") && atoi(getenv("KVQ_SIDE_COPIES")) == 0);
+        const bool side = red || (side_copies && want_hits);
+        if (side && !e->red_stream) {
+            CK(cudaStreamCreateWithFlags(&e->red_stream, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&e->ev_ra, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&e->ev_rb, cudaEventDisableTiming));
+            CK(cudaEventCreate(&e->ev_r0)); CK(cudaEventCreate(&e->ev_r1));
+        }
+        cudaStream_t cs = s0.stream;            // where the counter copies go
+        if (side && !red) { CK(cudaEventRecord(e->ev_ra, s0.stream)); CK(cudaStreamWaitEvent(e->red_stream, e->ev_ra, 0)); cs = e->red_stream; }
+        CK(cudaMemcpyAsync(s0.h_ctr.p, st->d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, cs));
         const size_t row = e->acc.row_words();
         auto enqueue_reduce = [&](cudaStream_t rs) {
             // tail of the row from the batch's device counters, then the sum over the ranks into d_red (the rank's own
@@ -1923,18 +1934,14 @@ static int scan_staged_impl(kvq_engine *e, kvq_staged *st, const char *const *se
             if (rs != s0.stream) CK(cudaEventRecord(e->ev_rb, rs));
         };
         if (red) {
-            if (!e->red_stream) {
-                CK(cudaStreamCreateWithFlags(&e->red_stream, cudaStreamNonBlocking));
-                CK(cudaEventCreateWithFlags(&e->ev_ra, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&e->ev_rb, cudaEventDisableTiming));
-                CK(cudaEventCreate(&e->ev_r0)); CK(cudaEventCreate(&e->ev_r1));
-            }
             e->d_red.ensure(row * 8); e->pin_acc.ensure(row * 8);
             enqueue_reduce(e->red_stream);
         } else {   // the per-template accumulators ride behind the kernels instead of a blocking copy later
             const bool want_cov = e->tpl.nplus > 0 && e->tpl.cov_total > 0;
             const size_t words = want_cov ? e->acc.words() : 2 * e->acc.ns;
             e->pin_acc.ensure(words * 8);
-            CK(cudaMemcpyAsync(e->pin_acc.p, e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost, s0.stream));
+            CK(cudaMemcpyAsync(e->pin_acc.p, e->acc.d_all.p, words * 8, cudaMemcpyDeviceToHost, cs));
+            if (side) CK(cudaEventRecord(e->ev_rb, cs));
         }
         // the hits are put into the reference's order on the device (KvqOrder); a last kernel exports the
         // ordered records, the hitseq offsets and the hitseq bytes into the result's page-locked host buffer
@@ -1965,7 +1972,7 @@ static int scan_staged_impl(kvq_engine *e, kvq_staged *st, const char *const *se
             CK(cudaMemcpyAsync(e->pin_ord.p, ord.status, 4, cudaMemcpyDeviceToHost, s0.stream));
         }
         mark();
-        if (red) CK(cudaStreamWaitEvent(s0.stream, e->ev_rb, 0));
+        if (side) CK(cudaStreamWaitEvent(s0.stream, e->ev_rb, 0));
         CK(cudaStreamSynchronize(s0.stream));
         mark();
         float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1));
