@@ -1061,31 +1061,39 @@ inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Even
     std::vector<Bytes> bufs((size_t) W);
     for (int t = 0; t < W; t++) bufs[(size_t) t] = take_spare((size_t) 4 << 20);
     auto range = [&](int t) { return std::make_pair(cand.size() * (size_t) t / (size_t) W, cand.size() * (size_t) (t + 1) / (size_t) W); };
+    const Bits bits{f_, 8 * size_};
     team_->run(W, [&](int t) {
-        z_stream z; memset(&z, 0, sizeof(z));
-        if (inflateInit2(&z, -15) != Z_OK) return;
+        // the in-tree decoder (twice zlib's rate), one member at a time: cells with an empty, known history, then bytes
         Bytes &buf = bufs[(size_t) t];
+        MarkerOut o;
+        CrossTracker ct; ct.next = NO_BOUNDARY; ct.fsize = 0;
         size_t used = 0;
         const auto r = range(t);
         for (size_t i = r.first; i < r.second; i++) {
             Cand &c = cand[i];
-            inflateReset2(&z, -15);
             const int64_t lim = std::min(size_, c.data + PIECE);    // the member must end inside the piece read at its start
-            z.next_in = const_cast<Bytef *>(f_ + c.data); z.avail_in = (uInt) (lim - c.data);
             c.off = used;
-            for (;;) {
-                if (buf.size() - used < (256u << 10)) buf.resize(buf.size() * 2);
-                z.next_out = buf.data() + used; z.avail_out = (uInt) std::min<size_t>(buf.size() - used, 1u << 30);
-                const uInt out0 = z.avail_out;
-                const int st = inflate(&z, Z_NO_FLUSH);
-                used += out0 - z.avail_out;
-                if (st == Z_STREAM_END) { c.ok = true; c.end = lim - (int64_t) z.avail_in; break; }
-                if (st != Z_OK || (z.avail_in == 0 && z.avail_out != 0) || used - c.off > ((size_t) 64 << 20)) break;
+            o.n = 0;
+            int64_t pos = 8 * c.data;
+            bool fin = false, good = true;
+            while (!fin && good) {
+                pos = marker_block(bits, pos, o, ct, &fin, (int64_t) 64 << 20, (const uint8_t *) "", 0);
+                good = pos >= 0 && ((pos + 7) >> 3) <= lim;
             }
-            if (!c.ok) used = c.off;
-            c.len = used - c.off;
+            if (!good) continue;
+            c.ok = true; c.end = (pos + 7) >> 3; c.len = (size_t) o.n;
+            if (buf.size() - used < c.len + 64) buf.resize(std::max(buf.size() * 2, used + c.len + 64));
+            uint8_t *out = buf.data() + used;
+            const uint16_t *cells = o.cells.data();
+            int64_t q = 0;
+#if defined(__SSE2__)
+            for (; q + 16 <= o.n; q += 16)
+                _mm_storeu_si128((__m128i *) (out + q), _mm_packus_epi16(_mm_loadu_si128((const __m128i *) (cells + q)),
+                                                                         _mm_loadu_si128((const __m128i *) (cells + q + 8))));
+#endif
+            for (; q < o.n; q++) out[q] = (uint8_t) cells[q];
+            used += c.len;
         }
-        inflateEnd(&z);
     });
     // chain from the current member on
     std::vector<size_t> chain;
