@@ -482,6 +482,17 @@ def test_staged_hits_ordered_on_device(checker, tmp_path):
             got = e.scan_staged(st, sq, nplus=0)
             assert_same_result(got, want, what='%s, scan %d' % (name, rep))
         st.free()
+    # few and many hits in turn on the same stream (buffers and tables of the ordering kernels are reused from scan to scan)
+    text = ''.join(recs[:2000]) + ''.join('@p%d\n%s\n+\n%s\n' % (i, 'A' * 150, 'I' * 150) for i in range(200))
+    fn = str(tmp_path / 'ord2.fastq')
+    open(fn, 'w').write(text)
+    st = e.stage([np.frombuffer(text.encode(), dtype=np.uint8)])
+    want_few = oracle(checker, fn, seqs, cfg)
+    want_many = oracle(checker, fn, ['A' * 60], cfg, impl='oracle')
+    assert 1000 < len(want_few['hits']) < 24576 < len(want_many['hits']) < 65536
+    for rep, (sq, want) in enumerate([(seqs, want_few), (seqs, want_few), (['A' * 60], want_many), (['A' * 60], want_many), (seqs, want_few)]):
+        assert_same_result(e.scan_staged(st, sq, nplus=0), want, what='few / many hits in turn, scan %d' % rep)
+    st.free()
     e.close()
 
 
