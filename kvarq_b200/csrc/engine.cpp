@@ -381,7 +381,7 @@ struct GzGate {
 
 class GzAhead : public Source {
 public:
-    static constexpr int64_t BLOCK = 4ll << 20, LIMIT = 1ll << 30;      // read-ahead per file
+    static constexpr int64_t BLOCK = 4ll << 20, LIMIT = 512ll << 20;    // read-ahead per file
     GzAhead(const std::string &name, int threads, std::shared_ptr<GzGate> gate = nullptr, int index = 0)
         : name_(name), threads_(threads), gate_(std::move(gate)), index_(index) { th_ = std::thread([this] { run(); }); }
     ~GzAhead() override {
