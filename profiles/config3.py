@@ -4,7 +4,7 @@ scanned end to end from the two .fastq.gz files (host inflate -> pinned batches 
 KVQ_C3_PAIRS pairs (default: the stated 1 764 613 = 200x, 2 x 0.92 GB FastQ).  Prints one line per
 input kind: the same reads as plain files, as single-member gz (chunk-parallel inflate, gz_parallel.h),
 as single-member gz with one zlib stream per file (KVQ_GZ_THREADS=1, the round-1 path) and -- with
-KVQ_C3_GZM=1 -- as multi-member gz (one member per 16 MiB); KVQ_C3_SWEEP=12,14 adds lines with that many inflate threads.
+KVQ_C3_GZM=1 -- as multi-member gz (one member per 16 MiB) and as BGZF-like gz (one member per 64 KiB); KVQ_C3_SWEEP=12,14 adds lines with that many inflate threads.
 Parity at this size: hits / hitseqs / stats of every gz scan == those of the plain-file scan of the same
 reads (the plain path is pinned to the reference by tests/), and the first KVQ_C3_ORACLE_PAIRS pairs,
 gzipped on their own, are checked against the CPU checker (oracle/, nthreads = cores).
@@ -50,6 +50,11 @@ def make_mate(args):
                 cut = len(raw) if cut < 0 else cut + 1
                 f.write(gzip.compress(raw[at:cut], 6)); at = cut
         out['gzm'] = fm
+        fb = os.path.join(tmp, 'c3b_%d.fastq.gz' % k)          # BGZF-like: one member per 64 KiB (Illumina's converters)
+        with open(fb, 'wb') as f:
+            for at in range(0, len(raw), 65280):
+                f.write(gzip.compress(raw[at:at + 65280], 6))
+        out['bgzf'] = fb
     return out
 
 
@@ -69,7 +74,7 @@ def main():
     e = Engine(0)
     e.config(nthreads=os.cpu_count() or 8, **CFG)
     ref = None
-    kinds = [('plain', 'plain', None), ('gz', 'gz', None), ('gz-1thread', 'gz', '1')] + ([('gzm', 'gzm', None)] if gzm else [])
+    kinds = [('plain', 'plain', None), ('gz', 'gz', None), ('gz-1thread', 'gz', '1')] + ([('gzm', 'gzm', None), ('bgzf', 'bgzf', None)] if gzm else [])
     kinds += [('gz-%sthreads' % n, 'gz', n) for n in os.environ.get('KVQ_C3_SWEEP', '').split(',') if n]      # inflate thread sweep
     for name, key, threads in kinds:
         files = [m[key] for m in mates]
@@ -111,7 +116,7 @@ def main():
     print('CONFIG3 prefix of %d pairs (gz) == CPU checker (oracle, %d threads, %.1f s): hits %d, records %d, stats incl. total %d' %
           (npre, os.cpu_count() or 8, time.time() - t0, len(want['hits']), want['stats']['records_parsed'], want['stats']['total']), flush=True)
     for m in mates:
-        for k in ('plain', 'gz', 'gzm', 'pre'):
+        for k in ('plain', 'gz', 'gzm', 'bgzf', 'pre'):
             if k in m:
                 os.remove(m[k])
     os.rmdir(tmp)
