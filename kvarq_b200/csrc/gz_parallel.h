@@ -730,7 +730,7 @@ public:
     {
         if (spares) { for (auto &b : *spares) if (spare_.size() < 64) spare_.push_back(std::move(b)); spares->clear(); }
         if (done_) return false;
-        if (small_members_ && at_member_start_ && threads_ > 1 && member_round(outs, ev)) return true;
+        if ((small_members_ || members_ > 1) && at_member_start_ && threads_ > 1 && member_round(outs, ev)) return true;
         if (par_ok_ && threads_ > 1) {
             if (parallel_round(outs, ev)) return true;
             par_ok_ = false;
@@ -773,7 +773,7 @@ private:
         piece_base_ = data_at;
         member_out0_ = produced_;
         par_ok_ = !small_members_; par_bit_ = 8 * data_at; window_.clear();
-        at_member_start_ = true;
+        at_member_start_ = true; members_++;
     }
 
     // ---- the reference's reader (workhorse.c:781-885), zlib instead of miniz
@@ -858,7 +858,7 @@ private:
     const uint8_t *f_; int64_t size_; int threads_;
     z_stream zs_; bool live_ = false;
     int64_t rd_ = 0, remaining_ = 0, produced_ = 0, piece_base_ = 0, member_out0_ = 0, par_bytes_ = 0;
-    bool done_ = false, par_ok_ = false, small_members_ = false, at_member_start_ = false; int short_rounds_ = 0;
+    bool done_ = false, par_ok_ = false, small_members_ = false, at_member_start_ = false; int short_rounds_ = 0, members_ = 0;
     int64_t par_bit_ = 0; std::vector<uint8_t> window_;
 };
 
@@ -1031,33 +1031,40 @@ inline bool FileDecoder::parallel_round(std::vector<Bytes> &outs, std::vector<Ev
     return true;
 }
 
-// Files made of many short members (BGZF and the .fastq.gz of Illumina's converters: one member per <= 64 KiB;
-// detected by parallel_round): members are independent streams, so a round decodes every member that starts in
-// the next stretch of the file on its own -- candidates are the places where a valid member header stands --
-// and chains them the way the reference walks from member to member (end of the deflate data, <= 10 bytes of
-// junk (the trailer), next header: workhorse.c:842-866).  A candidate nobody arrives at was not a member.  The
-// read positions follow from the layout: every member here lies inside the first 1 MiB piece read at its start.
+// Files made of several members (BGZF and the .fastq.gz of Illumina's converters: one member per <= 64 KiB;
+// concatenated or block-wise compressed files: members of megabytes).  Members are independent streams, so a
+// round decodes the members that start in the next stretch of the file side by side -- candidates are the
+// places where a valid member header stands -- and chains them the way the reference walks from member to
+// member (end of the deflate data, <= 10 bytes of junk (the trailer), next header: workhorse.c:842-866).  A
+// candidate nobody arrives at was not a member.  The read positions follow from the layout: a 1 MiB piece is
+// read at every member's data start and whenever a symbol runs over the end of the last piece (CrossTracker).
+// Tried at the start of every member but a file's first.
 // State on entry and on return true: at a member's data start, nothing of it read (as after fill()'s `at_member`).
 inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Event> &ev)
 {
     const int64_t P = rd_;                                          // data start of the current member
-    constexpr int64_t STRETCH = 1 << 20, MARGIN = 2 << 20;          // per thread; the end of the file is the sequential reader's
-    const int64_t scan_end = std::min(size_ - MARGIN, P + (int64_t) threads_ * STRETCH);
-    if (scan_end <= P + 4096) return false;
-    struct Cand { int64_t data, end = -1; size_t off = 0, len = 0; bool ok = false; };
+    constexpr int64_t MARGIN = 2 << 20;                             // the end of the file is the sequential reader's
+    // at least one candidate per thread (within 512 MiB), beyond that up to 1 MiB of file per thread (short members)
+    const int64_t scan_max = std::min(size_ - MARGIN, P + ((int64_t) 512 << 20));
+    const int64_t dense_end = P + (int64_t) threads_ * (1 << 20);
+    if (scan_max <= P + 4096) return false;
+    struct Cand { int64_t data, end = -1; size_t off = 0, len = 0; bool ok = false; std::vector<Crossing> cross; };
     std::vector<Cand> cand;
     cand.push_back(Cand{P});
-    for (int64_t q = P; q + 18 < scan_end; q++) {
-        const void *hit = memchr(f_ + q, 0x1F, (size_t) (scan_end - 18 - q));
+    for (int64_t q = P; q + 18 < scan_max; q++) {
+        if ((int) cand.size() >= threads_ && q >= dense_end) break;
+        const void *hit = memchr(f_ + q, 0x1F, (size_t) (scan_max - 18 - q));
         if (!hit) break;
         q = (const uint8_t *) hit - f_;
+        if ((int) cand.size() >= threads_ && q >= dense_end) break;
         if (f_[q + 1] != 0x8B || f_[q + 2] != 8 || (f_[q + 3] & (0x02 | 0x20 | 0xC0))) continue;
         int64_t d = q;
-        if (skip_header(d, 0) == nullptr && d < scan_end && d > P) cand.push_back(Cand{d});
+        if (skip_header(d, 0) == nullptr && d < scan_max && d > P) cand.push_back(Cand{d});
     }
     if (cand.size() < 4) return false;                              // not that kind of file after all
     if (!team_) team_.reset(new Team(threads_));
     const int W = (int) std::min<size_t>((size_t) threads_, cand.size());
+    if ((int) cells_pool_.size() < W) cells_pool_.resize((size_t) W);
     std::vector<Bytes> bufs((size_t) W);
     for (int t = 0; t < W; t++) bufs[(size_t) t] = take_spare((size_t) 4 << 20);
     auto range = [&](int t) { return std::make_pair(cand.size() * (size_t) t / (size_t) W, cand.size() * (size_t) (t + 1) / (size_t) W); };
@@ -1066,12 +1073,16 @@ inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Even
         // the in-tree decoder (twice zlib's rate), one member at a time: cells with an empty, known history, then bytes
         Bytes &buf = bufs[(size_t) t];
         MarkerOut o;
-        CrossTracker ct; ct.next = NO_BOUNDARY; ct.fsize = 0;
+        o.cells.swap(cells_pool_[(size_t) t]);
         size_t used = 0;
         const auto r = range(t);
         for (size_t i = r.first; i < r.second; i++) {
             Cand &c = cand[i];
-            const int64_t lim = std::min(size_, c.data + PIECE);    // the member must end inside the piece read at its start
+            // (a member of more than 64 MiB is left to the chunk rounds; a chance match of the magic bytes inside a
+            //  member's data decodes rubbish for a few symbols and fails)
+            const int64_t lim = size_ - MARGIN;
+            CrossTracker ct;
+            ct.init(c.data, 8 * c.data, size_);
             c.off = used;
             o.n = 0;
             int64_t pos = 8 * c.data;
@@ -1081,7 +1092,7 @@ inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Even
                 good = pos >= 0 && ((pos + 7) >> 3) <= lim;
             }
             if (!good) continue;
-            c.ok = true; c.end = (pos + 7) >> 3; c.len = (size_t) o.n;
+            c.ok = true; c.end = (pos + 7) >> 3; c.len = (size_t) o.n; c.cross.swap(ct.list);
             if (buf.size() - used < c.len + 64) buf.resize(std::max(buf.size() * 2, used + c.len + 64));
             uint8_t *out = buf.data() + used;
             const uint16_t *cells = o.cells.data();
@@ -1094,6 +1105,7 @@ inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Even
             for (; q < o.n; q++) out[q] = (uint8_t) cells[q];
             used += c.len;
         }
+        o.cells.swap(cells_pool_[(size_t) t]);
     });
     // chain from the current member on
     std::vector<size_t> chain;
@@ -1116,6 +1128,7 @@ inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Even
     ev.push_back(Event{out, std::min(size_, P + std::min<int64_t>(PIECE, size_ - P)), false});    // the piece read at the current member's start
     for (size_t k = 0; k < chain.size(); k++) {
         const Cand &c = cand[chain[k]];
+        for (const Crossing &x : c.cross) ev.push_back(Event{out + x.out, std::min(size_, x.boundary + PIECE), false});
         out += (int64_t) c.len;
         const int64_t d = k + 1 < chain.size() ? cand[chain[k + 1]].data : next_data;
         ev.push_back(Event{out, d, true});

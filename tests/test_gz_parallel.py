@@ -106,6 +106,7 @@ def test_files_of_many_short_members(harness, tmp_path):
         'bgzf': bgzf(fq) + bgzf(b''),                                                    # (with the empty EOF member)
         'members64k': plain,
         'junk2': bgzf(fq, junk=b'\x00\x01'),
+        'members3m': b''.join(gzip.compress(fq[i:i + 3000000], 6) for i in range(0, len(fq), 3000000)),     # (> 1 MiB compressed each)
         'uneven': b''.join(gzip.compress(fq[a:b], 6) for a, b in zip([0, 30000, 9000000, 9100000, 20000000], [30000, 9000000, 9100000, 20000000, len(fq)])),
         'magic': b''.join(gzip.compress(fq[i:i + 65280].replace(b'@SYN', b'\x1f\x8b\x08\x00'), 0) for i in range(0, 8000000, 65280)) + plain,
     }
@@ -117,6 +118,6 @@ def test_files_of_many_short_members(harness, tmp_path):
             par, ev_par, nb = run(harness, threads, fn, str(tmp_path / 'par.bin'))
             assert par == seq, name + ': bytes differ'
             assert ev_par == ev_seq, name + ': read events differ'
-            if name in ('bgzf', 'members64k', 'junk2'):
+            if name in ('bgzf', 'members64k', 'junk2', 'members3m'):
                 assert nb > 0.5 * len(seq), name + ': the member rounds were not taken'
         assert seq == inflate_members(blob), name + ': sequential reader differs from zlib'
