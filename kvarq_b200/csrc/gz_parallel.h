@@ -719,7 +719,8 @@ public:
 
     int64_t disk_pos() const { return rd_; }
     int64_t produced() const { return produced_; }
-    bool parallel_mode() const { return par_ok_ && threads_ > 1 && !done_; }   // the next call of next() tries a parallel round
+    // the next call of next() tries a parallel round (chunks of a member, or members side by side)
+    bool parallel_mode() const { return (par_ok_ || ((small_members_ || members_ > 1) && at_member_start_)) && threads_ > 1 && !done_; }
     int64_t parallel_bytes() const { return par_bytes_; }      // inflated bytes that came out of parallel rounds
 
     // Appends the next stretch of output (one or more buffers) and the read events that fall into it.
@@ -1062,6 +1063,8 @@ inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Even
         if (skip_header(d, 0) == nullptr && d < scan_max && d > P) cand.push_back(Cand{d});
     }
     if (cand.size() < 4) return false;                              // not that kind of file after all
+    // a few long members only (the tail of a file): the chunk rounds keep every thread busy inside each of them
+    if ((int) cand.size() < threads_ / 2 && (cand.back().data - P) / (int64_t) cand.size() > (1 << 20)) return false;
     if (!team_) team_.reset(new Team(threads_));
     const int W = (int) std::min<size_t>((size_t) threads_, cand.size());
     if ((int) cells_pool_.size() < W) cells_pool_.resize((size_t) W);
