@@ -121,3 +121,40 @@ def test_files_of_many_short_members(harness, tmp_path):
             if name in ('bgzf', 'members64k', 'junk2', 'members3m'):
                 assert nb > 0.5 * len(seq), name + ': the member rounds were not taken'
         assert seq == inflate_members(blob), name + ': sequential reader differs from zlib'
+
+
+def test_corrupt_inputs_end_the_same_way(harness, tmp_path):
+    """Flipped bits, overwritten stretches, truncation, a stray member header: the parallel decoder never trusts
+    what it cannot chain, so it ends like the sequential reader -- same bytes and read positions where the stream
+    stays decodable, the same error where it does not (the bytes delivered in front of an error may differ: the
+    engine raises IOError for the whole scan either way, csrc/workhorse.c:819-826)."""
+    import random
+    g = synth.genome(200000, seed=8)
+    fq = synth.fastq_reads(g, 50000, readlen=150, seed=9).tobytes()                    # ~16 MB
+    base = {'single': gzip.compress(fq, 6),
+            'blocks': b''.join(gzip.compress(fq[i:i + 65280], 6) for i in range(0, len(fq), 65280)),
+            'members': b''.join(gzip.compress(fq[i:i + 3000000], 6) for i in range(0, len(fq), 3000000))}
+    rng = random.Random(5)
+    for name, blob in base.items():
+        for kind in range(4):
+            b = bytearray(blob)
+            if kind == 0:
+                for _ in range(rng.randint(1, 5)):
+                    b[rng.randrange(len(b))] ^= 1 << rng.randrange(8)
+            elif kind == 1:
+                a = rng.randrange(len(b) - 5000)
+                b[a:a + rng.randint(1, 4000)] = bytes(rng.randrange(256) for _ in range(rng.randint(1, 4000)))
+            elif kind == 2:
+                b = b[:rng.randrange(len(b) // 2, len(b))]
+            else:
+                a = rng.randrange(len(b))
+                b[a:a] = b'\x1f\x8b\x08\x00' + bytes(rng.randrange(256) for _ in range(20))
+            fn = str(tmp_path / ('%s_%d.fastq.gz' % (name, kind)))
+            open(fn, 'wb').write(bytes(b))
+            seq, ev_seq, _ = run(harness, 1, fn, str(tmp_path / 'seq.bin'))
+            par, ev_par, _ = run(harness, 4, fn, str(tmp_path / 'par.bin'))
+            err_seq = [l for l in ev_seq.splitlines() if l.startswith('ERROR')]
+            err_par = [l for l in ev_par.splitlines() if l.startswith('ERROR')]
+            assert err_seq == err_par, (name, kind)
+            if not err_seq:
+                assert par == seq and ev_par == ev_seq, (name, kind)
