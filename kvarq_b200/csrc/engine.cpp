@@ -1264,10 +1264,7 @@ void reset_accum(kvq_engine *e, cudaStream_t st)
 void enqueue_kernels(kvq_engine *e, const KvqBatch &b, const KvqParams &p, const KvqOut &o,
                      cudaStream_t st, cudaEvent_t ev0, cudaEvent_t ev1)
 {
-    CK(cudaMemsetAsync(o.ctr, 0, sizeof(KvqCounters), st));
-    CK(cudaMemsetAsync(&o.ctr->err_key, 0xFF, sizeof(unsigned long long), st));
-    CK(cudaMemsetAsync(&o.ctr->longest, 0xFF, sizeof(long long), st));        // rls_longest = -1 (workhorse.c:332)
-    CK(cudaMemsetAsync(b.tile_status, 0, (size_t) std::max(1, b.ntiles) * 4, st));
+    cuda_check((cudaError_t) kvq_launch_reset(o.ctr, b.tile_status, b.ntiles, st), "reset kernel launch");
     if (ev0) CK(cudaEventRecord(ev0, st));
     cuda_check((cudaError_t) kvq_launch_scan(b, e->tpl.dev, p, o, e->sm_count, st), "scan kernel launch");
     cuda_check((cudaError_t) kvq_launch_emit(b, e->tpl.dev, p, o, e->sm_count, st), "emit kernel launch");
@@ -1296,7 +1293,7 @@ void launch_slot(kvq_engine *e, Slot &s, ScanTotals &tot)
     CK(cudaMemcpyAsync(s.h_ctr.p, s.d_ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, s.stream));
     s.h_live.ensure(2 * e->acc.ns * 8);
     CK(cudaMemcpyAsync(s.h_live.p, e->acc.d_all.p, 2 * e->acc.ns * 8, cudaMemcpyDeviceToHost, s.stream));
-    tot.launches += 3; tot.h2d += hb.nbytes + (int64_t) hb.cuts.size() * 8; tot.d2h += sizeof(KvqCounters);
+    tot.launches += 4; tot.h2d += hb.nbytes + (int64_t) hb.cuts.size() * 8; tot.d2h += sizeof(KvqCounters);
     tot.stream_bytes += hb.nbytes;
 }
 
@@ -1318,7 +1315,7 @@ KvqParams rerun_for_survivors(kvq_engine *e, const KvqBatch &b, const OutBufs &o
         CK(cudaMemcpyAsync(h_ctr.p, ob.ctr.p, sizeof(KvqCounters), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         c = *h_ctr.as<KvqCounters>();
-        tot.launches += 3; tot.acc_fetched = false; tot.spec_hits = tot.spec_blob = 0;
+        tot.launches += 4; tot.acc_fetched = false; tot.spec_hits = tot.spec_blob = 0;
     }
     if (c.surv_count > ob.surv_cap || c.phase_retry)
         throw KvqError(KVQ_ERR_RUNTIME, "internal: batch still incomplete after re-running it (survivor queue / line phases)");
@@ -1346,7 +1343,7 @@ void collect_hits(kvq_engine *e, const KvqBatch &b, const OutBufs &ob, const Kvq
             if (c2.phase_retry || c2.surv_count > ob.surv_cap || c2.hit_count != nh)
                 throw KvqError(KVQ_ERR_RUNTIME, "internal: re-run with larger hit buffers did not reproduce the batch");
         }
-        tot.launches += 3; tot.spec_hits = tot.spec_blob = 0;
+        tot.launches += 4; tot.spec_hits = tot.spec_blob = 0;
     }
     if (nh == 0) return;
     const size_t h0 = tot.hits.size(), b0 = tot.blob.size();
@@ -1976,7 +1973,7 @@ static int scan_staged_impl(kvq_engine *e, kvq_staged *st, const char *const *se
         CK(cudaStreamSynchronize(s0.stream));
         mark();
         float ms = 0; CK(cudaEventElapsedTime(&ms, s0.ev0, s0.ev1));
-        tot.kernel_ms = ms; tot.launches = 3; tot.stream_bytes = st->nbytes; tot.d2h = sizeof(KvqCounters);
+        tot.kernel_ms = ms; tot.launches = 4; tot.stream_bytes = st->nbytes; tot.d2h = sizeof(KvqCounters);
         KvqCounters c = *s0.h_ctr.as<KvqCounters>();
         const int64_t launches0 = tot.launches;
         const KvqParams used = rerun_for_survivors(e, b, bufs_of(*st), c, s0.h_ctr, s0.stream, tot);

@@ -195,3 +195,5 @@ int kvq_launch_order(const KvqBatch &b, const KvqOut &o, const KvqOrder &ord, vo
 // tail of the accumulator row from the batch's device counters (see scan_kernel.cu); tail[KVQ_HIST + 4] = 1 when the
 // batch has to be run again (survivor queue overflow, contradicted line phase)
 int kvq_launch_tail(const KvqCounters *ctr, unsigned long long *tail, long long parsed, unsigned long long surv_cap, void *stream);
+// zeroed counters (err_key = ~0, longest = -1) and tile status words: what a batch starts from, one launch
+int kvq_launch_reset(KvqCounters *ctr, uint32_t *tile_status, int ntiles, void *stream);

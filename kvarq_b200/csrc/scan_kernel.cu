@@ -1608,6 +1608,27 @@ int kvq_launch_order(const KvqBatch &b, const KvqOut &o, const KvqOrder &ord, vo
     return (int) cudaGetLastError();
 }
 
+// ---- the state a batch starts from, in one launch (instead of four memsets in a row in front of every scan kernel) ----
+namespace {
+__global__ void kvq_reset_kernel(KvqCounters *ctr, uint32_t *tile_status, int ntiles)
+{
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nt = gridDim.x * blockDim.x;
+    uint32_t *c = reinterpret_cast<uint32_t *>(ctr);
+    constexpr int ERR = (int) (offsetof(KvqCounters, err_key) / 4), LON = (int) (offsetof(KvqCounters, longest) / 4);
+    // all zero but err_key = ~0 (no format error yet) and longest = -1 (rls_longest, workhorse.c:332)
+    for (int i = tid; i < (int) (sizeof(KvqCounters) / 4); i += nt)
+        c[i] = (i == ERR || i == ERR + 1 || i == LON || i == LON + 1) ? 0xFFFFFFFFu : 0u;
+    for (int i = tid; i < ntiles; i += nt) tile_status[i] = 0;
+}
+} // namespace
+
+int kvq_launch_reset(KvqCounters *ctr, uint32_t *tile_status, int ntiles, void *stream)
+{
+    static_assert(sizeof(KvqCounters) % 4 == 0, "KvqCounters is zeroed word by word");
+    kvq_reset_kernel<<<64, 256, 0, (cudaStream_t) stream>>>(ctr, tile_status, ntiles < 1 ? 1 : ntiles);
+    return (int) cudaGetLastError();
+}
+
 // ---- tail of the accumulator row (multi-GPU scans that reduce their counters right behind the kernels) ----
 // [readlengths KVQ_HIST][records][bases][parsed][longest + 1][this rank's batch has to be run again]: what the
 // host adds to the row before a reduce (engine.cpp:upload_tail), written from the batch's device counters so
@@ -1639,6 +1660,7 @@ int kvq_launch_tail(const KvqCounters *ctr, unsigned long long *tail, long long 
 // the rule tag of a hit (which the public kvq_hit_t does not carry) is derived from the tuple and the
 // template length.  Every GPU that loads the library holds the array (2 MiB) until exit; all calls
 // share it, so calls that overlap on the GPU race (serialise them on one stream).
+#include <cstddef>
 #include <mutex>
 #include <string>
 #include "../../include/kvarq_b200.h"
