@@ -1081,7 +1081,7 @@ inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Even
         const auto r = range(t);
         for (size_t i = r.first; i < r.second; i++) {
             Cand &c = cand[i];
-            // (a member of more than 64 MiB is left to the chunk rounds; a chance match of the magic bytes inside a
+            // (a member of more than 32 MiB is left to the chunk rounds: a round holds one member per thread in memory; a chance match of the magic bytes inside a
             //  member's data decodes rubbish for a few symbols and fails)
             const int64_t lim = size_ - MARGIN;
             CrossTracker ct;
@@ -1091,7 +1091,7 @@ inline bool FileDecoder::member_round(std::vector<Bytes> &outs, std::vector<Even
             int64_t pos = 8 * c.data;
             bool fin = false, good = true;
             while (!fin && good) {
-                pos = marker_block(bits, pos, o, ct, &fin, (int64_t) 64 << 20, (const uint8_t *) "", 0);
+                pos = marker_block(bits, pos, o, ct, &fin, (int64_t) 32 << 20, (const uint8_t *) "", 0);
                 good = pos >= 0 && ((pos + 7) >> 3) <= lim;
             }
             if (!good) continue;
