@@ -1002,6 +1002,7 @@ struct TemplateSet {
         par.maxerrors = E; par.minoverlap = O; par.minreadlength = cfg.minreadlength;
         par.amin = (int) (signed char) cfg.Amin;
         par.seed_ok = seed_ok; par.npieces = pieces < 1 ? 1 : pieces; par.max_seqlen = max_len;
+        par.pieces_inv = (uint32_t) std::min<uint64_t>((1ull << 32) / (uint64_t) par.npieces + 1, 0xFFFFFFFFull);
         par.want_hits = 1; par.accumulate = 1; par.exact_phase = exact_phase_knob();
         par.t1x = t1x_on ? KVQ_T1X_K * pieces : 0;
         par.min_seed_rl = KVQ_SEED_K * par.npieces;

@@ -45,6 +45,7 @@ struct KvqParams {
     int32_t t1x;                        // 0, or (many templates) KVQ_T1X_K * npieces: T1 seeds of templates at least this long pass the 12-mer second level
     int32_t seed_ok;                    // floor(minoverlap/(E+1)) >= K and E+1 <= KVQ_MAX_PIECES
     int32_t npieces;                    // E+1
+    uint32_t pieces_inv;                // 2^32 / npieces + 1: floor(x / npieces) == __umulhi(x, pieces_inv) for x < 2^19 (x = j * seqlen)
     int32_t max_seqlen;                 // longest template (decides the whole-read T2 probes)
     int32_t want_hits;                  // 0: count only (no hit records / blob written)
     int32_t min_seed_rl;                // KVQ_SEED_K * npieces: shortest read the seed scheme covers

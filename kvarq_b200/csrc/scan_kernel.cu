@@ -521,11 +521,12 @@ __device__ __noinline__ void emit_hit(const KvqTemplates &t, const KvqParams &p,
     }
 }
 
-// Warp-cooperative variant: lane 0 reserves the output slots, all lanes copy the hitseq bytes
-// and update the coverage arrays.
+// Cooperative variant for a group of G lanes (gmask = the group's lanes, sub = lane within the group, first =
+// the group's first lane): the first lane reserves the output slots, all lanes copy the hitseq bytes and update
+// the coverage arrays.
 __device__ __noinline__ void emit_hit_warp(const KvqTemplates &t, const KvqParams &p, const KvqOut &o, int seq, int d,
                               int ro, int to, int L, int rl, int sl, int64_t file_pos, const uint8_t *rd,
-                              const uint8_t *tp, int copies, int rule, int lane)
+                              const uint8_t *tp, int copies, int rule, int lane, int G, uint32_t gmask, int first)
 {
     unsigned long long slot = 0, boff = 0;
     if (lane == 0) {
@@ -536,8 +537,8 @@ __device__ __noinline__ void emit_hit_warp(const KvqTemplates &t, const KvqParam
         slot = atomicAdd(&o.ctr->hit_count, (unsigned long long) copies);
         if (p.want_hits) boff = atomicAdd(&o.ctr->blob_used, (unsigned long long) copies * (unsigned long long) L);
     }
-    slot = __shfl_sync(0xffffffffu, slot, 0);
-    boff = __shfl_sync(0xffffffffu, boff, 0);
+    slot = __shfl_sync(gmask, slot, first);
+    boff = __shfl_sync(gmask, boff, first);
     if (p.want_hits) {
         for (int c = 0; c < copies; c++) {
             if (lane == 0 && slot + c < o.hit_cap) {
@@ -548,14 +549,14 @@ __device__ __noinline__ void emit_hit_warp(const KvqTemplates &t, const KvqParam
                 o.hits[slot + c] = h;
             }
             if (boff + (unsigned long long) (c + 1) * L <= o.blob_cap)
-                for (int j = lane; j < L; j += 32) o.blob[boff + (unsigned long long) c * L + j] = rd[ro + j];
+                for (int j = lane; j < L; j += G) o.blob[boff + (unsigned long long) c * L + j] = rd[ro + j];
         }
     }
     if (t.nplus > 0 && p.accumulate) {
         const bool plus = seq < t.nplus;
         const int tpl = plus ? seq : seq - t.nplus;
         const unsigned long long cb = __ldg(t.cov_off + tpl);
-        for (int j = lane; j < L; j += 32) {
+        for (int j = lane; j < L; j += G) {
             const int sidx = to + j;
             const unsigned long long pidx = cb + (unsigned long long) (plus ? sidx : sl - 1 - sidx);
             atomicAdd(&o.coverage[pidx], (unsigned long long) copies);
@@ -579,11 +580,11 @@ __device__ __forceinline__ int byte_mismatches(const uint8_t *a, const uint8_t *
 
 // Exhaustive matcher: one warp per (read, seq) pair, lanes over all diagonals, raw bytes.
 __device__ __noinline__ void exhaustive_pair(const KvqParams &p, const KvqTemplates &t, const KvqOut &o,
-                                const uint8_t *rd, int rl, int64_t file_pos, int sq, int lane)
+                                const uint8_t *rd, int rl, int64_t file_pos, int sq, int lane, int G = 32)
 {
     const int sl = __ldg(t.len + sq);
     const uint8_t *tp = t.bytes + __ldg(t.byte_off + sq);
-    for (int d = -(rl - 1) + lane; d <= sl - 1; d += 32) {
+    for (int d = -(rl - 1) + lane; d <= sl - 1; d += G) {
         int ro, to, L, rule;
         const int copies = diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule);
         if (!copies) continue;
@@ -600,7 +601,7 @@ __device__ __noinline__ bool canonical_seed(const KvqParams &p, const KvqTemplat
                                const uint32_t *tpk, int rl, int sl, int d, int kind, int pos)
 {
     for (int j = 0; j < p.npieces; j++) {
-        const int toff = j * sl / p.npieces;
+        const int toff = (int) __umulhi((unsigned) (j * sl), p.pieces_inv);       // floor(j * sl / npieces) without the division (KvqParams)
         const int pj = toff - d;
         if (pj < 0 || pj > rl - KVQ_SEED_K) continue;
         const uint32_t x16 = extract16(rpk, rb + pj) ^ extract16_g(tpk, toff);
@@ -1343,20 +1344,30 @@ kvq_long_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
 // counters, fused coverage).  seq < 0: exhaustive matching of the read.  Nothing happens when the
 // queue overflowed: the host re-runs the batch with a larger one.
 #ifndef KVQ_EMIT_BLOCKS
-#define KVQ_EMIT_BLOCKS 8                 // resident blocks per SM (latency-bound: one warp per record, dependent loads)
+#define KVQ_EMIT_BLOCKS 8                 // resident blocks per SM (latency-bound: dependent loads per survivor)
+#endif
+#ifndef KVQ_EMIT_G
+#define KVQ_EMIT_G 32                     // lanes per survivor in the emit kernel (32 / G survivors per warp side by side);
+                                          // measured, kernels of one config-2 step: G = 32: 0.7157 ms, 16: 0.7220, 8: 0.7255
 #endif
 template <bool BIG>
 __global__ void __launch_bounds__(256, KVQ_EMIT_BLOCKS)
 kvq_emit_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqTemplates t,
                 const __grid_constant__ KvqParams p, const __grid_constant__ KvqOut o)
 {
-    __shared__ uint32_t rpk_all[8][KVQ_MAXRL_FAST / 16 + 4];
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    uint32_t *rpk = rpk_all[wib];
+    // G lanes per survivor, 32 / G survivors per warp side by side.  Every warp walks ~6 survivors in a row, each a
+    // chain of dependent loads (record -> template -> read bytes -> codes -> tables -> atomics); several survivors per
+    // warp shorten the row but run their (divergent) chains through one instruction stream -- slower, see KVQ_EMIT_G
+    constexpr int G = KVQ_EMIT_G, NG = 32 / G;
+    __shared__ uint32_t rpk_all[8 * NG][KVQ_MAXRL_FAST / 16 + 4];
+    const int wlane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int grp = wlane / G, lane = wlane % G, first = grp * G;
+    const uint32_t gmask = (G == 32 ? 0xFFFFFFFFu : ((1u << G) - 1u) << first);
+    uint32_t *rpk = rpk_all[wib * NG + grp];
     const unsigned long long n = o.ctr->surv_count;
     if (n > o.surv_cap || o.ctr->phase_retry) return;
-    const unsigned long long nw = (unsigned long long) gridDim.x * 8;
-    for (unsigned long long i = (unsigned long long) blockIdx.x * 8 + wib; i < n; i += nw) {
+    const unsigned long long nw = (unsigned long long) gridDim.x * 8 * NG;
+    for (unsigned long long i = ((unsigned long long) blockIdx.x * 8 + wib) * NG + grp; i < n; i += nw) {
         const uint4 q0 = __ldg(reinterpret_cast<const uint4 *>(o.surv + i));
         const uint4 q1 = __ldg(reinterpret_cast<const uint4 *>(o.surv + i) + 1);
         const long long rd0 = (long long) (((unsigned long long) q0.y << 32) | q0.x);
@@ -1364,10 +1375,10 @@ kvq_emit_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         const uint8_t *rdp = b.data + rd0;
         if (seq < 0) {
             if (seq == -1)
-                for (int sq = 0; sq < t.nseqs; sq++) exhaustive_pair(p, t, o, rdp, rl, b.base_fpos + rd0, sq, lane);
+                for (int sq = 0; sq < t.nseqs; sq++) exhaustive_pair(p, t, o, rdp, rl, b.base_fpos + rd0, sq, lane, G);
             else
                 for (int k = 0; k < t.n_exh; k++)
-                    exhaustive_pair(p, t, o, rdp, rl, b.base_fpos + rd0, __ldg(t.exh_list + k), lane);
+                    exhaustive_pair(p, t, o, rdp, rl, b.base_fpos + rd0, __ldg(t.exh_list + k), lane, G);
             continue;
         }
         const int sl = __ldg(t.len + seq);
@@ -1375,24 +1386,29 @@ kvq_emit_kernel(const __grid_constant__ KvqBatch b, const __grid_constant__ KvqT
         const int copies = diag_rule(d, rl, sl, p.minoverlap, ro, to, L, rule);
         const uint8_t *tp = t.bytes + __ldg(t.byte_off + seq);
         int e = 0;
-        for (int j = lane; j < L; j += 32) e += (rdp[ro + j] != tp[to + j]);
-        e = __reduce_add_sync(0xffffffffu, e);
+        for (int j = lane; j < L; j += G) e += (rdp[ro + j] != tp[to + j]);
+#pragma unroll
+        for (int x = G / 2; x > 0; x >>= 1) e += __shfl_xor_sync(gmask, e, x);
         if (e > p.maxerrors || !copies) continue;
-        // 2-bit codes of the read for the canonical-seed rule
-        __syncwarp();
-        for (int w = lane; w < (rl + 15) / 16 + 2; w += 32) {
+        // 2-bit codes of the read for the canonical-seed rule: every lane packs 8 bases (16 bits), neighbours are
+        // joined to words -- 8 G bases per pass; bytes behind the read are loaded (the batch is followed by zeroed
+        // slack) and masked away
+        __syncwarp(gmask);
+        const int nwords = (rl + 15) / 16 + 2;
+        for (int w0 = 0; w0 < nwords; w0 += G / 2) {
+            const int at = 16 * w0 + 8 * lane;
             uint32_t v = 0;
 #pragma unroll
-            for (int k = 0; k < 16; k++) {
-                const int at = 16 * w + k;
-                if (at < rl) v |= KVQ_CODE(rdp[at]) << (2 * k);
-            }
-            rpk[w] = v;
+            for (int k = 0; k < 8; k++) v |= KVQ_CODE(rdp[at + k]) << (2 * k);
+            const int valid = min(max(rl - at, 0), 8);
+            v &= (1u << (2 * valid)) - 1u;
+            v |= __shfl_down_sync(gmask, v, 1, G) << 16;
+            if (!(lane & 1) && w0 + (lane >> 1) < nwords) rpk[w0 + (lane >> 1)] = v;
         }
-        __syncwarp();
+        __syncwarp(gmask);
         if (!canonical_seed<BIG>(p, t, rpk, 0, t.packed + __ldg(t.packed_off + seq), rl, sl, d,
                                  (int) (q1.y >> 16), (int) (q1.y & 0xFFFFu))) continue;
-        emit_hit_warp(t, p, o, seq, d, ro, to, L, rl, sl, b.base_fpos + rd0, rdp, tp, copies, rule, lane);
+        emit_hit_warp(t, p, o, seq, d, ro, to, L, rl, sl, b.base_fpos + rd0, rdp, tp, copies, rule, lane, G, gmask, first);
     }
 }
 
