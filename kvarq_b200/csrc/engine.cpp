@@ -230,6 +230,11 @@ struct PlainFileSource : Source {
     void preload(char *dst, int64_t max) override {
         const int64_t m = std::min(max, size - pos);
         if (m <= 0) { stg_len = 0; return; }
+        if (map) {      // pages of a mapping behind the file's end raise SIGBUS: a file that shrank since it was opened ends the scan here
+            struct stat st;
+            if (fstat(fd, &st) != 0 || (int64_t) st.st_size < size)
+                throw KvqError(KVQ_ERR_IO, "error while reading from file in fastq_read");          // :894
+        }
         int64_t have = 0;
         if (stg_len > 0 && pos >= stg_off && pos < stg_off + stg_len) {     // what the last batch left over
             have = std::min(m, stg_off + stg_len - pos);
