@@ -6,8 +6,8 @@ Ctrl-C within 2 s calls engine.stop()) -> testsuite calls -> JSON result file.
 Testsuites are not discovered on disk and exec'd like the reference's (`kvarq/testsuites.py`): they
 are built from tables (kvarq_b200/testsuites.py).  `-l` takes
     MTBC/phylo  MTBC/resistance  MTBC/spoligo  MTBC        with --genome <ancestor .bases / FASTA | synthetic>
-    ebola  coll14  CanSNPer/<organism>                     from a --tables JSON (layout of
-                                                           tests/golden/testsuite_data.json)
+    ebola  coll14  CanSNPer/<organism>                     from the bundled tables (testsuite_tables.json) or
+                                                           a --tables JSON of the same layout
 """
 import argparse
 import json
@@ -34,6 +34,9 @@ def load_suites(names, genome=None, tables=None):
         G = genes.Genome.from_bases(synth.mtbc_genome(), 'MTB ancestor (synthetic)')
     elif genome:
         G = genes.Genome(genome, 'MTB ancestor')
+    if not tables:                          # the tables generated from the reference's data files, shipped with the package
+        bundled = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'testsuite_tables.json')
+        tables = bundled if os.path.exists(bundled) else None
     data = json.load(open(tables)) if tables else None
     for name in names:
         if name == 'MTBC' or name.startswith('MTBC/'):
@@ -149,7 +152,7 @@ def parser():
     p.add_argument('-p', '--progress', action='store_true')
     p.add_argument('-l', '--select', action='append', help='testsuite to load (see module docstring); may be repeated')
     p.add_argument('--genome', help='MTB ancestor genome (.bases / FASTA) for the MTBC suites, or "synthetic"')
-    p.add_argument('--tables', help='JSON with testsuite tables (ebola, coll14, CanSNPer)')
+    p.add_argument('--tables', help='JSON with testsuite tables (ebola, coll14, CanSNPer); default: the bundled ones')
     p.add_argument('-t', '--threads', type=int, default=DEFAULTS['threads'])
     p.add_argument('-Q', '--quality', type=int, default=DEFAULTS['quality'])
     p.add_argument('-e', '--errors', type=int, default=DEFAULTS['errors'])
