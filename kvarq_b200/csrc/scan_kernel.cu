@@ -1,22 +1,30 @@
 // sm_100a kernels of the KvarQ read-scanning path (reference: csrc/workhorse.c:976-1197).
 //
-// Persistent kernel, one CTA per SM, every WARP an independent worker (no block-wide barrier in
-// the steady state).  A warp claims 8 KiB tiles of the FastQ stream in stream order from a global
-// queue and runs the whole path on its tile:
-//   P1  coalesced 128-bit loads, 32 bytes per lane; straight from registers every 32-byte word
-//       is reduced to three bit planes kept in shared memory: newline mask, quality-pass mask
-//       (byte >= Amin) and 2-bit base codes.  The raw bytes are never staged.  A warp prefix scan
-//       ranks the newlines and scatters their positions; the tile's newline count is published
-//       and the line phase of the tile (newlines of its segment before it, mod 4) resolved by a
-//       lane-parallel decoupled look-back                                [workhorse.c:1018-1030]
+// kvq_scan_kernel: persistent, one CTA per SM, every WARP an independent worker (no block-wide barrier
+// in the steady state).  A warp claims 10 KiB tiles of the FastQ stream in stream order from a global
+// queue and runs the path on its tile:
+//   P1  coalesced 128-bit loads, 32 bytes per lane, rows through three register sets; straight from
+//       registers every 32-byte word is reduced to bit planes in shared memory: quality-pass mask
+//       (byte >= Amin) and 2-bit base codes; the newline mask stays in registers.  One packed warp scan
+//       ranks the newlines of three rows and their positions are scattered without divergent branches.
+//       The line phase of the tile (newlines of its segment before it, mod 4) is INFERRED from the
+//       tile's own line starts ('@' / '+' pattern), published at once and checked against the
+//       predecessor's prefix afterwards; an undecided tile walks back to the nearest prefix
+//       (decoupled look-back); a contradiction makes the host re-run the batch with exact phases
+//                                                                              [workhorse.c:1018-1030]
 //   P2  one lane per record: its 4 newlines, '@' / '+' sanity checks, Phred trim (first longest
 //       run >= Amin) on the quality-pass plane, histogram, length filter  [workhorse.c:1037-1103]
-//   P3  seed probes on the code plane: every read offset against the byte-per-key table T1
+//   P3  seed probes on the code plane: every read offset against the byte-per-key role table T1
 //       (template pieces) in shared memory, a few fixed read offsets against the bitmap T2 (all
 //       template offsets); seeds go to a small per-warp stack that is drained 32 at a time
-//   P4  bucket walk (tables in L2), XOR/popc Hamming verify on packed words, then warp-wide
-//       byte-exact confirm, canonical-seed dedupe, hit emission through atomics and the fused
-//       coverage update                                       [workhorse.c:1107-1175,408-443]
+//   P4  one candidate per seed and pass (table entries in L2), XOR/popc Hamming verify on packed
+//       words; the few survivors are queued for the emit kernel
+// kvq_emit_kernel: one warp per survivor -- byte-exact confirm, canonical-seed dedupe, hit emission
+// through atomics and the fused coverage update                    [workhorse.c:1107-1175,408-443]
+// kvq_long_kernel: records longer than a tile's spill rows / reads longer than 512 bases, exhaustively.
+// kvq_order_*: the hits of an HBM-resident scan in the reference's nthreads=1 order, exported into the
+// result's page-locked buffer.  kvq_reset_kernel / kvq_tail_kernel: a batch's start state; the tail of
+// the counter row for the all-reduce.
 // Reads or templates the seed scheme cannot cover take the exhaustive matcher (same acceptance
 // rule, every diagonal).  Acceptance rule: SURVEY.md Appendix B / workhorse.c:1112-1174.
 #include <cuda_runtime.h>
