@@ -402,7 +402,7 @@ __device__ __forceinline__ void scatter_newlines(WarpSmem &s, const KvqBatch &b,
 __device__ __forceinline__ int resolve_phase(const KvqBatch &b, int tile, int first, int n_tile, int lane)
 {
     volatile uint32_t *st = b.tile_status;
-    if (first) return 0;                            // published as an inclusive prefix by the look-ahead
+    if (first) return 0;                            // (the first tile of a segment: nothing in front of it; its owner publishes the inclusive prefix)
     int acc = 0;
     for (int j = tile - 1;;) {
         const int i = j - lane;
